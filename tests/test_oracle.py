@@ -1,0 +1,143 @@
+"""CPU tests: the restated oracle (oracle/lstm_oracle.py) against golden vectors produced by
+the reference's own modules (oracle/make_golden.py), plus internal consistency of the oracle
+(closed-form NLL vs the dense Woodbury path, generator statistics)."""
+import numpy as np
+import pytest
+import torch
+
+import lstm_oracle as O
+
+torch.set_num_threads(4)
+torch.set_float32_matmul_precision("highest")
+
+
+@pytest.fixture(scope="module")
+def data(golden_dir):
+    d = np.load(golden_dir / "golden_data.npz")
+    return {k: torch.from_numpy(d[k]) for k in d.files}
+
+
+def test_data_prep_matches_reference(data):
+    X, y, factor, inv_psi = O.build_dataset(data["r_stocks"], data["r_market"], 60, 30, 90, True,
+                                            data["alphas"], data["betas"])
+    assert torch.equal(X, data["X"])
+    assert torch.equal(y, data["y"])
+    assert torch.allclose(factor, data["factor"], rtol=0, atol=0)
+    assert torch.allclose(inv_psi, data["inv_psi"], rtol=1e-6)
+    a_hat, b_hat, _, _ = O.ols_targets(y[..., :2])
+    assert torch.allclose(a_hat, data["ols_alpha"], rtol=1e-6, atol=1e-7)
+    assert torch.allclose(b_hat, data["ols_beta"], rtol=1e-6, atol=1e-7)
+
+
+def _model_from_golden(g):
+    torch.manual_seed(int(g["meta"][1]))
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    return m
+
+
+@pytest.mark.parametrize("kind", ["mse", "nll", "combined"])
+def test_training_steps_match_reference(kind, data, golden_dir):
+    g = np.load(golden_dir / f"golden_{kind}.npz")
+    m = _model_from_golden(g)
+    # same seed -> same default init as the reference module
+    assert np.array_equal(O.flat_params(m).numpy(), g["init"])
+    assert [n for n, _ in m.named_parameters()] == list(g["names"])
+    opt = O.make_optimizer(m)
+    X, y, factor, inv_psi = data["X"], data["y"], data["factor"], data["inv_psi"]
+    order = [(0, 2), (2, 4), (0, 2)]
+    running = {"mse": [], "nll": []}
+    for s, (lo, hi) in enumerate(order):
+        batch = (X[lo:hi], y[lo:hi], factor[lo:hi], inv_psi[lo:hi])
+        m.train()
+        ls = O.batch_losses(m, batch, kind)
+        opt.zero_grad()
+        ls["total"].backward()
+        if s == 0:
+            g0 = O.flat_grads(m).numpy()
+            np.testing.assert_allclose(g0, g["grads0"], rtol=1e-5, atol=1e-6 * np.abs(g["grads0"]).max())
+        gn = O.clip_global_norm(list(m.parameters()), float(g["clip"]))
+        if s == 0:
+            assert float(gn) == pytest.approx(float(g["gnorm0"]), rel=1e-5)
+        opt.step()
+        assert float(ls["total"].detach()) == pytest.approx(float(g["losses"][s]), rel=1e-6)
+        for k in ("mse", "nll"):
+            if k in ls:
+                # the golden value is the on_epoch running metric (equal batch sizes -> mean so far)
+                running[k].append(float(ls[k].detach()))
+                assert np.mean(running[k]) == pytest.approx(float(g[k][s]), rel=1e-6)
+    np.testing.assert_allclose(O.flat_params(m).numpy(), g["final"], rtol=1e-5, atol=1e-7)
+    val = [O.eval_windows(m, X[w:w + 1], y[w:w + 1], factor[w:w + 1], inv_psi[w:w + 1], kind)["total"]
+           for w in (4, 5)]
+    np.testing.assert_allclose(val, g["val_total"], rtol=1e-5)
+    t = O.test_windows(m, X[4:6], y[4:6], factor[4:6], inv_psi[4:6])
+    assert t["mae"] == pytest.approx(float(g["test_mae"]), rel=1e-5)
+    assert t["nll"] == pytest.approx(float(g["test_nll"]), rel=1e-5)
+
+
+def test_closed_form_nll_equals_dense(data):
+    torch.manual_seed(0)
+    K, n = 300, 30
+    alpha = torch.randn(K, dtype=torch.float64) * 0.1
+    beta = (1 + 0.3 * torch.randn(K, dtype=torch.float64)).requires_grad_()
+    alpha.requires_grad_()
+    inv_psi = 1.0 / (0.05 + torch.rand(K, dtype=torch.float64))
+    tgt = torch.randn(K, n, dtype=torch.float64)
+    fm, fv = torch.tensor(0.07, dtype=torch.float64), torch.tensor(0.4, dtype=torch.float64)
+    dense = O.gaussian_nll_dense((alpha + beta * fm)[:, None],
+                                 O.woodbury_inverse_cov(beta[:, None], torch.diag(inv_psi), fv), tgt)
+    closed = O.gaussian_nll_closed_form(alpha, beta, inv_psi, fm, fv, tgt)
+    assert float(closed) == pytest.approx(float(dense), rel=1e-12)
+    gd = torch.autograd.grad(dense, [alpha, beta])
+    gc = torch.autograd.grad(closed, [alpha, beta])
+    for a, b in zip(gd, gc):
+        np.testing.assert_allclose(a.numpy(), b.numpy(), rtol=1e-9, atol=1e-9)
+
+
+def test_explicit_mask_lstm_equals_fused():
+    torch.manual_seed(3)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    e = O.ExplicitMaskLstm(m)
+    x = torch.randn(17, 60, 3)
+    a0, b0 = m(x)
+    a1, b1 = e(x)
+    assert torch.allclose(a0, a1, atol=1e-6) and torch.allclose(b0, b1, atol=1e-6)
+
+
+def test_plateau_schedule_matches_torch():
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.Adam([p], lr=1e-4)
+    ref = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode="min", factor=0.5, patience=2)
+    mine = O.PlateauSchedule(1e-4)
+    seq = [5.0, 4.0, 4.1, 4.2, 4.3, 4.0, 3.99999, 4.5, 4.6, 4.7, 4.8, 4.9, 1.0, 2.0, 2.0, 2.0, 2.0]
+    for v in seq:
+        ref.step(v)
+        assert mine.step(v) == pytest.approx(opt.param_groups[0]["lr"], rel=1e-12)
+
+
+def test_philox_known_answer():
+    # Random123 known-answer vectors for philox4x32-10
+    out = O.philox4x32_10(np.uint32(0), np.uint32(0), np.uint32(0), np.uint32(0), 0, 0)
+    assert [int(x) for x in out] == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
+    f = 0xFFFFFFFF
+    out = O.philox4x32_10(np.uint32(f), np.uint32(f), np.uint32(f), np.uint32(f), f, f)
+    assert [int(x) for x in out] == [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD]
+    out = O.philox4x32_10(np.uint32(0x243F6A88), np.uint32(0x85A308D3), np.uint32(0x13198A2E),
+                          np.uint32(0x03707344), 0xA4093822, 0x299F31D0)
+    assert [int(x) for x in out] == [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]
+
+
+def test_generator_distribution():
+    from scipy import stats
+    r_s, r_m, a, b = O.generate_days(0, 20000, 8, seed=1234)
+    t_m = (r_m.astype(np.float64) - O.MKT_LOC) / O.MKT_SCALE
+    assert stats.kstest(t_m, stats.t(5).cdf).pvalue > 1e-3
+    eps = (r_s.astype(np.float64) - a[:, None] - b[:, None] * r_m[None, :]) / O.IDIO_SCALE
+    assert stats.kstest(eps[3], stats.t(5).cdf).pvalue > 1e-3
+    # stocks are independent given the market
+    assert abs(np.corrcoef(eps[0], eps[1])[0, 1]) < 0.03
+    al, be = O.stock_coefficients(4000, seed=7)
+    assert stats.kstest((al - O.ALPHA_LOC) / O.ALPHA_SCALE, "norm").pvalue > 1e-3
+    assert stats.kstest((be - O.BETA_LOC) / O.BETA_SCALE, "norm").pvalue > 1e-3
+    # determinism / window addressing: window w == days [90w, 90w+90)
+    r2, m2, _, _ = O.generate_days(90 * 7, 90, 8, seed=1234)
+    assert np.array_equal(r2, r_s[:, 630:720]) and np.array_equal(m2, r_m[630:720])
