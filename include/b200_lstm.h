@@ -1,0 +1,180 @@
+/*
+ * b200_lstm.h -- C ABI of libb200lstm.so: the per-step training loop of the
+ * MarkoMiljkovic45/masters-thesis trainer as hand-written sm_100a CUDA kernels.
+ *
+ * The reference is pure Python over PyTorch/Lightning and has no FFI of its own; each
+ * entry point below replaces the LIBRARY CALL the reference makes at the cited
+ * file:line (paths relative to the reference checkout).  A binding a maintainer of
+ * the reference would add is shown in INTEGRATION.md (ctypes, ~40 lines).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host
+ *   - every buffer, including workspace, is owned and allocated by the caller
+ *     (query sizes with the *_bytes functions); the library never allocates
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*; NULL = the
+ *     legacy default stream); no call synchronises the device
+ *   - return value: 0 on success, negative on error (-1 invalid argument,
+ *     -2 unsupported configuration, -1000-cudaError for a CUDA runtime error);
+ *     b200_last_error() returns a thread-local message for the last failure
+ *   - fp32 everywhere in memory; int64 for row counts
+ *
+ * Memory layouts (N = n_windows * n_stocks sequences, T = lookback, n = target days,
+ * F = input features, H = hidden size, L = layers)
+ *   x          [T][N][F]     time-major look-back features [r_s, r_m, r_s*r_m(, r_s^2, r_m^2)]
+ *   y_stock    [N][n]        target-window stock returns
+ *   y_market   [n_windows][n]
+ *   factor     [n_windows][2]  (mean, unbiased variance) of the target-window market return
+ *   inv_psi    [N]           1 / unbiased residual variance of the per-window OLS
+ *   params / grads / adam m,v : one flat fp32 vector in torch state_dict order
+ *        for l in 0..L-1: weight_ih_l (4H x I_l), weight_hh_l (4H x H), bias_ih_l (4H), bias_hh_l (4H)
+ *        alpha_head.weight (H), alpha_head.bias (1), beta_head.weight (H), beta_head.bias (1)
+ *        with I_0 = F, I_l = H; gate row order i,f,g,o (torch.nn.LSTM)
+ *   stash_h, stash_c  [L][T][N][H]  hidden and cell state of every layer and step
+ *   hT         = stash_h + ((L-1)*T + (T-1)) * N * H      (final hidden of the top layer)
+ */
+#ifndef B200_LSTM_H
+#define B200_LSTM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+#define B200_OK 0
+#define B200_ERR_INVALID (-1)
+#define B200_ERR_UNSUPPORTED (-2)
+
+/* LSTM engine selector (`mode` arguments) */
+#define B200_MODE_FFMA 0      /* fp32 CUDA-core path: exact-fp32 reference engine */
+#define B200_MODE_TC_PRECISE 1 /* tcgen05 bf16x3 split (fp32-equivalent products), fp32 accumulate in TMEM */
+#define B200_MODE_TC_FAST 2    /* tcgen05 single bf16 product, fp32 accumulate */
+
+/* loss selector, configs/loss/{mse,nll,combined}.yaml */
+#define B200_LOSS_MSE 0
+#define B200_LOSS_NLL 1
+#define B200_LOSS_COMBINED 2
+
+B200_API int b200_version(void);
+B200_API const char* b200_last_error(void);
+/* 1 when the LSTM engine `mode` is compiled into this library, else 0 */
+B200_API int b200_mode_available(int mode);
+
+/* number of fp32 parameters of the model (src/model.py:88-97): 51,074 for F=3,H=64,L=2 */
+B200_API int64_t b200_param_count(int n_features, int hidden, int layers);
+/* offset (in floats) of layer l's weight_ih inside the flat vector; l == layers gives the heads */
+B200_API int64_t b200_param_offset(int n_features, int hidden, int layers, int l);
+
+/* ---------------------------------------------------------------- batch generation
+ * Replaces SyntheticLogReturns.generate (src/data.py:49-59, torch.distributions on the host),
+ * lookback_target_split / add_quadratic_features / ols_features (src/common.py:81-149) and the
+ * DataLoader collate + H2D copy (src/data.py:236-238): window w covers absolute days
+ * [w*stride, w*stride + lookback + target) of one Philox4x32-10 addressed series (generator
+ * specification: oracle/lstm_oracle.py "generator spec").  window_idx (int64, device) selects
+ * arbitrary windows; when NULL, windows first_window .. first_window+n_windows-1 are produced. */
+B200_API int b200_gen_batch(uint64_t seed, const int64_t* window_idx, int64_t first_window, int64_t n_windows,
+                   int n_stocks, int lookback, int target, int64_t stride, int n_features,
+                   float* x, float* y_stock, float* y_market, float* factor, float* inv_psi,
+                   void* stream);
+/* per-stock true alpha_i, beta_i of the run (src/data.py:53-54) */
+B200_API int b200_gen_coefficients(uint64_t seed, int n_stocks, float* alpha, float* beta, void* stream);
+/* raw Philox4x32-10 blocks, for bit-exact checks against the numpy specification:
+ * counters [n][4] uint32 -> out [n][4] uint32 */
+B200_API int b200_philox4x32(uint64_t seed, const uint32_t* counters, int64_t n, uint32_t* out, void* stream);
+/* inter-layer dropout keep-mask exactly as the LSTM kernels regenerate it: out [T][N][H] floats,
+ * 0 or 1/(1-p), for the INPUT of layer `layer` (1..L-1).  Replaces aten::bernoulli_ inside
+ * nn.LSTM(dropout=p) (src/model.py:92). */
+B200_API int b200_dropout_mask(uint64_t seed, int layer, int64_t n_seq, int T, int hidden, float p,
+                      float* out, void* stream);
+
+/* ---------------------------------------------------------------- LSTM encoder
+ * b200_lstm_fwd replaces self.lstm(lstm_input) (src/model.py:104, nn.LSTM -> oneDNN
+ * mkldnn_rnn_layer / cuDNN _cudnn_rnn); b200_lstm_bwd_layer replaces its autograd backward
+ * (mkldnn_rnn_layer_backward).  One launch sequence per layer; layers run bottom-up in fwd and
+ * must be called top-down (layer = L-1 .. 0) in bwd so that a data-parallel caller can start
+ * reducing a layer's gradients while the layers below are still running.
+ *
+ * training != 0 applies inter-layer dropout p with the Philox mask of b200_dropout_mask.
+ * workspace: at least b200_lstm_workspace_bytes(...) bytes, shared by fwd and bwd calls of a step. */
+B200_API size_t b200_lstm_workspace_bytes(int mode, int64_t n_seq, int T, int n_features, int hidden, int layers);
+B200_API int b200_lstm_fwd(int mode, const float* params, int n_features, int hidden, int layers,
+                  const float* x, int64_t n_seq, int T, float* stash_h, float* stash_c,
+                  float dropout_p, uint64_t dropout_seed, int training,
+                  void* workspace, size_t workspace_bytes, void* stream);
+/* dhT: [N][H] gradient of the loss w.r.t. the top layer's final hidden state (from the heads
+ * kernels).  grads: flat gradient vector; the call OVERWRITES the slice of layer `layer`. */
+B200_API int b200_lstm_bwd_layer(int mode, int layer, const float* params, int n_features, int hidden, int layers,
+                        const float* x, int64_t n_seq, int T, const float* stash_h, const float* stash_c,
+                        const float* dhT, float* grads,
+                        float dropout_p, uint64_t dropout_seed, int training,
+                        void* workspace, size_t workspace_bytes, void* stream);
+/* all layers, top-down */
+B200_API int b200_lstm_bwd(int mode, const float* params, int n_features, int hidden, int layers,
+                  const float* x, int64_t n_seq, int T, const float* stash_h, const float* stash_c,
+                  const float* dhT, float* grads,
+                  float dropout_p, uint64_t dropout_seed, int training,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- heads + objective
+ * Replaces alpha_head/beta_head (src/model.py:107-108, addmm), the decoder arithmetic of
+ * _shared_step (src/model.py:192-202, 234-249, 286-306), torchmetrics MeanSquaredError,
+ * inverse_returns_covariance (src/common.py:50-78) + MultivariateGaussianNLLLoss
+ * (src/model.py:54-69: matmul/trace/logdet) and their autograd backward.  The NLL uses the
+ * diagonal-plus-rank-1 closed form, O(N*n) instead of O(N^2).
+ *
+ * Rows are grouped into NLL groups of windows_per_group consecutive windows; a group is one joint
+ * Gaussian over windows_per_group*n_stocks rows using the FIRST window's factor (the reference's
+ * literal batch semantics, src/model.py:237-247).  Training: windows_per_group = n_windows.
+ * Validation/test (batch 1, src/data.py:241-244): windows_per_group = 1.
+ *
+ * losses_out[4] = { mse (mean over all elements), nll (mean over groups),
+ *                   total (mse | nll | nll + mse_weight*mse), mae (mean |pred - target|) }
+ * dhT (nullable: forward only) [N][H]; head_grads (nullable) [2H+2] in flat-vector order;
+ * alpha_out/beta_out (nullable) [N].  grad_scale multiplies every gradient (1/world_size under
+ * data parallelism so that an NCCL sum yields the DDP mean). */
+B200_API size_t b200_heads_workspace_bytes(int64_t n_windows, int n_stocks, int n_target, int hidden);
+B200_API int b200_heads_loss_fwd_bwd(int loss_kind, float mse_weight, const float* head_params, int hidden,
+                            const float* hT, const float* y_stock, const float* y_market,
+                            const float* factor, const float* inv_psi,
+                            int64_t n_windows, int n_stocks, int n_target, int64_t windows_per_group,
+                            float grad_scale, float* alpha_out, float* beta_out, float* losses_out,
+                            float* dhT, float* head_grads,
+                            void* workspace, size_t workspace_bytes, void* stream);
+/* the two names SURVEY.md section 8b lists; thin wrappers over the call above */
+B200_API int b200_heads_mse_fwd_bwd(const float* head_params, int hidden, const float* hT,
+                           const float* y_stock, const float* y_market,
+                           int64_t n_windows, int n_stocks, int n_target, float grad_scale,
+                           float* losses_out, float* dhT, float* head_grads,
+                           void* workspace, size_t workspace_bytes, void* stream);
+B200_API int b200_heads_nll_fwd_bwd(const float* head_params, int hidden, const float* hT,
+                           const float* y_stock, const float* factor, const float* inv_psi,
+                           int64_t n_windows, int n_stocks, int n_target, int64_t windows_per_group,
+                           float grad_scale, float* losses_out, float* dhT, float* head_grads,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- gradient norm, clip, Adam
+ * b200_grad_sqnorm replaces the linalg_vector_norm calls of clip_grad_norm_ (Lightning
+ * gradient_clip_val, train.py:171): sqnorm_out[0] = sum g^2 (fp32, deterministic two-level
+ * reduction).  workspace: b200_sqnorm_workspace_bytes(count). */
+B200_API size_t b200_sqnorm_workspace_bytes(int64_t count);
+B200_API int b200_grad_sqnorm(const float* grads, int64_t count, float* sqnorm_out,
+                     void* workspace, size_t workspace_bytes, void* stream);
+/* Replaces the clip scaling + torch.optim.Adam.step (src/model.py:150-154): L2-coupled weight
+ * decay, bias correction, eps outside the sqrt(v_hat).  clip_val <= 0 or sqnorm == NULL disables
+ * clipping; otherwise g *= min(1, clip_val / (sqrt(*sqnorm) + 1e-6)).  step is 1-based.
+ * zero_grad != 0 clears g after use (Lightning's zero_grad). */
+B200_API int b200_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t count,
+                   float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                   float clip_val, const float* sqnorm, int zero_grad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_LSTM_H */

@@ -1,0 +1,120 @@
+// C-ABI glue: error reporting, parameter-vector geometry and the LSTM engine dispatch.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return -1000 - (int)e;
+}
+
+// engines (lstm_ffma.cu, lstm_tc.cu)
+size_t ffma_workspace_bytes(int64_t N, int T, int L);
+int ffma_fwd(const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h, float* stash_c,
+             float p, uint64_t seed, int training, cudaStream_t st);
+int ffma_bwd_layer(int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
+                   const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
+                   int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+bool tc_available();
+size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L);
+int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
+           float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
+                 const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
+                 int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_version(void) { return 100; }
+extern "C" const char* b200_last_error(void) { return g_err; }
+extern "C" int b200_mode_available(int mode) {
+    if (mode == B200_MODE_FFMA) return 1;
+    if (mode == B200_MODE_TC_PRECISE || mode == B200_MODE_TC_FAST) return tc_available() ? 1 : 0;
+    return 0;
+}
+
+extern "C" int64_t b200_param_offset(int F, int H, int L, int l) {
+    if (F <= 0 || H <= 0 || L <= 0 || l < 0 || l > L) return -1;
+    int64_t off = 0;
+    for (int i = 0; i < l; ++i) {
+        const int64_t in = i == 0 ? F : H;
+        off += 4LL * H * in + 4LL * H * H + 8LL * H;
+    }
+    return off;
+}
+
+extern "C" int64_t b200_param_count(int F, int H, int L) {
+    if (F <= 0 || H <= 0 || L <= 0) return -1;
+    return b200_param_offset(F, H, L, L) + 2LL * H + 2;
+}
+
+static int check_lstm_args(const char* who, int mode, const float* params, int F, int H, int L, const float* x,
+                           int64_t N, int T, const void* sh, const void* sc, float p) {
+    B200_CHECK_ARG(mode >= 0 && mode <= 2, "%s: unknown mode %d", who, mode);
+    B200_CHECK_ARG(params && x && sh && sc, "%s: null pointer", who);
+    B200_CHECK_ARG(F > 0 && F <= 8 && H > 0 && L > 0 && L < 65536, "%s: bad model dims F=%d H=%d L=%d", who, F, H, L);
+    B200_CHECK_ARG(N > 0 && T > 0 && T < 65536, "%s: bad batch dims N=%lld T=%d", who, (long long)N, T);
+    B200_CHECK_ARG(p >= 0.f && p < 1.f, "%s: dropout must be in [0,1), got %f", who, p);
+    return B200_OK;
+}
+
+extern "C" size_t b200_lstm_workspace_bytes(int mode, int64_t n_seq, int T, int n_features, int hidden, int layers) {
+    if (n_seq <= 0 || T <= 0 || layers <= 0) return 0;
+    // generous default: room for a 64 Ki-sequence da chunk; callers may pass less (smaller chunks)
+    size_t ffma = ffma_workspace_bytes(n_seq, T, layers);
+    if (mode == B200_MODE_FFMA) return ffma;
+    size_t tc = tc_workspace_bytes(mode, n_seq, T, n_features, hidden, layers);
+    return tc > ffma ? tc : ffma;
+}
+
+extern "C" int b200_lstm_fwd(int mode, const float* params, int n_features, int hidden, int layers, const float* x,
+                             int64_t n_seq, int T, float* stash_h, float* stash_c, float dropout_p,
+                             uint64_t dropout_seed, int training, void* workspace, size_t workspace_bytes, void* stream) {
+    int rc = check_lstm_args("lstm_fwd", mode, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p);
+    if (rc) return rc;
+    if (mode == B200_MODE_FFMA)
+        return ffma_fwd(params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p, dropout_seed, training,
+                        (cudaStream_t)stream);
+    return tc_fwd(mode, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p, dropout_seed, training,
+                  workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int b200_lstm_bwd_layer(int mode, int layer, const float* params, int n_features, int hidden, int layers,
+                                   const float* x, int64_t n_seq, int T, const float* stash_h, const float* stash_c,
+                                   const float* dhT, float* grads, float dropout_p, uint64_t dropout_seed, int training,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+    int rc = check_lstm_args("lstm_bwd", mode, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p);
+    if (rc) return rc;
+    B200_CHECK_ARG(layer >= 0 && layer < layers, "lstm_bwd: layer %d out of range", layer);
+    B200_CHECK_ARG(dhT && grads && workspace, "lstm_bwd: null pointer");
+    if (mode == B200_MODE_FFMA)
+        return ffma_bwd_layer(layer, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dhT, grads, dropout_p,
+                              dropout_seed, training, workspace, workspace_bytes, (cudaStream_t)stream);
+    return tc_bwd_layer(mode, layer, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dhT, grads, dropout_p,
+                        dropout_seed, training, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int b200_lstm_bwd(int mode, const float* params, int n_features, int hidden, int layers, const float* x,
+                             int64_t n_seq, int T, const float* stash_h, const float* stash_c, const float* dhT,
+                             float* grads, float dropout_p, uint64_t dropout_seed, int training, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+    for (int l = layers - 1; l >= 0; --l) {
+        int rc = b200_lstm_bwd_layer(mode, l, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dhT, grads,
+                                     dropout_p, dropout_seed, training, workspace, workspace_bytes, stream);
+        if (rc) return rc;
+    }
+    return B200_OK;
+}

@@ -1,0 +1,209 @@
+// On-device batch generation: Philox4x32-10 -> Box-Muller -> Student-t(5) single-factor DGP,
+// fused with windowing, the interaction feature and the per-window OLS targets.
+//
+// Replaces (reference file:line)
+//   SyntheticLogReturns.generate          src/data.py:49-59   (distribution parameters 36-39)
+//   lookback_target_split                 src/common.py:81-112
+//   add_quadratic_features                src/common.py:115-130
+//   ols_features / _batched_ols           src/common.py:132-149, 33-47
+//   DataLoader collate + pinned H2D       src/data.py:236-238
+// The generator is a pure function of (seed, stock, absolute day); the written specification
+// is oracle/lstm_oracle.py ("generator spec"), which the tests compare against.
+//
+// One CTA per window: the (S x 90) block of returns is generated into shared memory once, then
+// written out time-major ([T][N][F], coalesced 4-byte stores over stock*F) and reduced per stock
+// for the OLS targets.  HBM-bound in principle (writes (T*F + n + 1) * 4 B per sequence), in
+// practice Philox/Box-Muller ALU bound; either way <1% of a training step.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr uint32_t ID_MARKET = 0xFFFFFFFFu;
+constexpr uint32_t ID_COEFF = 0xFFFFFFFEu;
+
+__device__ __forceinline__ float u01(uint32_t x) { return ((float)(x >> 8) + 0.5f) * 5.9604644775390625e-08f; }
+
+__device__ __forceinline__ void box_muller(uint32_t xa, uint32_t xb, float& z0, float& z1) {
+    float r = sqrtf(-2.0f * logf(u01(xa)));
+    float ang = 6.283185307179586f * u01(xb);
+    float s, c;
+    sincosf(ang, &s, &c);
+    z0 = r * c;
+    z1 = r * s;
+}
+
+// Student-t(5) = Z0 / sqrt((Z1^2+...+Z5^2)/5), exact for integer df; two Philox blocks per draw.
+__device__ __forceinline__ float student_t5(uint64_t day, uint32_t ident, uint64_t seed) {
+    uint32_t lo = (uint32_t)day, hi = (uint32_t)(day >> 32);
+    U4 a = philox4x32_10(lo, hi, ident, 0u, (uint32_t)seed, (uint32_t)(seed >> 32));
+    U4 b = philox4x32_10(lo, hi, ident, 1u, (uint32_t)seed, (uint32_t)(seed >> 32));
+    float z0, z1, z2, z3, z4, z5;
+    box_muller(a.x, a.y, z0, z1);
+    box_muller(a.z, a.w, z2, z3);
+    box_muller(b.x, b.y, z4, z5);
+    float chi = z1 * z1 + z2 * z2 + z3 * z3 + z4 * z4 + z5 * z5;
+    return z0 / sqrtf(chi * 0.2f);
+}
+
+__device__ __forceinline__ void stock_coeff(uint64_t seed, uint32_t i, float& alpha, float& beta) {
+    U4 x = philox4x32_10(i, 0u, ID_COEFF, 0u, (uint32_t)seed, (uint32_t)(seed >> 32));
+    float z0, z1;
+    box_muller(x.x, x.y, z0, z1);
+    alpha = 0.0098f + 0.1271f * z0;   // src/data.py:38
+    beta = 0.9444f + 0.3521f * z1;    // src/data.py:39
+}
+
+__global__ void __launch_bounds__(256)
+gen_batch_kernel(uint64_t seed, const int64_t* __restrict__ window_idx, int64_t first_window, int64_t n_windows,
+                 int S, int T, int n, int64_t stride, int F,
+                 float* __restrict__ x, float* __restrict__ y_stock, float* __restrict__ y_market,
+                 float* __restrict__ factor, float* __restrict__ inv_psi) {
+    extern __shared__ float sm[];
+    const int W = T + n;
+    float* rs = sm;               // [S][W]
+    float* rm = rs + S * W;       // [W]
+    float* coef = rm + W;         // [S][2]
+    float* stat = coef + 2 * S;   // [2]: market mean, centred sum of squares
+
+    const int64_t N = n_windows * S;
+    for (int64_t wl = blockIdx.x; wl < n_windows; wl += gridDim.x) {
+        const int64_t w = window_idx ? window_idx[wl] : first_window + wl;
+        const uint64_t day0 = (uint64_t)w * (uint64_t)stride;
+        const int64_t row0 = wl * S;
+
+        for (int d = threadIdx.x; d < W; d += blockDim.x)
+            rm[d] = 0.0678f + 0.5099f * student_t5(day0 + d, ID_MARKET, seed);   // src/data.py:36
+        for (int s = threadIdx.x; s < S; s += blockDim.x) stock_coeff(seed, (uint32_t)s, coef[2 * s], coef[2 * s + 1]);
+        __syncthreads();
+        for (int i = threadIdx.x; i < S * W; i += blockDim.x) {
+            int s = i / W, d = i - s * W;
+            float eps = 0.3140f * student_t5(day0 + d, (uint32_t)s, seed);          // src/data.py:37
+            rs[i] = (coef[2 * s] + coef[2 * s + 1] * rm[d]) + eps;
+        }
+        if (threadIdx.x == 0) {
+            float mean = 0.f;
+            for (int j = 0; j < n; ++j) mean += rm[T + j];
+            mean /= (float)n;
+            float ss = 0.f;
+            for (int j = 0; j < n; ++j) { float d = rm[T + j] - mean; ss += d * d; }
+            stat[0] = mean;
+            stat[1] = ss;
+            factor[2 * wl] = mean;
+            factor[2 * wl + 1] = ss / (float)(n - 1);      // torch.var: unbiased (src/common.py:141-144)
+        }
+        __syncthreads();
+
+        // look-back features, time-major
+        const int SF = S * F;
+        for (int i = threadIdx.x; i < T * SF; i += blockDim.x) {
+            int t = i / SF, r = i - t * SF;
+            int s = r / F, f = r - s * F;
+            float a = rs[s * W + t], m = rm[t];
+            float v = f == 0 ? a : f == 1 ? m : f == 2 ? a * m : f == 3 ? a * a : m * m;
+            x[((int64_t)t * N + row0) * F + r] = v;
+        }
+        for (int i = threadIdx.x; i < S * n; i += blockDim.x) {
+            int s = i / n, j = i - s * n;
+            y_stock[row0 * n + i] = rs[s * W + T + j];
+        }
+        for (int j = threadIdx.x; j < n; j += blockDim.x) y_market[wl * n + j] = rm[T + j];
+
+        // per-stock OLS on the target window (closed form of pinv(X^T X) X^T y for [1, m])
+        const float mbar = stat[0], smm = stat[1];
+        for (int s = threadIdx.x; s < S; s += blockDim.x) {
+            const float* r = rs + s * W + T;
+            float rbar = 0.f;
+            for (int j = 0; j < n; ++j) rbar += r[j];
+            rbar /= (float)n;
+            float smr = 0.f;
+            for (int j = 0; j < n; ++j) smr += (rm[T + j] - mbar) * (r[j] - rbar);
+            float b = smr / smm, a = rbar - b * mbar;
+            float ebar = 0.f;
+            for (int j = 0; j < n; ++j) ebar += r[j] - (a + b * rm[T + j]);
+            ebar /= (float)n;
+            float see = 0.f;
+            for (int j = 0; j < n; ++j) { float e = r[j] - (a + b * rm[T + j]) - ebar; see += e * e; }
+            inv_psi[row0 + s] = (float)(n - 1) / see;      // 1 / unbiased residual variance
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void gen_coeff_kernel(uint64_t seed, int S, float* alpha, float* beta) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < S) stock_coeff(seed, (uint32_t)s, alpha[s], beta[s]);
+}
+
+__global__ void philox_kernel(uint64_t seed, const uint32_t* __restrict__ ctr, int64_t n, uint32_t* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    U4 r = philox4x32_10(ctr[4 * i], ctr[4 * i + 1], ctr[4 * i + 2], ctr[4 * i + 3], (uint32_t)seed, (uint32_t)(seed >> 32));
+    out[4 * i] = r.x; out[4 * i + 1] = r.y; out[4 * i + 2] = r.z; out[4 * i + 3] = r.w;
+}
+
+__global__ void dropout_mask_kernel(uint64_t seed, int layer, int64_t N, int T, int H, float p, float* __restrict__ out) {
+    const int HB = H / 8;
+    const int64_t total = (int64_t)T * N * HB;
+    const uint32_t thr = dropout_threshold(p);
+    const float scale = 1.0f / (1.0f - p);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int ub = (int)(i % HB);
+        int64_t rt = i / HB;
+        int64_t row = rt % N;
+        int t = (int)(rt / N);
+        U4 b = dropout_block(seed, layer, row, t, ub);
+        float* o = out + ((int64_t)t * N + row) * H + ub * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = dropout_lane16(b, j) >= thr ? scale : 0.0f;
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_gen_batch(uint64_t seed, const int64_t* window_idx, int64_t first_window, int64_t n_windows,
+                              int n_stocks, int lookback, int target, int64_t stride, int n_features,
+                              float* x, float* y_stock, float* y_market, float* factor, float* inv_psi,
+                              void* stream) {
+    B200_CHECK_ARG(n_windows >= 0 && n_stocks > 0 && lookback > 0 && target > 1 && stride > 0,
+                   "gen_batch: bad sizes (n_windows=%lld S=%d T=%d n=%d)", (long long)n_windows, n_stocks, lookback, target);
+    B200_CHECK_ARG(n_features == 3 || n_features == 5, "gen_batch: n_features must be 3 or 5, got %d", n_features);
+    B200_CHECK_ARG(x && y_stock && y_market && factor && inv_psi, "gen_batch: null output pointer");
+    if (n_windows == 0) return B200_OK;
+    size_t smem = ((size_t)n_stocks * (lookback + target) + (lookback + target) + 2 * n_stocks + 2) * sizeof(float);
+    B200_CHECK_ARG(smem <= 200 * 1024, "gen_batch: window of %d stocks x %d days does not fit shared memory", n_stocks,
+                   lookback + target);
+    B200_CUDA(cudaFuncSetAttribute(gen_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t grid = n_windows < (int64_t)num_sms() * 16 ? n_windows : (int64_t)num_sms() * 16;
+    gen_batch_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(seed, window_idx, first_window, n_windows, n_stocks,
+                                                                         lookback, target, stride, n_features, x, y_stock,
+                                                                         y_market, factor, inv_psi);
+    B200_LAUNCH_CHECK("gen_batch_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_gen_coefficients(uint64_t seed, int n_stocks, float* alpha, float* beta, void* stream) {
+    B200_CHECK_ARG(n_stocks > 0 && alpha && beta, "gen_coefficients: bad arguments");
+    gen_coeff_kernel<<<(n_stocks + 127) / 128, 128, 0, (cudaStream_t)stream>>>(seed, n_stocks, alpha, beta);
+    B200_LAUNCH_CHECK("gen_coeff_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_philox4x32(uint64_t seed, const uint32_t* counters, int64_t n, uint32_t* out, void* stream) {
+    B200_CHECK_ARG(n >= 0 && (n == 0 || (counters && out)), "philox4x32: bad arguments");
+    if (n == 0) return B200_OK;
+    philox_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, counters, n, out);
+    B200_LAUNCH_CHECK("philox_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_dropout_mask(uint64_t seed, int layer, int64_t n_seq, int T, int hidden, float p, float* out,
+                                 void* stream) {
+    B200_CHECK_ARG(n_seq > 0 && T > 0 && hidden > 0 && hidden % 8 == 0 && out, "dropout_mask: bad sizes");
+    B200_CHECK_ARG(p >= 0.f && p < 1.f, "dropout_mask: p must be in [0,1), got %f", p);
+    B200_CHECK_ARG(layer >= 1 && layer < 65536 && T < 65536, "dropout_mask: layer/T out of range");
+    dropout_mask_kernel<<<num_sms() * 8, 256, 0, (cudaStream_t)stream>>>(seed, layer, n_seq, T, hidden, p, out);
+    B200_LAUNCH_CHECK("dropout_mask_kernel");
+    return B200_OK;
+}

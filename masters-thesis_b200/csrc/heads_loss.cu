@@ -1,0 +1,340 @@
+// alpha/beta heads + objective + their gradients, as four small bandwidth-bound kernels.
+//
+// Replaces (reference file:line)
+//   alpha_head / beta_head (addmm)                       src/model.py:107-108
+//   decoder r_pred = alpha + beta * r_m, MSE metric      src/model.py:199-206 (torchmetrics MeanSquaredError)
+//   inverse_returns_covariance (dense Woodbury)          src/common.py:50-78
+//   MultivariateGaussianNLLLoss (matmul, trace, logdet)  src/model.py:54-69
+//   combined objective nll + mse_weight * mse            src/model.py:308-319
+//   autograd backward of all of the above
+//
+// NLL closed form.  With p_i = 1/psi_i, d_it = r_it - alpha_i - beta_i*mu, s = sum p_i beta_i^2,
+// Dn = 1/sigma^2 + s, u_t = sum_i p_i beta_i d_it, the inverse covariance Psi^-1 - (Psi^-1 b)(Psi^-1 b)^T / Dn
+// is diagonal plus rank one, so
+//   logdet = sum ln p_i - ln(1 + sigma^2 s)          quad = sum_t [ sum_i p_i d_it^2 - u_t^2 / Dn ]
+//   L = 0.5 [ n (K ln 2pi - logdet) + quad ]
+//   dL/dalpha_i = -p_i sum_t d_it + p_i beta_i sum_t u_t / Dn
+//   dL/dbeta_i  = mu dL/dalpha_i - p_i sum_t u_t d_it / Dn + p_i beta_i sum_t u_t^2 / Dn^2 + n sigma^2 p_i beta_i / (1 + sigma^2 s)
+// (validated against autograd through the dense reference path in tests/test_oracle.py).
+//
+// Kernels: K1 rows -> alpha, beta and per-window partial sums (fp64); K2 windows -> group statistics and
+// per-group losses; K2b groups -> losses_out; K3 rows -> dalpha, dbeta, dhT and per-window head-gradient
+// partials; K4 partials -> head gradients.  All cross-row reductions are fixed-order (deterministic).
+// Algorithmic HBM bytes per sequence: K1 reads hT (4H) + targets (4n); K3 reads hT + targets again and
+// writes dhT (4H): 12H + 8n + ~16 = 1,024 B at H=64, n=30.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int HEADS_THREADS = 128;
+constexpr int HEADS_WARPS = HEADS_THREADS / 32;
+constexpr int MAX_N_TARGET = 32;   // one lane per target day
+constexpr int PW_FIXED = 8;        // [0] sse [1] sae [2] s [3] sum ln p [4] sum p d^2 [5..7] unused, then u_t
+
+struct HeadsWs {
+    float* alpha;    // [N]
+    float* beta;     // [N]
+    double* wpart;   // [B][PW]
+    float* gstat;    // [G][PW]   0 mu, 1 1/Dn, 2 sum u/Dn, 3 sum u^2/Dn^2, 4 n s2/(1+s2 s), 8.. u_t/Dn
+    double* gloss;   // [G][4]    nll, sse, sae
+    float* hpart;    // [B][2H+2]
+};
+
+__host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static size_t heads_ws_layout(int64_t B, int S, int n, int H, int64_t G, char* base, HeadsWs* ws) {
+    const int PW = PW_FIXED + n;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return base ? base + o : (char*)nullptr; };
+    char* a = take((size_t)B * S * 4);
+    char* b = take((size_t)B * S * 4);
+    char* w = take((size_t)B * PW * 8);
+    char* g = take((size_t)G * PW * 4);
+    char* l = take((size_t)G * 4 * 8);
+    char* h = take((size_t)B * (2 * H + 2) * 4);
+    if (ws) { ws->alpha = (float*)a; ws->beta = (float*)b; ws->wpart = (double*)w; ws->gstat = (float*)g; ws->gloss = (double*)l; ws->hpart = (float*)h; }
+    return off;
+}
+
+// K1 ------------------------------------------------------------------------------------------
+template <int H>
+__global__ void __launch_bounds__(HEADS_THREADS)
+heads_stats_kernel(const float* __restrict__ hp, const float* __restrict__ hT, const float* __restrict__ y_stock,
+                   const float* __restrict__ y_market, const float* __restrict__ factor, const float* __restrict__ inv_psi,
+                   int S, int n, int64_t wpg, bool do_nll, float* __restrict__ alpha_o, float* __restrict__ beta_o,
+                   double* __restrict__ wpart) {
+    constexpr int HL = H / 32;
+    const int PW = PW_FIXED + n;
+    const int64_t w = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ float red[HEADS_WARPS][PW_FIXED + MAX_N_TARGET];
+
+    float wa[HL], wb[HL];
+#pragma unroll
+    for (int i = 0; i < HL; ++i) { wa[i] = hp[lane + 32 * i]; wb[i] = hp[H + 1 + lane + 32 * i]; }
+    const float ba = hp[H], bb = hp[2 * H + 1];
+    const float m = (y_market && lane < n) ? y_market[w * n + lane] : 0.f;
+    float mu = 0.f;
+    if (do_nll) mu = factor[2 * ((w / wpg) * wpg)];
+
+    float sse = 0.f, sae = 0.f, spq = 0.f, uacc = 0.f, s_acc = 0.f, lp_acc = 0.f;
+    for (int r = warp; r < S; r += HEADS_WARPS) {
+        const int64_t row = w * S + r;
+        const float* h = hT + row * H;
+        float pa = 0.f, pb = 0.f;
+#pragma unroll
+        for (int i = 0; i < HL; ++i) { float hv = h[lane + 32 * i]; pa += hv * wa[i]; pb += hv * wb[i]; }
+        const float al = warp_sum(pa) + ba, be = warp_sum(pb) + bb;
+        if (lane == 0) { alpha_o[row] = al; beta_o[row] = be; }
+        const float rt = lane < n ? y_stock[row * n + lane] : 0.f;
+        if (y_market && lane < n) { float e = al + be * m - rt; sse += e * e; sae += fabsf(e); }
+        if (do_nll) {
+            const float p = inv_psi[row];
+            if (lane < n) { float d = rt - (al + be * mu); spq += p * d * d; uacc += p * be * d; }
+            if (lane == 0) { s_acc += p * be * be; lp_acc += logf(p); }
+        }
+    }
+    sse = warp_sum(sse); sae = warp_sum(sae); spq = warp_sum(spq);
+    if (lane == 0) { red[warp][0] = sse; red[warp][1] = sae; red[warp][2] = s_acc; red[warp][3] = lp_acc; red[warp][4] = spq; }
+    red[warp][PW_FIXED + lane] = uacc;
+    __syncthreads();
+    for (int c = threadIdx.x; c < PW; c += HEADS_THREADS) {
+        double v = 0.0;
+        if (c < 5 || c >= PW_FIXED)
+            for (int q = 0; q < HEADS_WARPS; ++q) v += (double)red[q][c];
+        wpart[w * PW + c] = v;
+    }
+}
+
+// K2 ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+heads_group_kernel(const double* __restrict__ wpart, const float* __restrict__ factor, int S, int n, int64_t wpg,
+                   bool do_nll, float* __restrict__ gstat, double* __restrict__ gloss) {
+    const int PW = PW_FIXED + n;
+    const int64_t g = blockIdx.x;
+    __shared__ double part[4][64];
+    __shared__ double tot[64];
+    const int c = threadIdx.x & 63, q = threadIdx.x >> 6;
+    double v = 0.0;
+    if (c < PW)
+        for (int64_t i = q; i < wpg; i += 4) v += wpart[(g * wpg + i) * PW + c];
+    part[q][c] = v;
+    __syncthreads();
+    if (threadIdx.x < 64) tot[c] = (part[0][c] + part[1][c]) + (part[2][c] + part[3][c]);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double nll = 0.0;
+        if (do_nll) {
+            const double mu = factor[2 * g * wpg], s2 = factor[2 * g * wpg + 1];
+            const double s = tot[2], lp = tot[3], pq = tot[4];
+            const double Dn = 1.0 / s2 + s;
+            double su = 0.0, su2 = 0.0;
+            for (int t = 0; t < n; ++t) { double u = tot[PW_FIXED + t]; su += u; su2 += u * u; gstat[g * PW + PW_FIXED + t] = (float)(u / Dn); }
+            const double K = (double)wpg * S;
+            const double logdet = lp - log1p(s2 * s);
+            const double quad = pq - su2 / Dn;
+            nll = 0.5 * ((double)n * (K * 1.8378770664093453 - logdet) + quad);
+            gstat[g * PW + 0] = (float)mu;
+            gstat[g * PW + 1] = (float)(1.0 / Dn);
+            gstat[g * PW + 2] = (float)(su / Dn);
+            gstat[g * PW + 3] = (float)(su2 / (Dn * Dn));
+            gstat[g * PW + 4] = (float)((double)n * s2 / (1.0 + s2 * s));
+        }
+        gloss[g * 4 + 0] = nll;
+        gloss[g * 4 + 1] = tot[0];
+        gloss[g * 4 + 2] = tot[1];
+    }
+}
+
+// K2b -----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+heads_final_kernel(const double* __restrict__ gloss, int64_t G, double n_elems, int loss_kind, float mse_weight,
+                   float* __restrict__ losses) {
+    __shared__ double red[3][256];
+    double a = 0, b = 0, c = 0;
+    for (int64_t g = threadIdx.x; g < G; g += 256) { a += gloss[g * 4]; b += gloss[g * 4 + 1]; c += gloss[g * 4 + 2]; }
+    red[0][threadIdx.x] = a; red[1][threadIdx.x] = b; red[2][threadIdx.x] = c;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) for (int k = 0; k < 3; ++k) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double nll = red[0][0] / (double)G, mse = red[1][0] / n_elems, mae = red[2][0] / n_elems;
+        losses[0] = (float)mse;
+        losses[1] = (float)nll;
+        losses[2] = (float)(loss_kind == B200_LOSS_MSE ? mse : loss_kind == B200_LOSS_NLL ? nll : nll + (double)mse_weight * mse);
+        losses[3] = (float)mae;
+    }
+}
+
+// K3 ------------------------------------------------------------------------------------------
+template <int H>
+__global__ void __launch_bounds__(HEADS_THREADS)
+heads_grad_kernel(const float* __restrict__ hp, const float* __restrict__ hT, const float* __restrict__ y_stock,
+                  const float* __restrict__ y_market, const float* __restrict__ inv_psi,
+                  const float* __restrict__ alpha_i, const float* __restrict__ beta_i, const float* __restrict__ gstat,
+                  int S, int n, int64_t wpg, float c_mse, float c_nll, float* __restrict__ dhT, float* __restrict__ hpart) {
+    constexpr int HL = H / 32;
+    const int PW = PW_FIXED + n;
+    const int64_t w = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ float red[HEADS_WARPS][2 * H + 2];
+
+    float wa[HL], wb[HL], ga[HL], gb[HL];
+#pragma unroll
+    for (int i = 0; i < HL; ++i) { wa[i] = hp[lane + 32 * i]; wb[i] = hp[H + 1 + lane + 32 * i]; ga[i] = 0.f; gb[i] = 0.f; }
+    float gba = 0.f, gbb = 0.f;
+    const bool do_mse = c_mse != 0.f, do_nll = c_nll != 0.f;
+    const float m = (do_mse && lane < n) ? y_market[w * n + lane] : 0.f;
+    const float* gs = gstat + (w / wpg) * PW;
+    float mu = 0.f, rDn = 0.f, suD = 0.f, su2D = 0.f, c4 = 0.f, uD = 0.f;
+    if (do_nll) { mu = gs[0]; rDn = gs[1]; suD = gs[2]; su2D = gs[3]; c4 = gs[4]; uD = lane < n ? gs[PW_FIXED + lane] : 0.f; }
+    (void)rDn;
+
+    for (int r = warp; r < S; r += HEADS_WARPS) {
+        const int64_t row = w * S + r;
+        const float al = alpha_i[row], be = beta_i[row];
+        const float rt = lane < n ? y_stock[row * n + lane] : 0.f;
+        float da = 0.f, db = 0.f;
+        if (do_mse) {
+            float e = lane < n ? al + be * m - rt : 0.f;
+            float se = warp_sum(e), sem = warp_sum(e * m);
+            da += c_mse * se;
+            db += c_mse * sem;
+        }
+        if (do_nll) {
+            const float p = inv_psi[row];
+            float d = lane < n ? rt - (al + be * mu) : 0.f;
+            float sd = warp_sum(d), sud = warp_sum(uD * d);
+            float dan = -p * sd + p * be * suD;
+            float dbn = mu * dan - p * sud + p * be * su2D + c4 * p * be;
+            da += c_nll * dan;
+            db += c_nll * dbn;
+        }
+        const float* h = hT + row * H;
+        float* o = dhT + row * H;
+#pragma unroll
+        for (int i = 0; i < HL; ++i) {
+            float hv = h[lane + 32 * i];
+            ga[i] += da * hv;
+            gb[i] += db * hv;
+            o[lane + 32 * i] = da * wa[i] + db * wb[i];
+        }
+        gba += da;
+        gbb += db;
+    }
+#pragma unroll
+    for (int i = 0; i < HL; ++i) { red[warp][lane + 32 * i] = ga[i]; red[warp][H + 1 + lane + 32 * i] = gb[i]; }
+    if (lane == 0) { red[warp][H] = gba; red[warp][2 * H + 1] = gbb; }
+    __syncthreads();
+    for (int c = threadIdx.x; c < 2 * H + 2; c += HEADS_THREADS) {
+        float v = 0.f;
+        for (int q = 0; q < HEADS_WARPS; ++q) v += red[q][c];
+        hpart[w * (2 * H + 2) + c] = v;
+    }
+}
+
+// K4 ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+heads_reduce_kernel(const float* __restrict__ hpart, int64_t B, int NC, float* __restrict__ out) {
+    __shared__ double red[256];
+    const int c = blockIdx.x;
+    double v = 0.0;
+    for (int64_t w = threadIdx.x; w < B; w += 256) v += (double)hpart[w * NC + c];
+    red[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[c] = (float)red[0];
+}
+
+template <int H>
+static int heads_launch(int loss_kind, float mse_weight, const float* hp, const float* hT, const float* y_stock,
+                        const float* y_market, const float* factor, const float* inv_psi, int64_t B, int S, int n,
+                        int64_t wpg, float grad_scale, float* alpha_out, float* beta_out, float* losses_out, float* dhT,
+                        float* head_grads, const HeadsWs& ws, cudaStream_t st) {
+    const bool do_nll = loss_kind != B200_LOSS_MSE;
+    const int64_t G = B / wpg;
+    float* al = alpha_out ? alpha_out : ws.alpha;
+    float* be = beta_out ? beta_out : ws.beta;
+    heads_stats_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, factor, inv_psi, S, n, wpg,
+                                                                 do_nll, al, be, ws.wpart);
+    B200_LAUNCH_CHECK("heads_stats_kernel");
+    heads_group_kernel<<<(unsigned)G, 256, 0, st>>>(ws.wpart, factor, S, n, wpg, do_nll, ws.gstat, ws.gloss);
+    B200_LAUNCH_CHECK("heads_group_kernel");
+    const double n_elems = (double)B * S * n;
+    heads_final_kernel<<<1, 256, 0, st>>>(ws.gloss, G, n_elems, loss_kind, mse_weight, losses_out);
+    B200_LAUNCH_CHECK("heads_final_kernel");
+    if (dhT) {
+        const float w_mse = loss_kind == B200_LOSS_MSE ? 1.f : loss_kind == B200_LOSS_NLL ? 0.f : mse_weight;
+        const float c_mse = (float)((double)grad_scale * w_mse * 2.0 / n_elems);
+        const float c_nll = do_nll ? (float)((double)grad_scale / (double)G) : 0.f;
+        heads_grad_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, inv_psi, al, be, ws.gstat, S, n,
+                                                                    wpg, c_mse, c_nll, dhT, ws.hpart);
+        B200_LAUNCH_CHECK("heads_grad_kernel");
+        if (head_grads) {
+            heads_reduce_kernel<<<2 * H + 2, 256, 0, st>>>(ws.hpart, B, 2 * H + 2, head_grads);
+            B200_LAUNCH_CHECK("heads_reduce_kernel");
+        }
+    }
+    return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_heads_workspace_bytes(int64_t n_windows, int n_stocks, int n_target, int hidden) {
+    if (n_windows <= 0 || n_stocks <= 0 || n_target <= 0 || hidden <= 0) return 0;
+    // sized for the worst case windows_per_group = 1 (one group per window)
+    return heads_ws_layout(n_windows, n_stocks, n_target, hidden, n_windows, nullptr, nullptr);
+}
+
+extern "C" int b200_heads_loss_fwd_bwd(int loss_kind, float mse_weight, const float* head_params, int hidden,
+                                       const float* hT, const float* y_stock, const float* y_market, const float* factor,
+                                       const float* inv_psi, int64_t n_windows, int n_stocks, int n_target,
+                                       int64_t windows_per_group, float grad_scale, float* alpha_out, float* beta_out,
+                                       float* losses_out, float* dhT, float* head_grads, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+    B200_CHECK_ARG(loss_kind >= 0 && loss_kind <= 2, "heads: unknown loss kind %d", loss_kind);
+    B200_CHECK_ARG(n_windows > 0 && n_stocks > 0, "heads: empty batch (n_windows=%lld, n_stocks=%d)", (long long)n_windows, n_stocks);
+    B200_CHECK_ARG(n_target >= 2 && n_target <= MAX_N_TARGET, "heads: target window must be 2..%d days, got %d", MAX_N_TARGET, n_target);
+    B200_CHECK_ARG(head_params && hT && y_stock && losses_out && workspace, "heads: null pointer");
+    B200_CHECK_ARG(windows_per_group > 0 && n_windows % windows_per_group == 0,
+                   "heads: n_windows=%lld not divisible by windows_per_group=%lld", (long long)n_windows, (long long)windows_per_group);
+    if (loss_kind != B200_LOSS_MSE) B200_CHECK_ARG(factor && inv_psi, "heads: NLL needs factor and inv_psi");
+    if (loss_kind != B200_LOSS_NLL) B200_CHECK_ARG(y_market, "heads: MSE needs y_market");
+    B200_CHECK_ARG(!head_grads || dhT, "heads: head_grads requires dhT");
+    HeadsWs ws;
+    size_t need = heads_ws_layout(n_windows, n_stocks, n_target, hidden, n_windows / windows_per_group, (char*)workspace, &ws);
+    B200_CHECK_ARG(workspace_bytes >= need, "heads: workspace too small (%zu < %zu)", workspace_bytes, need);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (hidden) {
+        case 32: return heads_launch<32>(loss_kind, mse_weight, head_params, hT, y_stock, y_market, factor, inv_psi, n_windows, n_stocks, n_target, windows_per_group, grad_scale, alpha_out, beta_out, losses_out, dhT, head_grads, ws, st);
+        case 64: return heads_launch<64>(loss_kind, mse_weight, head_params, hT, y_stock, y_market, factor, inv_psi, n_windows, n_stocks, n_target, windows_per_group, grad_scale, alpha_out, beta_out, losses_out, dhT, head_grads, ws, st);
+        case 128: return heads_launch<128>(loss_kind, mse_weight, head_params, hT, y_stock, y_market, factor, inv_psi, n_windows, n_stocks, n_target, windows_per_group, grad_scale, alpha_out, beta_out, losses_out, dhT, head_grads, ws, st);
+        case 256: return heads_launch<256>(loss_kind, mse_weight, head_params, hT, y_stock, y_market, factor, inv_psi, n_windows, n_stocks, n_target, windows_per_group, grad_scale, alpha_out, beta_out, losses_out, dhT, head_grads, ws, st);
+        default: set_error("heads: hidden size %d not supported (32, 64, 128, 256)", hidden); return B200_ERR_UNSUPPORTED;
+    }
+}
+
+extern "C" int b200_heads_mse_fwd_bwd(const float* head_params, int hidden, const float* hT, const float* y_stock,
+                                      const float* y_market, int64_t n_windows, int n_stocks, int n_target,
+                                      float grad_scale, float* losses_out, float* dhT, float* head_grads, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+    return b200_heads_loss_fwd_bwd(B200_LOSS_MSE, 0.f, head_params, hidden, hT, y_stock, y_market, nullptr, nullptr, n_windows,
+                                   n_stocks, n_target, n_windows > 0 ? n_windows : 1, grad_scale, nullptr, nullptr, losses_out,
+                                   dhT, head_grads, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200_heads_nll_fwd_bwd(const float* head_params, int hidden, const float* hT, const float* y_stock,
+                                      const float* factor, const float* inv_psi, int64_t n_windows, int n_stocks,
+                                      int n_target, int64_t windows_per_group, float grad_scale, float* losses_out,
+                                      float* dhT, float* head_grads, void* workspace, size_t workspace_bytes, void* stream) {
+    return b200_heads_loss_fwd_bwd(B200_LOSS_NLL, 0.f, head_params, hidden, hT, y_stock, nullptr, factor, inv_psi, n_windows,
+                                   n_stocks, n_target, windows_per_group, grad_scale, nullptr, nullptr, losses_out, dhT,
+                                   head_grads, workspace, workspace_bytes, stream);
+}

@@ -1,0 +1,150 @@
+"""Device-side step engine: owns the flat parameter/optimiser vectors, the activation stash and the
+workspaces (torch tensors are the memory owner), and drives the C-ABI kernels on torch's current
+stream.  One instance per process (= per GPU).
+
+The sequence of one optimisation step mirrors Lightning's automatic optimisation of the reference
+(train.py:169-187, src/model.py:204-209): forward -> loss -> (zero_grad) backward -> clip -> Adam.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import LOSS_KINDS, MODES, check, ptr
+
+
+class LstmEngine:
+    def __init__(self, n_features=3, hidden=64, layers=2, dropout=0.0, device="cuda:0", mode="ffma",
+                 lookback=60, target=30, n_stocks=100):
+        if not torch.cuda.is_available():
+            raise _lib.B200Error("LstmEngine needs a CUDA device; there is no CPU fallback")
+        self.lib = _lib.load()
+        self.F, self.H, self.L, self.p = int(n_features), int(hidden), int(layers), float(dropout)
+        self.T, self.n, self.S = int(lookback), int(target), int(n_stocks)
+        self.mode = MODES[mode] if isinstance(mode, str) else int(mode)
+        self.device = torch.device(device)
+        self.P = int(self.lib.b200_param_count(self.F, self.H, self.L))
+        self.head_off = int(self.lib.b200_param_offset(self.F, self.H, self.L, self.L))
+        self.P_pad = (self.P + 3) // 4 * 4
+        z = lambda: torch.zeros(self.P_pad, dtype=torch.float32, device=self.device)
+        self.params, self.grads, self.exp_avg, self.exp_avg_sq = z(), z(), z(), z()
+        self.losses = torch.zeros(4, dtype=torch.float32, device=self.device)
+        self.sqnorm = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.sq_ws = torch.empty(int(self.lib.b200_sqnorm_workspace_bytes(self.P_pad)), dtype=torch.uint8, device=self.device)
+        self.opt_step = 0
+        self._cap = 0          # capacity in windows
+        self.launches = 0      # kernel launches issued (bench.py's gpu_launches claim)
+
+    # ------------------------------------------------------------------ buffers
+    def ensure_capacity(self, n_windows: int):
+        if n_windows <= self._cap:
+            return
+        N = n_windows * self.S
+        dev = self.device
+        self.stash_h = torch.empty(self.L * self.T * N * self.H, dtype=torch.float32, device=dev)
+        self.stash_c = torch.empty_like(self.stash_h)
+        self.dhT = torch.empty(N * self.H, dtype=torch.float32, device=dev)
+        self.alpha = torch.empty(N, dtype=torch.float32, device=dev)
+        self.beta = torch.empty(N, dtype=torch.float32, device=dev)
+        ws = int(self.lib.b200_lstm_workspace_bytes(self.mode, N, self.T, self.F, self.H, self.L))
+        self.lstm_ws = torch.empty(max(ws, 256), dtype=torch.uint8, device=dev)
+        hws = int(self.lib.b200_heads_workspace_bytes(n_windows, self.S, self.n, self.H))
+        self.heads_ws = torch.empty(max(hws, 256), dtype=torch.uint8, device=dev)
+        self._cap = n_windows
+
+    def stash_bytes(self, n_windows: int) -> int:
+        return 2 * self.L * self.T * n_windows * self.S * self.H * 4
+
+    @property
+    def stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def load_params(self, flat: torch.Tensor):
+        assert flat.numel() == self.P, (flat.numel(), self.P)
+        self.params[: self.P].copy_(flat.to(self.device, torch.float32))
+
+    def reset_optimizer(self):
+        self.exp_avg.zero_(); self.exp_avg_sq.zero_(); self.grads.zero_(); self.opt_step = 0
+
+    # ------------------------------------------------------------------ kernels
+    def forward(self, batch, training=False, dropout_seed=0):
+        """LSTM forward of every layer; fills the stash.  Replaces self.lstm(...) (src/model.py:104)."""
+        self.ensure_capacity(batch.n_windows)
+        N = batch.n_windows * self.S
+        check(self.lib.b200_lstm_fwd(self.mode, ptr(self.params), self.F, self.H, self.L, ptr(batch.x), N, self.T,
+                                     ptr(self.stash_h), ptr(self.stash_c), self.p, int(dropout_seed), int(bool(training)),
+                                     ptr(self.lstm_ws), self.lstm_ws.numel(), self.stream), "b200_lstm_fwd")
+        self.launches += self.L
+        self._N = N
+
+    def final_hidden(self, n_windows):
+        N = n_windows * self.S
+        off = ((self.L - 1) * self.T + (self.T - 1)) * N * self.H
+        return self.stash_h[off: off + N * self.H]
+
+    def heads(self, batch, kind="mse", mse_weight=100.0, windows_per_group=None, grad_scale=1.0, want_grad=True):
+        """Heads + objective (+ gradients into dhT and the head slice of grads).  losses -> self.losses."""
+        B = batch.n_windows
+        wpg = B if windows_per_group is None else int(windows_per_group)
+        k = LOSS_KINDS[kind] if isinstance(kind, str) else int(kind)
+        hT = self.final_hidden(B)
+        head_params = self.params[self.head_off:]
+        head_grads = self.grads[self.head_off:]
+        check(self.lib.b200_heads_loss_fwd_bwd(
+            k, float(mse_weight), ptr(head_params), self.H, ptr(hT), ptr(batch.y_stock), ptr(batch.y_market),
+            ptr(batch.factor), ptr(batch.inv_psi), B, self.S, self.n, wpg, float(grad_scale),
+            ptr(self.alpha), ptr(self.beta), ptr(self.losses), ptr(self.dhT) if want_grad else None,
+            ptr(head_grads) if want_grad else None, ptr(self.heads_ws), self.heads_ws.numel(), self.stream),
+            "b200_heads_loss_fwd_bwd")
+        self.launches += 5 if want_grad else 3
+        return self.losses
+
+    def backward(self, batch, training=True, dropout_seed=0, on_layer_done=None):
+        """BPTT, top layer first; on_layer_done(layer) is called after each layer's launches are queued
+        (the data-parallel trainer hooks its bucket all-reduce here)."""
+        N = batch.n_windows * self.S
+        for layer in range(self.L - 1, -1, -1):
+            check(self.lib.b200_lstm_bwd_layer(self.mode, layer, ptr(self.params), self.F, self.H, self.L, ptr(batch.x), N,
+                                               self.T, ptr(self.stash_h), ptr(self.stash_c), ptr(self.dhT), ptr(self.grads),
+                                               self.p, int(dropout_seed), int(bool(training)), ptr(self.lstm_ws),
+                                               self.lstm_ws.numel(), self.stream), "b200_lstm_bwd_layer")
+            self.launches += 3
+            if on_layer_done is not None:
+                on_layer_done(layer)
+
+    def layer_slice(self, layer):
+        """(offset, length) in floats of a layer's gradient slice; layer == L gives the heads."""
+        lo = int(self.lib.b200_param_offset(self.F, self.H, self.L, layer))
+        hi = self.P if layer == self.L else int(self.lib.b200_param_offset(self.F, self.H, self.L, layer + 1))
+        return lo, hi - lo
+
+    def optimizer_step(self, lr, clip_val=0.0, weight_decay=1e-5, betas=(0.9, 0.999), eps=1e-8):
+        """Global-norm clip + Adam on the flat vector (train.py:171, src/model.py:150-154)."""
+        self.opt_step += 1
+        use_clip = clip_val is not None and clip_val > 0
+        if use_clip:
+            check(self.lib.b200_grad_sqnorm(ptr(self.grads), self.P_pad, ptr(self.sqnorm), ptr(self.sq_ws),
+                                            self.sq_ws.numel(), self.stream), "b200_grad_sqnorm")
+            self.launches += 2
+        check(self.lib.b200_adam_step(ptr(self.params), ptr(self.grads), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                                      self.P_pad, float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                      float(weight_decay), self.opt_step, float(clip_val) if use_clip else 0.0,
+                                      ptr(self.sqnorm) if use_clip else None, 1, self.stream), "b200_adam_step")
+        self.launches += 1
+
+    def train_step(self, batch, kind, lr, clip_val, mse_weight=100.0, dropout_seed=0, grad_scale=1.0,
+                   on_layer_done=None, before_optimizer=None):
+        """One optimisation step; returns the device tensor [mse, nll, total, mae] (no host sync)."""
+        self.forward(batch, training=True, dropout_seed=dropout_seed)
+        losses = self.heads(batch, kind, mse_weight, None, grad_scale, want_grad=True)
+        self.backward(batch, True, dropout_seed, on_layer_done)
+        if before_optimizer is not None:
+            before_optimizer()
+        self.optimizer_step(lr, clip_val)
+        return losses
+
+    def eval_windows(self, batch, kind="combined", mse_weight=100.0):
+        """Validation / test semantics: every window is its own batch (src/data.py:241-244); returns the
+        device tensor [mean mse, mean per-window nll, mean total, mae]."""
+        self.forward(batch, training=False)
+        return self.heads(batch, kind, mse_weight, windows_per_group=1, want_grad=False)

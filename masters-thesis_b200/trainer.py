@@ -1,0 +1,244 @@
+"""B200Trainer: the object `train.py` builds in place of lightning.Trainer when `trainer=b200`.
+
+It restates Lightning's fit/test loops around the reference modules (train.py:169-198): epochs of
+shuffled training batches -> one fused device step each (forward, objective, BPTT, global-norm clip,
+Adam), validation with batch size 1 semantics every `check_val_every_n_epoch` epochs, ReduceLROnPlateau
+on loss/total/val (src/model.py:156-172), best/last checkpoints (train.py:151-161) and the test loop
+(src/model.py:119-147).  Under torchrun (WORLD_SIZE > 1) it is data parallel: each rank takes its share
+of every global batch and gradients are summed (pre-scaled by 1/W) with bucketed all-reduces issued
+per layer on a communication stream while the lower layers' backward kernels are still running.
+"""
+from __future__ import annotations
+
+import math
+import os
+import time
+from pathlib import Path
+
+import torch
+
+from .grad_sync import GradBucketer
+
+
+class PlateauSchedule:
+    """torch.optim.lr_scheduler.ReduceLROnPlateau(mode='min', factor, patience) with torch's defaults
+    (relative threshold 1e-4, cooldown 0, min_lr 0, eps 1e-8) -- src/model.py:156-161."""
+
+    def __init__(self, lr, factor=0.5, patience=2, threshold=1e-4, eps=1e-8):
+        self.lr, self.factor, self.patience, self.threshold, self.eps = lr, factor, patience, threshold, eps
+        self.best, self.num_bad = math.inf, 0
+
+    def step(self, metric):
+        if metric < self.best * (1.0 - self.threshold):
+            self.best, self.num_bad = metric, 0
+        else:
+            self.num_bad += 1
+        if self.num_bad > self.patience:
+            new_lr = self.lr * self.factor
+            if self.lr - new_lr > self.eps:
+                self.lr = new_lr
+            self.num_bad = 0
+        return self.lr
+
+
+class _CheckpointState:
+    """The two attributes of ModelCheckpoint that train.py reads (train.py:193-194, 210, 220)."""
+
+    def __init__(self, dirpath=None):
+        self.dirpath = dirpath
+        self.best_model_path = ""
+        self.best_model_score = None
+        self.last_model_path = ""
+
+
+def _precision_to_mode(precision, engine):
+    if engine and engine != "auto":
+        return engine
+    return {"32-true": "tc_precise", "32": "tc_precise", "bf16-mixed": "tc_fast", "bf16": "tc_fast"}.get(str(precision), "tc_precise")
+
+
+class B200Trainer:
+    def __init__(self, max_epochs=4, gradient_clip_val=None, precision="32-true", enable_progress_bar=False,
+                 enable_model_summary=True, logger=None, callbacks=None, check_val_every_n_epoch=1, *,
+                 devices=1, max_steps=-1, seed=1234, bucket_mb=0.25, engine="auto", eval_batch_windows=512,
+                 checkpoint_dir=None, log_dir=None, limit_val_windows=None, limit_test_windows=None, verbose=True):
+        self.max_epochs, self.clip = int(max_epochs), gradient_clip_val
+        self.precision, self.check_val_every_n_epoch = precision, int(check_val_every_n_epoch)
+        self.max_steps, self.seed, self.bucket_mb = int(max_steps), int(seed), float(bucket_mb)
+        self.mode = _precision_to_mode(precision, engine)
+        self.eval_batch_windows = int(eval_batch_windows)
+        self.limit_val_windows, self.limit_test_windows = limit_val_windows, limit_test_windows
+        self.verbose = verbose and int(os.environ.get("RANK", "0")) == 0
+        self.checkpoint_callback = _CheckpointState(checkpoint_dir)
+        self.log_dir = log_dir
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.device = torch.device(f"cuda:{self.local_rank}")
+        self.global_step, self.current_epoch = 0, 0
+        self.history = []            # one dict of logged metrics per epoch
+        self.step_losses = []        # device tensors [mse, nll, total, mae] per step when record_steps
+        self.record_steps = False
+        self._tb = None
+        self._sync = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _init_distributed(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                dist.init_process_group("nccl", device_id=self.device)
+            self._sync = GradBucketer(self.world, self.bucket_mb, device=self.device)
+
+    def _writer(self):
+        if self._tb is None and self.log_dir and self.rank == 0:
+            try:
+                from torch.utils.tensorboard import SummaryWriter
+                self._tb = SummaryWriter(self.log_dir)
+            except Exception:            # tensorboard missing: scalars stay in self.history
+                self._tb = False
+        return self._tb or None
+
+    def _log(self, metrics, epoch):
+        self.history.append(dict(metrics, epoch=epoch))
+        w = self._writer()
+        if w:
+            for k, v in metrics.items():
+                w.add_scalar(k, v, epoch)
+
+    def _attach(self, model, dm):
+        torch.cuda.set_device(self.device)
+        if model.engine is None:
+            hp = dm.hparams
+            model.attach(self.device, self.mode, hp["lookback_window"], hp["target_window"], dm.n_stocks)
+        return model.engine
+
+    def dropout_seed(self, step):
+        return (self.seed * 1000003 + step) & 0xFFFFFFFFFFFFFFFF
+
+    # ------------------------------------------------------------------ one step
+    def training_step(self, model, batch, lr):
+        e = model.engine
+        sync = self._sync
+        on_layer = None
+        if sync is not None:
+            sync.begin(e.grads, e.P)
+            lo, ln = e.layer_slice(e.L)
+
+            def on_layer(layer, _e=e, _s=sync):
+                _s.layer_ready(*_e.layer_slice(layer), last=(layer == 0))
+        e.forward(batch, training=True, dropout_seed=self.dropout_seed(self.global_step))
+        losses = e.heads(batch, model.loss_kind, model.hparams.get("mse_weight", 100.0), None,
+                         1.0 / self.world, want_grad=True)
+        if sync is not None:
+            sync.layer_ready(lo, ln, last=False)          # heads slice opens the first bucket
+        e.backward(batch, True, self.dropout_seed(self.global_step), on_layer)
+        if sync is not None:
+            sync.wait()
+        e.optimizer_step(lr, self.clip if self.clip else 0.0, model.hparams["weight_decay"])
+        self.global_step += 1
+        return losses
+
+    # ------------------------------------------------------------------ loops
+    @torch.no_grad()
+    def evaluate(self, model, dm, split="val"):
+        """Batch-1 semantics over the split, processed `eval_batch_windows` windows per launch."""
+        e = self._attach(model, dm)
+        lo, hi = (dm.train_end, dm.val_end) if split == "val" else (dm.val_end, dm.n_windows)
+        limit = self.limit_val_windows if split == "val" else self.limit_test_windows
+        if limit:
+            hi = min(hi, lo + int(limit))
+        acc = torch.zeros(4, dtype=torch.float64, device=self.device)
+        done = 0
+        kind = model.loss_kind if split == "val" else "combined"
+        while done < hi - lo:
+            nb = min(self.eval_batch_windows, hi - lo - done)
+            batch = dm.source.generate(first_window=lo + done, n_windows=nb)
+            acc += e.eval_windows(batch, kind, model.hparams.get("mse_weight", 100.0)).double() * nb
+            done += nb
+        mse, nll, total, mae = (acc / max(done, 1)).tolist()
+        return {"mse": mse, "nll": nll, "total": total, "mae": mae, "windows": done}
+
+    def fit(self, model, datamodule=None):
+        dm = datamodule
+        dm.rank, dm.world_size, dm.device = self.rank, self.world, self.device
+        dm.prepare_data()
+        dm.setup("fit")
+        e = self._attach(model, dm)
+        self._init_distributed()
+        sched = PlateauSchedule(model.hparams["learning_rate"])
+        ck = self.checkpoint_callback
+        kind = model.loss_kind
+        stop = False
+        for epoch in range(self.max_epochs):
+            self.current_epoch = epoch
+            t0 = time.time()
+            loader = dm.train_dataloader()
+            acc = torch.zeros(4, dtype=torch.float64, device=self.device)
+            nb = 0
+            for batch in loader:
+                losses = self.training_step(model, batch, sched.lr)
+                acc += losses.double()
+                nb += 1
+                if self.record_steps:
+                    self.step_losses.append(losses.clone())
+                if 0 < self.max_steps <= self.global_step:
+                    stop = True
+                    break
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.all_reduce(acc)
+                acc /= self.world
+            mse, nll, total, _ = (acc / max(nb, 1)).tolist()
+            metrics = {"loss/total/train": total, "lr-Adam": sched.lr}
+            if kind in ("mse", "combined"):
+                metrics["loss/mse/train"] = mse
+            if kind in ("nll", "combined"):
+                metrics["loss/nll/train"] = nll
+            if (epoch + 1) % self.check_val_every_n_epoch == 0 or stop or epoch == self.max_epochs - 1:
+                v = self.evaluate(model, dm, "val")
+                metrics["loss/total/val"] = v["total"]
+                if kind in ("mse", "combined"):
+                    metrics["loss/mse/val"] = v["mse"]
+                if kind in ("nll", "combined"):
+                    metrics["loss/nll/val"] = v["nll"]
+                sched.step(v["total"])
+                if ck.best_model_score is None or v["total"] < float(ck.best_model_score):
+                    ck.best_model_score = torch.tensor(v["total"])
+                    ck.best_model_path = self._save(model, f"best_epoch={epoch:02d}_val={v['total']:.4f}.ckpt", epoch)
+                ck.last_model_path = self._save(model, "last.ckpt", epoch)
+            metrics["epoch_seconds"] = time.time() - t0
+            self._log(metrics, epoch)
+            if self.verbose:
+                print(f"[b200] epoch {epoch}: " + ", ".join(f"{k}={v:.6g}" for k, v in metrics.items()), flush=True)
+            if stop:
+                break
+        if ck.best_model_score is None:
+            ck.best_model_score = torch.tensor(float("nan"))
+        return self
+
+    def test(self, model, datamodule=None):
+        dm = datamodule
+        dm.prepare_data()
+        dm.setup("test")
+        self._attach(model, dm)
+        model.on_test_start()
+        t = self.evaluate(model, dm, "test")
+        model.test_results['test_loss']['mae'] = t["mae"]       # src/model.py:142-147
+        model.test_results['test_loss']['nll'] = t["nll"]
+        if self.verbose:
+            print(f"[b200] test: mae={t['mae']:.6f} nll={t['nll']:.6f} over {t['windows']} windows", flush=True)
+        return [{"test/mae": t["mae"], "test/nll": t["nll"]}]
+
+    def _save(self, model, filename, epoch):
+        """Lightning-layout checkpoint (state_dict + hyper_parameters), consumable by load_from_checkpoint
+        (test.py:178).  Rank 0 only."""
+        ck = self.checkpoint_callback
+        if not ck.dirpath or self.rank != 0:
+            return ""
+        d = Path(ck.dirpath)
+        d.mkdir(parents=True, exist_ok=True)
+        path = d / filename
+        torch.save({"state_dict": model.state_dict(), "hyper_parameters": dict(model.hparams), "epoch": epoch,
+                    "global_step": self.global_step, "pytorch-lightning_version": "2.6.0"}, path)
+        return str(path)

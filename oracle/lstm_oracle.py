@@ -147,7 +147,7 @@ class OracleLstm(torch.nn.Module):
 class ExplicitMaskLstm(torch.nn.Module):
     """Same network as OracleLstm, built from single-layer nn.LSTMs so that the
     inter-layer dropout masks can be injected (shape (L-1, N, T, H), already
-    scaled by 1/(1-p)).  Used for the shared-Philox-mask parity gate and to read
+    scaled by 1/(1-p); indexed masks[l] = mask applied to the OUTPUT of layer l).  Used for the shared-Philox-mask parity gate and to read
     every layer's hidden sequence."""
 
     def __init__(self, src: OracleLstm):
@@ -157,7 +157,8 @@ class ExplicitMaskLstm(torch.nn.Module):
         for l in range(L):
             cell = torch.nn.LSTM(src.lstm.input_size if l == 0 else H, H, 1, batch_first=True)
             for name in ("weight_ih", "weight_hh", "bias_ih", "bias_hh"):
-                getattr(cell, f"{name}_l0").data = getattr(src.lstm, f"{name}_l{l}").data
+                # share the Parameter objects, so gradients land on the source module
+                setattr(cell, f"{name}_l0", getattr(src.lstm, f"{name}_l{l}"))
             self.layers.append(cell)
         self.alpha_head, self.beta_head = src.alpha_head, src.beta_head
 
@@ -446,3 +447,21 @@ def generate_windows(window_idx, n_stocks=100, lookback=60, target=30, stride=90
 class StepRecord:
     losses: dict
     grad_norm: float | None
+
+
+def dropout_mask(seed, layer, n_seq, T, hidden, p):
+    """Keep-mask of the input of layer `layer` (>=1), shape (T, N, H), values 0 or 1/(1-p), exactly as the
+    kernels regenerate it: Philox counter (row_lo, row_hi, t | layer<<16, unit//8), unit j of the block keeps
+    iff its 16-bit lane >= round(p*65536).  Integer work: compared bit-exactly with b200_dropout_mask."""
+    rows = np.arange(n_seq, dtype=np.uint64)[None, :, None]
+    ts = np.arange(T, dtype=np.uint32)[:, None, None]
+    ub = np.arange(hidden // 8, dtype=np.uint32)[None, None, :]
+    k0, k1 = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+    x = philox4x32_10((rows & np.uint64(0xFFFFFFFF)).astype(np.uint32), (rows >> np.uint64(32)).astype(np.uint32),
+                      ts | np.uint32(layer << 16), ub, k0, k1)
+    lanes = []
+    for w in x:
+        lanes += [w & np.uint32(0xFFFF), w >> np.uint32(16)]
+    u16 = np.stack(lanes, axis=-1).reshape(T, n_seq, hidden)
+    thr = min(65535, int(np.float32(p) * np.float32(65536.0) + np.float32(0.5)))
+    return np.where(u16 >= thr, np.float32(1.0 / (1.0 - p)), np.float32(0.0)).astype(np.float32)

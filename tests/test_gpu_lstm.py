@@ -1,0 +1,203 @@
+"""-m gpu: the LSTM engines and the full optimisation step, through the C-ABI, against
+(a) the golden vectors produced by the reference's own modules and (b) the CPU oracle."""
+import numpy as np
+import pytest
+import torch
+
+import lstm_oracle as O
+import masters_thesis_b200 as B
+from _gpu_util import DEV, golden_batches, make_engine, oracle_model, ref_batch, rel_err
+
+pytestmark = pytest.mark.gpu
+torch.set_float32_matmul_precision("highest")
+
+# engines under test; tcgen05 modes are appended once built (see ENGINES_TC)
+ENGINES = ["ffma"]
+if B._lib.load().b200_mode_available(B.MODES["tc_precise"]):
+    ENGINES += ["tc_precise"]
+
+# north_star tolerances: per-step loss 1e-4 relative, parameter gradients 1e-3 relative (of the largest entry)
+LOSS_RTOL, GRAD_RTOL = 1e-4, 1e-3
+
+
+@pytest.fixture(scope="module")
+def data(golden_dir):
+    return golden_batches(golden_dir)
+
+
+def _stash(e, n_windows):
+    N = n_windows * e.S
+    return e.stash_h[: e.L * e.T * N * e.H].reshape(e.L, e.T, N, e.H), e.stash_c[: e.L * e.T * N * e.H].reshape(e.L, e.T, N, e.H)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("layers,B_", [(2, 1), (2, 3), (4, 2)])
+def test_forward_hidden_states_vs_oracle(engine, layers, B_, data):
+    torch.manual_seed(5 + layers)
+    m = O.OracleLstm(3, 64, layers, 0.0)
+    flat = O.flat_params(m)
+    e = make_engine(flat, layers, 0.0, engine)
+    batch = B.DeviceBatch.from_reference(ref_batch(data, 0, B_), DEV)
+    e.forward(batch, training=False)
+    e.heads(batch, "mse", want_grad=False)
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        a, b, seqs = O.ExplicitMaskLstm(m)(data["X"][:B_].flatten(0, 1), return_all=True)
+    h, _ = _stash(e, B_)
+    for l in range(layers):
+        want = seqs[l].permute(1, 0, 2).numpy()          # (T, N, H)
+        np.testing.assert_allclose(h[l].cpu().numpy(), want, rtol=0, atol=2e-5 if engine != "ffma" else 2e-6)
+    N = B_ * 100
+    np.testing.assert_allclose(e.alpha[:N].cpu().numpy(), a[:, 0].numpy(), atol=1e-5)
+    np.testing.assert_allclose(e.beta[:N].cpu().numpy(), b[:, 0].numpy(), atol=1e-5)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("kind", ["mse", "nll", "combined"])
+def test_training_steps_vs_reference_golden(engine, kind, data, golden_dir):
+    """Three optimisation steps from the reference's initial state on the reference's batches:
+    losses, step-0 gradients and final parameters against what the reference's own modules produced."""
+    g = np.load(golden_dir / f"golden_{kind}.npz")
+    e = make_engine(torch.from_numpy(g["init"]), 2, 0.0, engine)
+    order = [(0, 2), (2, 4), (0, 2)]
+    clip = float(g["clip"])
+    for s, (lo, hi) in enumerate(order):
+        batch = B.DeviceBatch.from_reference(ref_batch(data, lo, hi), DEV)
+        e.forward(batch, training=True)
+        losses = e.heads(batch, kind, 100.0, None, 1.0, True).clone()
+        e.backward(batch, True)
+        if s == 0:
+            got = e.grads[: e.P].cpu().numpy()
+            assert rel_err(got, g["grads0"]) < GRAD_RTOL
+            # and per parameter tensor, so that small tensors are not hidden by large ones
+            off = 0
+            for name, n in zip(g["names"], [int(np.prod(s_)) for s_ in B.model._param_shapes(3, 64, 2)]):
+                assert rel_err(got[off:off + n], g["grads0"][off:off + n]) < GRAD_RTOL, name
+                off += n
+        e.optimizer_step(1e-4, clip)
+        assert float(losses[2]) == pytest.approx(float(g["losses"][s]), rel=LOSS_RTOL)
+        if s == 0:
+            assert float(torch.sqrt(e.sqnorm)) == pytest.approx(float(g["gnorm0"]), rel=GRAD_RTOL)
+    np.testing.assert_allclose(e.params[: e.P].cpu().numpy(), g["final"], rtol=0, atol=2e-6)
+    # validation / test semantics (batch of one window each)
+    vb = B.DeviceBatch.from_reference(ref_batch(data, 4, 6), DEV)
+    for w in (0, 1):
+        one = B.DeviceBatch.from_reference(ref_batch(data, 4 + w, 5 + w), DEV)
+        v = e.eval_windows(one, kind)
+        assert float(v[2]) == pytest.approx(float(g["val_total"][w]), rel=LOSS_RTOL)
+    t = e.eval_windows(vb, "combined")
+    assert float(t[3]) == pytest.approx(float(g["test_mae"]), rel=LOSS_RTOL)
+    assert float(t[1]) == pytest.approx(float(g["test_nll"]), rel=LOSS_RTOL)
+    np.testing.assert_allclose(e.alpha[:100].cpu().numpy(), g["alpha_w4"][:, 0], atol=2e-5)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("layers,p", [(2, 0.2), (4, 0.3)])
+def test_dropout_step_vs_oracle_with_shared_masks(engine, layers, p, data):
+    """Gate 2 of SURVEY.md: the kernels' Philox masks injected into the oracle's explicit-mask LSTM."""
+    torch.manual_seed(11)
+    m = O.OracleLstm(3, 64, layers, 0.0)
+    e = make_engine(O.flat_params(m), layers, p, engine)
+    B_, seed = 2, 0xABCDEF0123
+    N = B_ * 100
+    batch = B.DeviceBatch.from_reference(ref_batch(data, 1, 1 + B_), DEV)
+    e.forward(batch, training=True, dropout_seed=seed)
+    losses = e.heads(batch, "combined", 100.0, None, 1.0, True).clone()
+    e.backward(batch, True, dropout_seed=seed)
+    torch.cuda.synchronize()
+    masks = [torch.from_numpy(O.dropout_mask(seed, l + 1, N, 60, 64, p)).permute(1, 0, 2) for l in range(layers - 1)]
+    em = O.ExplicitMaskLstm(m)
+    ls = O.batch_losses(m, ref_batch(data, 1, 1 + B_), "combined", 100.0, forward=lambda x: em(x, masks))
+    m.zero_grad()
+    ls["total"].backward()
+    assert float(losses[2]) == pytest.approx(float(ls["total"]), rel=LOSS_RTOL)
+    assert rel_err(e.grads[: e.P].cpu().numpy(), O.flat_grads(m).numpy()) < GRAD_RTOL
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_ragged_rows_and_determinism(engine, data):
+    """N not a multiple of the CTA tile (S = 7 stocks), and bit-identical gradients run to run."""
+    torch.manual_seed(2)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    e = B.LstmEngine(3, 64, 2, 0.0, DEV, engine, n_stocks=7)
+    e.load_params(O.flat_params(m))
+    X, y, f, ip = ref_batch(data, 0, 3)
+    sub = [X[:, :7].contiguous(), y[:, :7].contiguous(), f, ip[:, :7].contiguous()]
+    batch = B.DeviceBatch.from_reference(sub, DEV)
+    runs = []
+    for _ in range(2):
+        e.forward(batch, training=True)
+        losses = e.heads(batch, "mse", 100.0, None, 1.0, True).clone()
+        e.backward(batch, True)
+        runs.append(e.grads[: e.P].clone())
+    assert torch.equal(runs[0], runs[1])
+    ls = O.batch_losses(m, sub, "mse")
+    m.zero_grad()
+    ls["total"].backward()
+    assert float(losses[2]) == pytest.approx(float(ls["total"]), rel=LOSS_RTOL)
+    assert rel_err(runs[0].cpu().numpy(), O.flat_grads(m).numpy()) < GRAD_RTOL
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_chunked_backward_equals_unchunked(engine, data):
+    """A workspace too small for the whole batch forces several da chunks; gradients must not change
+    beyond fp32 summation order."""
+    torch.manual_seed(4)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    e = make_engine(O.flat_params(m), 2, 0.0, engine)
+    batch = B.DeviceBatch.from_reference(ref_batch(data, 0, 4), DEV)
+    e.forward(batch, training=True)
+    e.heads(batch, "mse", 100.0, None, 1.0, True)
+    e.backward(batch, True)
+    full = e.grads[: e.P].clone()
+    if engine == "ffma":
+        fixed = e.lstm_ws.numel() - 60 * 400 * 256 * 4          # everything except the da buffer
+        e.lstm_ws = torch.empty(fixed + 60 * 128 * 256 * 4 + 4096, dtype=torch.uint8, device=DEV)   # room for 128 sequences
+        e.backward(batch, True)
+        assert rel_err(e.grads[: e.P].cpu().numpy(), full.cpu().numpy()) < 1e-5
+
+
+def test_trainer_fit_matches_oracle_loop():
+    """End to end through B200Trainer (the trainer=b200 object): 6 steps of batch 2 on device-generated
+    windows, then validation and test -- against the oracle loop fed the SAME windows."""
+    torch.manual_seed(1234)
+    model = B.FinancialLstmCombined(3, 64, 2, 0.0, 1e-4, mse_weight=100)
+    init = model.flat_parameters().clone()
+    dm = B.FinancialLstmDataModule(lookback_window=60, target_window=30, stride=90, batch_size=2, seed=77,
+                                   n_samples=90 * 40, device=DEV)
+    tr = B.B200Trainer(max_epochs=1, gradient_clip_val=5.0, max_steps=6, engine="ffma", verbose=False)
+    tr.record_steps = True
+    tr.fit(model, dm)
+    tr.test(model, dm)
+    # oracle on the same windows: replay the loader's shuffle
+    gen = torch.Generator().manual_seed(77)
+    order = torch.randperm(dm.train_end, generator=gen)
+    om = oracle_model(init, 2, 0.0)
+    opt = O.make_optimizer(om)
+    for s in range(6):
+        idx = order[2 * s: 2 * s + 2].tolist()
+        ls, _ = O.train_step(om, opt, O.generate_windows(idx, seed=77), "combined", 5.0)
+        assert float(tr.step_losses[s][2]) == pytest.approx(ls["total"], rel=5e-4)   # generator ulp differences included
+    vw = list(range(dm.train_end, dm.val_end))
+    v = O.eval_windows(om, *O.generate_windows(vw, seed=77), "combined")
+    assert float(tr.checkpoint_callback.best_model_score) == pytest.approx(v["total"], rel=5e-4)
+    t = O.test_windows(om, *O.generate_windows(list(range(dm.val_end, dm.n_windows)), seed=77))
+    assert model.test_results["test_loss"]["mae"] == pytest.approx(t["mae"], rel=5e-4)
+    assert model.test_results["test_loss"]["nll"] == pytest.approx(t["nll"], rel=5e-4)
+    np.testing.assert_allclose(model.flat_parameters().numpy(), O.flat_params(om).numpy(), atol=5e-6)
+
+
+def test_model_forward_api():
+    torch.manual_seed(9)
+    model = B.FinancialLstmMse(3, 64, 2, 0.2, 1e-4)
+    om = oracle_model(model.flat_parameters(), 2, 0.0)
+    model.attach(DEV, "ffma")
+    x = torch.randn(37, 60, 3)
+    a, b = model(x)
+    with torch.no_grad():
+        ao, bo = om(x)
+    assert a.shape == (37, 1)
+    np.testing.assert_allclose(a.cpu().numpy(), ao.numpy(), atol=1e-5)
+    np.testing.assert_allclose(b.cpu().numpy(), bo.numpy(), atol=1e-5)
+    sd = model.state_dict()
+    assert list(sd.keys()) == list(om.state_dict().keys())

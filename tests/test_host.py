@@ -1,0 +1,157 @@
+"""CPU tests (no GPU): library loads and exports every symbol of include/b200_lstm.h, config
+composition, model mirror initialisation, datamodule split arithmetic, gradient bucketing under gloo."""
+import os
+import re
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+import masters_thesis_b200 as B
+
+ROOT = Path(__file__).resolve().parent.parent
+CONFIGS = ROOT / "configs"
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = (ROOT / "include" / "b200_lstm.h").read_text()
+    declared = set(re.findall(r"B200_API [\w\s\*]+?\b(b200_\w+)\(", hdr))
+    assert len(declared) >= 19
+    lib = B._lib.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert declared == set(B._lib.PROTOTYPES), declared ^ set(B._lib.PROTOTYPES)
+    # host-only entry points work without a GPU
+    assert lib.b200_version() >= 100
+    assert lib.b200_param_count(3, 64, 2) == 51074
+    assert lib.b200_param_count(3, 64, 4) == 117634
+    assert lib.b200_param_count(3, 64, 8) == 250754
+    assert lib.b200_param_offset(3, 64, 2, 2) == 51074 - 130
+
+
+def test_missing_library_fails_loudly(tmp_path):
+    with pytest.raises(B.B200Error, match="no CPU fallback"):
+        B._lib.load(tmp_path / "nope.so")
+
+
+def test_engine_refuses_to_run_without_cuda():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(B.B200Error):
+        B.LstmEngine(3, 64, 2)
+
+
+def test_config_defaults_and_overrides():
+    cfg = B.compose_config(CONFIGS)
+    assert cfg.datamodule.name == "synthetic" and cfg.model.name == "small" and cfg.loss.name == "mse"
+    assert cfg.trainer.name == "fast" and cfg.trainer.max_epochs == 4 and cfg.trainer.gradient_clip_val == 5.0
+    assert cfg.model.input_size == 3 and cfg.model.hidden_size == 64 and cfg.model.num_layers == 2
+    assert cfg.logger.name == "FinancialLstm/synthetic"
+    assert cfg.logger.version == "mse_small_lr0.0001_fast"
+    assert cfg.checkpoint is None
+    cfg = B.compose_config(CONFIGS, overrides=["loss=combined", "model=large", "trainer=b200", "loss.mse_weight=0.7",
+                                                "datamodule.interaction_only=false", "datamodule.batch_size=4096"])
+    assert cfg.loss.module_class == "FinancialLstmCombined" and cfg.loss.mse_weight == 0.7
+    assert cfg.model.num_layers == 8 and cfg.model.input_size == 5
+    assert cfg.trainer.name == "b200" and cfg.datamodule.batch_size == 4096
+    assert cfg.logger.version == "combined_large_lr0.0001_b200"
+    with pytest.raises(ValueError, match="Could not find 'trainer/slower'"):
+        B.compose_config(CONFIGS, overrides=["trainer=slower"])
+
+
+def test_multirun_grid():
+    from masters_thesis_b200.config import expand_multirun, split_cli
+    multi, ov = split_cli(["-m", "datamodule=synthetic", "model=small,medium,large", "loss=mse,nll,combined", "trainer=fast,slow"])
+    assert multi
+    grid = expand_multirun(ov)
+    assert len(grid) == 18 and grid[0] == ["datamodule=synthetic", "model=small", "loss=mse", "trainer=fast"]
+
+
+def test_model_mirror_initialises_like_torch_modules():
+    torch.manual_seed(1234)
+    m = B.FinancialLstmNll(3, 64, 2, 0.2, 1e-4)
+    torch.manual_seed(1234)
+    lstm = torch.nn.LSTM(3, 64, 2, dropout=0.2, batch_first=True)
+    a, b = torch.nn.Linear(64, 1), torch.nn.Linear(64, 1)
+    want = torch.cat([p.detach().reshape(-1) for p in list(lstm.parameters()) + list(a.parameters()) + list(b.parameters())])
+    assert torch.equal(m.flat_parameters(), want)
+    sd = m.state_dict()
+    assert list(sd)[:4] == ["lstm.weight_ih_l0", "lstm.weight_hh_l0", "lstm.bias_ih_l0", "lstm.bias_hh_l0"]
+    assert sd["alpha_head.weight"].shape == (1, 64) and sd["beta_head.bias"].shape == (1,)
+    m2 = B.FinancialLstmNll(3, 64, 2, 0.2, 1e-4)
+    m2.load_state_dict(sd)
+    assert torch.equal(m2.flat_parameters(), want)
+    assert B.get_model_class("FinancialLstmCombined")(mse_weight=3.0).hparams["mse_weight"] == 3.0
+    with pytest.raises(ValueError):
+        B.get_model_class("Nope")
+
+
+def test_initial_state_matches_reference_golden(golden_dir):
+    g = np.load(golden_dir / "golden_mse.npz")
+    torch.manual_seed(int(g["meta"][1]))
+    m = B.FinancialLstmMse(3, 64, 2, 0.0, 1e-4)
+    assert np.array_equal(m.flat_parameters().numpy(), g["init"])
+    assert m.names == list(g["names"])
+
+
+def test_datamodule_split_matches_reference_arithmetic():
+    dm = B.FinancialLstmDataModule(lookback_window=60, target_window=30, stride=90, batch_size=1)
+    dm.prepare_data()
+    assert (dm.n_windows, dm.train_end, dm.val_end) == (11111, 7777, 9999)
+    assert dm.n_windows - dm.val_end == 1112
+    with pytest.raises(ValueError):
+        B.FinancialLstmDataModule(lookback_window=10, target_window=20, prediction_task=False)
+
+
+def test_plateau_schedule_matches_torch():
+    from masters_thesis_b200.trainer import PlateauSchedule
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.Adam([p], lr=1e-4)
+    ref = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, mode="min", factor=0.5, patience=2)
+    mine = PlateauSchedule(1e-4)
+    for v in [5.0, 4.0, 4.1, 4.2, 4.3, 4.0, 3.99999, 4.5, 4.6, 4.7, 4.8, 4.9, 1.0, 2.0, 2.0, 2.0, 2.0]:
+        ref.step(v)
+        assert mine.step(v) == pytest.approx(opt.param_groups[0]["lr"], rel=1e-12)
+
+
+_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from masters_thesis_b200.grad_sync import GradBucketer
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:" + sys.argv[2], rank=int(sys.argv[3]), world_size=2)
+rank = dist.get_rank()
+P, slices = 1000, [(900, 100), (600, 300), (250, 350), (0, 250)]       # heads, then layers top-down
+for bucket_mb, expect in [(0.0, 4), (400 * 4 / 2**20, 2), (100.0, 1)]:
+    g = torch.arange(P, dtype=torch.float32) * (rank + 1) / 2           # pre-scaled by 1/W
+    s = GradBucketer(2, bucket_mb)
+    s.begin(g, P)
+    for i, (o, n) in enumerate(slices):
+        s.layer_ready(o, n, last=(i == len(slices) - 1))
+    s.wait()
+    want = torch.arange(P, dtype=torch.float32) * 1.5                   # mean of rank grads x and 2x
+    assert torch.allclose(g, want), (bucket_mb, (g - want).abs().max())
+    assert len(s.flushes) == expect, (bucket_mb, s.flushes)
+    assert sum(n for _, n in s.flushes) == P
+try:
+    s.begin(g, P); s.layer_ready(900, 100); s.layer_ready(0, 250)
+    raise SystemExit("non-contiguous slice accepted")
+except ValueError:
+    pass
+dist.barrier()
+print("ok", rank)
+'''
+
+
+def test_grad_bucketer_world2_gloo(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(_WORKER)
+    port = str(29500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), str(ROOT), port, str(r)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+        assert "ok" in o
