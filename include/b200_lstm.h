@@ -67,6 +67,13 @@ B200_API const char* b200_last_error(void);
 /* 1 when the LSTM engine `mode` is compiled into this library, else 0 */
 B200_API int b200_mode_available(int mode);
 
+/* Per-kernel timing for bench.py's roofline leg (no counterpart in the reference).  While enabled,
+ * every kernel launch of the LSTM/heads/optimiser paths is bracketed by CUDA events on the launching
+ * stream.  b200_timing_report synchronises those events and writes one line per kernel:
+ * "<kernel name> <launches> <total milliseconds>\n". */
+B200_API int b200_timing_enable(int on);
+B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
+
 /* number of fp32 parameters of the model (src/model.py:88-97): 51,074 for F=3,H=64,L=2 */
 B200_API int64_t b200_param_count(int n_features, int hidden, int layers);
 /* offset (in floats) of layer l's weight_ih inside the flat vector; l == layers gives the heads */

@@ -19,6 +19,8 @@ PROTOTYPES = {
     "b200_version": (_i, []),
     "b200_last_error": (C.c_char_p, []),
     "b200_mode_available": (_i, [_i]),
+    "b200_timing_enable": (_i, [_i]),
+    "b200_timing_report": (_i, [C.c_char_p, _sz]),
     "b200_param_count": (_l, [_i, _i, _i]),
     "b200_param_offset": (_l, [_i, _i, _i, _i]),
     "b200_gen_batch": (_i, [_u64, _p, _l, _l, _i, _i, _i, _l, _i, _p, _p, _p, _p, _p, _p]),
@@ -72,3 +74,14 @@ def check(rc: int, what: str):
 def ptr(t):
     """Device pointer of a torch tensor (None -> NULL)."""
     return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def timing_report():
+    """{kernel name: (launches, total_ms)} accumulated since b200_timing_enable(1)."""
+    buf = C.create_string_buffer(1 << 14)
+    check(load().b200_timing_report(buf, len(buf)), "b200_timing_report")
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, n, ms = line.rsplit(" ", 2)
+        out[name] = (int(n), float(ms))
+    return out

@@ -19,6 +19,41 @@ int cuda_fail(cudaError_t e, const char* what) {
     return -1000 - (int)e;
 }
 
+// ---- per-kernel timing registry ---------------------------------------------------------------
+struct TimingSlot {
+    const char* name;
+    cudaEvent_t ev[2 * 4096];
+    int used;       // events recorded (pairs * 2)
+    int allocated;  // events created
+};
+static TimingSlot g_slots[32];
+static int g_nslots = 0;
+static bool g_timing = false;
+static TimingSlot* g_open = nullptr;
+
+void timing_begin(const char* name, cudaStream_t st) {
+    if (!g_timing) return;
+    TimingSlot* s = nullptr;
+    for (int i = 0; i < g_nslots; ++i)
+        if (g_slots[i].name == name || strcmp(g_slots[i].name, name) == 0) { s = &g_slots[i]; break; }
+    if (!s) {
+        if (g_nslots == 32) return;
+        s = &g_slots[g_nslots++];
+        s->name = name; s->used = 0; s->allocated = 0;
+    }
+    if (s->used + 2 > 2 * 4096) return;
+    while (s->allocated < s->used + 2) cudaEventCreate(&s->ev[s->allocated++]);
+    cudaEventRecord(s->ev[s->used], st);
+    g_open = s;
+}
+
+void timing_end(cudaStream_t st) {
+    if (!g_timing || !g_open) return;
+    cudaEventRecord(g_open->ev[g_open->used + 1], st);
+    g_open->used += 2;
+    g_open = nullptr;
+}
+
 // engines (lstm_ffma.cu, lstm_tc.cu)
 size_t ffma_workspace_bytes(int64_t N, int T, int L);
 int ffma_fwd(const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h, float* stash_c,
@@ -44,6 +79,33 @@ extern "C" int b200_mode_available(int mode) {
     if (mode == B200_MODE_FFMA) return 1;
     if (mode == B200_MODE_TC_PRECISE || mode == B200_MODE_TC_FAST) return tc_available() ? 1 : 0;
     return 0;
+}
+
+extern "C" int b200_timing_enable(int on) {
+    g_timing = on != 0;
+    if (on) for (int i = 0; i < g_nslots; ++i) g_slots[i].used = 0;
+    return B200_OK;
+}
+
+extern "C" int b200_timing_report(char* buf, size_t buf_bytes) {
+    B200_CHECK_ARG(buf && buf_bytes > 0, "timing_report: null buffer");
+    size_t off = 0;
+    buf[0] = 0;
+    for (int i = 0; i < g_nslots; ++i) {
+        TimingSlot& s = g_slots[i];
+        if (s.used == 0) continue;
+        B200_CUDA(cudaEventSynchronize(s.ev[s.used - 1]));
+        double total = 0.0;
+        for (int k = 0; k < s.used; k += 2) {
+            float ms = 0.f;
+            B200_CUDA(cudaEventElapsedTime(&ms, s.ev[k], s.ev[k + 1]));
+            total += ms;
+        }
+        int n = snprintf(buf + off, buf_bytes - off, "%s %d %.6f\n", s.name, s.used / 2, total);
+        if (n < 0 || (size_t)n >= buf_bytes - off) break;
+        off += (size_t)n;
+    }
+    return B200_OK;
 }
 
 extern "C" int64_t b200_param_offset(int F, int H, int L, int l) {

@@ -33,6 +33,16 @@ int cuda_fail(cudaError_t e, const char* what);
         if (_e != cudaSuccess) return b200::cuda_fail(_e, "launch " name); \
     } while (0)
 
+// ---- optional per-kernel timing (bench.py's roofline leg): CUDA events recorded on the launching
+// stream around each named launch while enabled; zero cost when disabled.
+void timing_begin(const char* name, cudaStream_t st);
+void timing_end(cudaStream_t st);
+struct TimedLaunch {
+    cudaStream_t st;
+    TimedLaunch(const char* name, cudaStream_t s) : st(s) { timing_begin(name, s); }
+    ~TimedLaunch() { timing_end(st); }
+};
+
 inline int num_sms() {
     static int cached[64] = {0};
     int dev = 0;

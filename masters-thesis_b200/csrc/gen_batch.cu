@@ -176,16 +176,16 @@ extern "C" int b200_gen_batch(uint64_t seed, const int64_t* window_idx, int64_t 
                    lookback + target);
     B200_CUDA(cudaFuncSetAttribute(gen_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t grid = n_windows < (int64_t)num_sms() * 16 ? n_windows : (int64_t)num_sms() * 16;
-    gen_batch_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(seed, window_idx, first_window, n_windows, n_stocks,
+    { TimedLaunch _t("gen_batch_kernel", (cudaStream_t)stream); gen_batch_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(seed, window_idx, first_window, n_windows, n_stocks,
                                                                          lookback, target, stride, n_features, x, y_stock,
-                                                                         y_market, factor, inv_psi);
+                                                                         y_market, factor, inv_psi); }
     B200_LAUNCH_CHECK("gen_batch_kernel");
     return B200_OK;
 }
 
 extern "C" int b200_gen_coefficients(uint64_t seed, int n_stocks, float* alpha, float* beta, void* stream) {
     B200_CHECK_ARG(n_stocks > 0 && alpha && beta, "gen_coefficients: bad arguments");
-    gen_coeff_kernel<<<(n_stocks + 127) / 128, 128, 0, (cudaStream_t)stream>>>(seed, n_stocks, alpha, beta);
+    { TimedLaunch _t("gen_coeff_kernel", (cudaStream_t)stream); gen_coeff_kernel<<<(n_stocks + 127) / 128, 128, 0, (cudaStream_t)stream>>>(seed, n_stocks, alpha, beta); }
     B200_LAUNCH_CHECK("gen_coeff_kernel");
     return B200_OK;
 }
@@ -193,7 +193,7 @@ extern "C" int b200_gen_coefficients(uint64_t seed, int n_stocks, float* alpha, 
 extern "C" int b200_philox4x32(uint64_t seed, const uint32_t* counters, int64_t n, uint32_t* out, void* stream) {
     B200_CHECK_ARG(n >= 0 && (n == 0 || (counters && out)), "philox4x32: bad arguments");
     if (n == 0) return B200_OK;
-    philox_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, counters, n, out);
+    { TimedLaunch _t("philox_kernel", (cudaStream_t)stream); philox_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, counters, n, out); }
     B200_LAUNCH_CHECK("philox_kernel");
     return B200_OK;
 }
@@ -203,7 +203,7 @@ extern "C" int b200_dropout_mask(uint64_t seed, int layer, int64_t n_seq, int T,
     B200_CHECK_ARG(n_seq > 0 && T > 0 && hidden > 0 && hidden % 8 == 0 && out, "dropout_mask: bad sizes");
     B200_CHECK_ARG(p >= 0.f && p < 1.f, "dropout_mask: p must be in [0,1), got %f", p);
     B200_CHECK_ARG(layer >= 1 && layer < 65536 && T < 65536, "dropout_mask: layer/T out of range");
-    dropout_mask_kernel<<<num_sms() * 8, 256, 0, (cudaStream_t)stream>>>(seed, layer, n_seq, T, hidden, p, out);
+    { TimedLaunch _t("dropout_mask_kernel", (cudaStream_t)stream); dropout_mask_kernel<<<num_sms() * 8, 256, 0, (cudaStream_t)stream>>>(seed, layer, n_seq, T, hidden, p, out); }
     B200_LAUNCH_CHECK("dropout_mask_kernel");
     return B200_OK;
 }

@@ -260,23 +260,23 @@ static int heads_launch(int loss_kind, float mse_weight, const float* hp, const 
     const int64_t G = B / wpg;
     float* al = alpha_out ? alpha_out : ws.alpha;
     float* be = beta_out ? beta_out : ws.beta;
-    heads_stats_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, factor, inv_psi, S, n, wpg,
-                                                                 do_nll, al, be, ws.wpart);
+    { TimedLaunch _t("heads_stats_kernel", st); heads_stats_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, factor, inv_psi, S, n, wpg,
+                                                                 do_nll, al, be, ws.wpart); }
     B200_LAUNCH_CHECK("heads_stats_kernel");
-    heads_group_kernel<<<(unsigned)G, 256, 0, st>>>(ws.wpart, factor, S, n, wpg, do_nll, ws.gstat, ws.gloss);
+    { TimedLaunch _t("heads_group_kernel", st); heads_group_kernel<<<(unsigned)G, 256, 0, st>>>(ws.wpart, factor, S, n, wpg, do_nll, ws.gstat, ws.gloss); }
     B200_LAUNCH_CHECK("heads_group_kernel");
     const double n_elems = (double)B * S * n;
-    heads_final_kernel<<<1, 256, 0, st>>>(ws.gloss, G, n_elems, loss_kind, mse_weight, losses_out);
+    { TimedLaunch _t("heads_final_kernel", st); heads_final_kernel<<<1, 256, 0, st>>>(ws.gloss, G, n_elems, loss_kind, mse_weight, losses_out); }
     B200_LAUNCH_CHECK("heads_final_kernel");
     if (dhT) {
         const float w_mse = loss_kind == B200_LOSS_MSE ? 1.f : loss_kind == B200_LOSS_NLL ? 0.f : mse_weight;
         const float c_mse = (float)((double)grad_scale * w_mse * 2.0 / n_elems);
         const float c_nll = do_nll ? (float)((double)grad_scale / (double)G) : 0.f;
-        heads_grad_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, inv_psi, al, be, ws.gstat, S, n,
-                                                                    wpg, c_mse, c_nll, dhT, ws.hpart);
+        { TimedLaunch _t("heads_grad_kernel", st); heads_grad_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, inv_psi, al, be, ws.gstat, S, n,
+                                                                    wpg, c_mse, c_nll, dhT, ws.hpart); }
         B200_LAUNCH_CHECK("heads_grad_kernel");
         if (head_grads) {
-            heads_reduce_kernel<<<2 * H + 2, 256, 0, st>>>(ws.hpart, B, 2 * H + 2, head_grads);
+            { TimedLaunch _t("heads_reduce_kernel", st); heads_reduce_kernel<<<2 * H + 2, 256, 0, st>>>(ws.hpart, B, 2 * H + 2, head_grads); }
             B200_LAUNCH_CHECK("heads_reduce_kernel");
         }
     }

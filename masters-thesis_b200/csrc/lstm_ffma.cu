@@ -489,9 +489,11 @@ int ffma_fwd(const float* params, int F, int H, int L, const float* x, int64_t N
         const size_t smem = fwd_smem(g);
         if (l == 0) {
             B200_CUDA(cudaFuncSetAttribute(lstm_ffma_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            TimedLaunch _t("lstm_ffma_fwd_kernel", st);
             lstm_ffma_fwd_kernel<true><<<grid, L_THREADS, smem, st>>>(g, x, N, T, stash_h, stash_c, false, seed, p);
         } else {
             B200_CUDA(cudaFuncSetAttribute(lstm_ffma_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            TimedLaunch _t("lstm_ffma_fwd_kernel", st);
             lstm_ffma_fwd_kernel<false><<<grid, L_THREADS, smem, st>>>(g, stash_h + (l - 1) * lsz, N, T, stash_h + l * lsz,
                                                                       stash_c + l * lsz, drop, seed, p);
         }
@@ -526,20 +528,22 @@ int ffma_bwd_layer(int layer, const float* params, int F, int H, int L, const fl
         (void)ntiles;
         if (layer == 0) {
             B200_CUDA(cudaFuncSetAttribute(lstm_ffma_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            TimedLaunch _t("lstm_ffma_bwd_kernel", st);
             lstm_ffma_bwd_kernel<true><<<grid, L_THREADS, smem, st>>>(g, xin, N, T, h_st, c_st, d_out, dhT, d_in, ws.da, c0, cn,
                                                                       ws.bpart, acc, false, seed, p);
         } else {
             B200_CUDA(cudaFuncSetAttribute(lstm_ffma_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            TimedLaunch _t("lstm_ffma_bwd_kernel", st);
             lstm_ffma_bwd_kernel<false><<<grid, L_THREADS, smem, st>>>(g, xin, N, T, h_st, c_st, d_out, dhT, d_in, ws.da, c0, cn,
                                                                        ws.bpart, acc, drop, seed, p);
         }
         B200_LAUNCH_CHECK("lstm_ffma_bwd_kernel");
         dim3 wg(2, ws.nsplit);
         if (layer == 0)
-            lstm_ffma_wgrad_kernel<true><<<wg, 256, 0, st>>>(g, xin, N, T, h_st, ws.da, c0, cn, ws.wpart, acc, false, seed, p);
+            { TimedLaunch _t("lstm_ffma_wgrad_kernel", st); lstm_ffma_wgrad_kernel<true><<<wg, 256, 0, st>>>(g, xin, N, T, h_st, ws.da, c0, cn, ws.wpart, acc, false, seed, p); }
         else
-            lstm_ffma_wgrad_kernel<false><<<wg, 256, 0, st>>>(g, xin, N, T, h_st, ws.da, c0, cn, ws.wpart, acc, drop, seed, p);
-        B200_LAUNCH_CHECK("lstm_ffma_wgrad_kernel");
+            { TimedLaunch _t("lstm_ffma_wgrad_kernel", st); lstm_ffma_wgrad_kernel<false><<<wg, 256, 0, st>>>(g, xin, N, T, h_st, ws.da, c0, cn, ws.wpart, acc, drop, seed, p); }
+            B200_LAUNCH_CHECK("lstm_ffma_wgrad_kernel");
     }
     float* gbase = grads + b200_param_offset(F, LH, L, layer);
     float* gw_ih = gbase;
@@ -547,8 +551,8 @@ int ffma_bwd_layer(int layer, const float* params, int F, int H, int L, const fl
     float* gb_ih = gw_hh + (int64_t)LG * LH;
     float* gb_hh = gb_ih + LG;
     const int total = LG * g.kin + LG * LH + LG;
-    lstm_grad_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws.wpart, ws.nsplit, ws.bpart, ws.bwd_grid * L_WARPS, g.kin, g.kp,
-                                                                 gw_ih, gw_hh, gb_ih, gb_hh);
+    { TimedLaunch _t("lstm_grad_reduce_kernel", st); lstm_grad_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws.wpart, ws.nsplit, ws.bpart, ws.bwd_grid * L_WARPS, g.kin, g.kp,
+                                                                 gw_ih, gw_hh, gb_ih, gb_hh); }
     B200_LAUNCH_CHECK("lstm_grad_reduce_kernel");
     return B200_OK;
 }

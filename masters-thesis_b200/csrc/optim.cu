@@ -115,9 +115,9 @@ extern "C" int b200_grad_sqnorm(const float* grads, int64_t count, float* sqnorm
     B200_CHECK_ARG(((uintptr_t)grads & 15) == 0, "grad_sqnorm: grads must be 16-byte aligned");
     B200_CHECK_ARG(workspace_bytes >= SQ_MAX_BLOCKS * sizeof(double), "grad_sqnorm: workspace too small");
     int nb = sq_blocks(count);
-    sqnorm_partial_kernel<<<nb, SQ_THREADS, 0, (cudaStream_t)stream>>>(grads, count, (double*)workspace);
+    { TimedLaunch _t("sqnorm_partial_kernel", (cudaStream_t)stream); sqnorm_partial_kernel<<<nb, SQ_THREADS, 0, (cudaStream_t)stream>>>(grads, count, (double*)workspace); }
     B200_LAUNCH_CHECK("sqnorm_partial_kernel");
-    sqnorm_final_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const double*)workspace, nb, sqnorm_out);
+    { TimedLaunch _t("sqnorm_final_kernel", (cudaStream_t)stream); sqnorm_final_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const double*)workspace, nb, sqnorm_out); }
     B200_LAUNCH_CHECK("sqnorm_final_kernel");
     return B200_OK;
 }
@@ -140,7 +140,7 @@ extern "C" int b200_adam_step(float* params, float* grads, float* exp_avg, float
     int64_t cap = (int64_t)num_sms() * 8;
     if (nb > cap) nb = cap;
     if (nb < 1) nb = 1;
-    adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, count, a, sqnorm, zero_grad);
+    { TimedLaunch _t("adam_kernel", (cudaStream_t)stream); adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, count, a, sqnorm, zero_grad); }
     B200_LAUNCH_CHECK("adam_kernel");
     return B200_OK;
 }
