@@ -173,6 +173,23 @@ B200_API int b200_heads_nll_fwd_bwd(const float* head_params, int hidden, const 
 B200_API size_t b200_sqnorm_workspace_bytes(int64_t count);
 B200_API int b200_grad_sqnorm(const float* grads, int64_t count, float* sqnorm_out,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* No counterpart in the reference.  Same result as b200_grad_sqnorm, for callers that have no way to
+ * hand over a workspace: a binding that only holds the gradient pointer (the ctypes stub in
+ * INTEGRATION.md owns no allocator), or a training/serving loop that has frozen its memory plan --
+ * the framework's caching allocator already holds the device memory, so a fresh cudaMalloc may fail,
+ * and it would stall every stream while it runs.  The partial sums go to an 8 KB array compiled into
+ * the library (one fp64 slot per 4,096 gradients) instead of caller memory.
+ *   - limit: count <= B200_SQNORM_STATIC_MAX (4,194,304 gradients, a 16 MB vector: every model of
+ *     configs/model/ including `wide`); larger counts are rejected with B200_ERR_INVALID
+ *   - the first call on each device looks up the array's device address; make that first call with
+ *     the device current and before starting any stream capture.  Later calls only launch kernels.
+ *   - nothing needs zeroing between calls (each call overwrites the slots it then reads), but all
+ *     calls on a device share the one array: two calls whose kernels can overlap on the GPU
+ *     (different streams, no ordering between them) race and return garbage.  Serialise them.
+ *   - allocates nothing: no cudaMalloc/cudaFree, no library or torch allocation. */
+#define B200_SQNORM_STATIC_MAX 4194304
+B200_API int b200_grad_sqnorm_static(const float* grads, int64_t count, float* sqnorm_out, void* stream);
+
 /* Replaces the clip scaling + torch.optim.Adam.step (src/model.py:150-154): L2-coupled weight
  * decay, bias correction, eps outside the sqrt(v_hat).  clip_val <= 0 or sqnorm == NULL disables
  * clipping; otherwise g *= min(1, clip_val / (sqrt(*sqnorm) + 1e-6)).  step is 1-based.

@@ -37,6 +37,7 @@ PROTOTYPES = {
     "b200_heads_nll_fwd_bwd": (_i, [_p, _i, _p, _p, _p, _p, _l, _i, _i, _l, _f, _p, _p, _p, _p, _sz, _p]),
     "b200_sqnorm_workspace_bytes": (_sz, [_l]),
     "b200_grad_sqnorm": (_i, [_p, _l, _p, _p, _sz, _p]),
+    "b200_grad_sqnorm_static": (_i, [_p, _l, _p, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _l, _f, _p, _i, _p]),
 }
 

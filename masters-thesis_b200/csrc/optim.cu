@@ -96,6 +96,12 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
         }
 }
 
+// Scratch of b200_grad_sqnorm_static: one fp64 partial per 4,096-gradient tile, so 1,024 slots cover
+// B200_SQNORM_STATIC_MAX gradients.  Lives in every CUDA context that loads the library until exit (8 KB).
+// In host code this name is only a handle; the device address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) double g_sqnorm_static_scratch[SQ_MAX_BLOCKS];
+static double* g_sqnorm_static_ptr[64] = {nullptr};    // per-device address of the array above
+
 static int sq_blocks(int64_t count) {
     int64_t b = (count / 4 + SQ_THREADS * 4 - 1) / (SQ_THREADS * 4);
     if (b < 1) b = 1;
@@ -142,5 +148,30 @@ extern "C" int b200_adam_step(float* params, float* grads, float* exp_avg, float
     if (nb < 1) nb = 1;
     { TimedLaunch _t("adam_kernel", (cudaStream_t)stream); adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, count, a, sqnorm, zero_grad); }
     B200_LAUNCH_CHECK("adam_kernel");
+    return B200_OK;
+}
+
+// Allocation-free variant of b200_grad_sqnorm (see include/b200_lstm.h).
+extern "C" int b200_grad_sqnorm_static(const float* grads, int64_t count, float* sqnorm_out, void* stream) {
+    B200_CHECK_ARG(count > 0 && grads && sqnorm_out, "grad_sqnorm_static: bad arguments");
+    B200_CHECK_ARG(count <= (int64_t)B200_SQNORM_STATIC_MAX,
+                   "grad_sqnorm_static: %lld gradients exceed the built-in scratch (max %lld); use b200_grad_sqnorm with a caller workspace",
+                   (long long)count, (long long)B200_SQNORM_STATIC_MAX);
+    B200_CHECK_ARG(((uintptr_t)grads & 15) == 0, "grad_sqnorm_static: grads must be 16-byte aligned");
+    int dev = 0;
+    B200_CUDA(cudaGetDevice(&dev));
+    B200_CHECK_ARG(dev >= 0 && dev < 64, "grad_sqnorm_static: device ordinal %d out of range", dev);
+    if (g_sqnorm_static_ptr[dev] == nullptr) {
+        // one-time set-up for this device (it is the current device): resolve the array's device address
+        double* p = nullptr;
+        B200_CUDA(cudaGetSymbolAddress((void**)&p, g_sqnorm_static_scratch));
+        g_sqnorm_static_ptr[dev] = p;
+    }
+    double* scratch = g_sqnorm_static_ptr[dev];
+    const int nb = sq_blocks(count);       // <= SQ_MAX_BLOCKS; every slot read below is written first, nothing to clear
+    { TimedLaunch _t("sqnorm_partial_kernel", (cudaStream_t)stream); sqnorm_partial_kernel<<<nb, SQ_THREADS, 0, (cudaStream_t)stream>>>(grads, count, scratch); }
+    B200_LAUNCH_CHECK("sqnorm_partial_kernel");
+    { TimedLaunch _t("sqnorm_final_kernel", (cudaStream_t)stream); sqnorm_final_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(scratch, nb, sqnorm_out); }
+    B200_LAUNCH_CHECK("sqnorm_final_kernel");
     return B200_OK;
 }
