@@ -175,3 +175,19 @@ def test_clip_and_adam_vs_torch(count, clip):
         assert float(dg.abs().max()) == 0.0          # zero_grad
         np.testing.assert_allclose(dp[:count].cpu().numpy(), tp.detach().numpy(), rtol=2e-5, atol=2e-7)
     assert float(dp[count:].abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("K", [16, 64])
+def test_tcgen05_gemm_selftest(K):
+    """UMMA descriptors / instruction descriptor / TMEM load mapping: a 128x256xK product with the bf16x3 split
+    must agree with the fp32 product to ~1e-5 relative."""
+    lib = load()
+    g = torch.Generator().manual_seed(K)
+    A = torch.randn(128, K, generator=g)
+    Bm = torch.randn(256, K, generator=g) * 0.125
+    D = torch.zeros(128, 256, device=DEV)
+    dA, dB = A.to(DEV), Bm.to(DEV)          # keep the device tensors alive across the call
+    check(lib.b200_tc_selftest(ptr(dA), ptr(dB), K, ptr(D), None), "tc_selftest")
+    torch.cuda.synchronize()
+    want = (A.double() @ Bm.double().T).numpy()
+    assert rel_err(D.cpu().numpy(), want) < 2e-5

@@ -78,7 +78,9 @@ def test_training_steps_vs_reference_golden(engine, kind, data, golden_dir):
         assert float(losses[2]) == pytest.approx(float(g["losses"][s]), rel=LOSS_RTOL)
         if s == 0:
             assert float(torch.sqrt(e.sqnorm)) == pytest.approx(float(g["gnorm0"]), rel=GRAD_RTOL)
-    np.testing.assert_allclose(e.params[: e.P].cpu().numpy(), g["final"], rtol=0, atol=2e-6)
+    # Adam normalises the gradient, so a parameter whose gradient is ~0 may move by a different fraction of
+    # lr = 1e-4 per step; 3 steps move a parameter by at most 3e-4
+    np.testing.assert_allclose(e.params[: e.P].cpu().numpy(), g["final"], rtol=0, atol=2e-6 if engine == "ffma" else 2e-5)
     # validation / test semantics (batch of one window each)
     vb = B.DeviceBatch.from_reference(ref_batch(data, 4, 6), DEV)
     for w in (0, 1):
