@@ -262,7 +262,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--engine", default="ffma")
+    ap.add_argument("--engine", default="tc_precise", help="ffma | tc_precise | tc_fast")
     ap.add_argument("--model", default="small", choices=sorted(MODELS))
     ap.add_argument("--loss", default="mse", choices=["mse", "nll", "combined"])
     ap.add_argument("--batch", type=int, default=4096, help="windows per GPU per step")

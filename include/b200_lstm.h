@@ -129,10 +129,13 @@ B200_API int b200_lstm_bwd(int mode, const float* params, int n_features, int hi
                   float dropout_p, uint64_t dropout_seed, int training,
                   void* workspace, size_t workspace_bytes, void* stream);
 
-/* Unit test hook of the tcgen05 engine (no counterpart in the reference): D[128][256] = A[128][K] * B[256][K]^T
- * (fp32 in/out, K in {16,32,48,64}) through the same UMMA descriptors, bf16x3 split, tcgen05.mma and
- * TMEM load path as the LSTM kernels. */
-B200_API int b200_tc_selftest(const float* A, const float* B, int K, float* D, void* stream);
+/* Unit test hook of the tcgen05 engine (no counterpart in the reference): one GEMM with M = 128 through the
+ * same UMMA descriptors, bf16x3 split, tcgen05.mma and TMEM load path as the LSTM kernels (fp32 in/out).
+ *   variant 0: D[128][N] = A[128][K] * B[N][K]^T   (forward gate GEMM: both operands K-major)
+ *   variant 1: D[128][N] = A[128][K] * B[K][N]     (data gradient: B image read MN-major)
+ *   variant 2: D[128][N] = A[K][128]^T * B[K][N]   (weight gradient: A and B images read MN-major)
+ * K, N multiples of 16, <= 256. */
+B200_API int b200_tc_selftest(const float* A, const float* B, int variant, int K, int N, float* D, void* stream);
 
 /* ---------------------------------------------------------------- heads + objective
  * Replaces alpha_head/beta_head (src/model.py:107-108, addmm), the decoder arithmetic of

@@ -474,6 +474,28 @@ static size_t ffma_ws_layout(int64_t N, int T, int L, size_t avail, char* base, 
 
 size_t ffma_workspace_bytes(int64_t N, int T, int L) { return ffma_ws_layout(N, T, L, 0, nullptr, nullptr); }
 
+// Shared with the tcgen05 engine (lstm_tc.cu): the dx ping-pong buffers and the partial-gradient areas of the same
+// workspace layout, and the fixed-order reduction of the partials into the layer's gradient slice.
+int ffma_ws_pointers(int64_t N, int T, int L, void* workspace, size_t ws_bytes, float** dx0, float** dx1, float** wpart,
+                     float** bpart, int* nsplit) {
+    FfmaWs ws;
+    const size_t need = ffma_ws_layout(N, T, L, ws_bytes, (char*)workspace, &ws);
+    (void)need;
+    *dx0 = ws.dx[0]; *dx1 = ws.dx[1]; *wpart = ws.wpart; *bpart = ws.bpart; *nsplit = ws.nsplit;
+    // everything up to (and including) bpart must fit; the da chunk that follows is unused by the tcgen05 engine
+    const size_t fixed = (size_t)((char*)ws.bpart - (char*)workspace) + (size_t)ws.bwd_grid * L_WARPS * LG * 4;
+    if (fixed > ws_bytes) { set_error("lstm_bwd: workspace too small (%zu < %zu)", ws_bytes, fixed); return B200_ERR_INVALID; }
+    return B200_OK;
+}
+
+int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float* gw_ih,
+                       float* gw_hh, float* gb_ih, float* gb_hh, cudaStream_t st) {
+    const int total = LG * kin + LG * LH + LG;
+    { TimedLaunch _t("lstm_grad_reduce_kernel", st); lstm_grad_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, nsplit, bpart, nbpart, kin, kp, gw_ih, gw_hh, gb_ih, gb_hh); }
+    B200_LAUNCH_CHECK("lstm_grad_reduce_kernel");
+    return B200_OK;
+}
+
 static size_t fwd_smem(const LayerGeom& g) { return ((size_t)g.ktot * WT_STRIDE + LG + (size_t)L_ROWS * (g.ktot + 4)) * 4; }
 static size_t bwd_smem(const LayerGeom& g) { return ((size_t)g.ktot * WT_STRIDE + LG + (size_t)L_ROWS * (LG + 4)) * 4; }
 

@@ -359,81 +359,574 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     if (warp == EPI_WARPS + LOADER_WARPS) tmem_dealloc(tmem_base, NTILE * TG);
 }
 
-// --------------------------------------------------------------------------------------------- self test
-// One 128 x 256 x K GEMM through exactly the descriptors, instruction and TMEM load path of the kernel above.
-__global__ void __launch_bounds__(128, 1)
-tc_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B, int K, float* __restrict__ D) {
+// --------------------------------------------------------------------------------------------- backward
+// Replaces the autograd backward of nn.LSTM (mkldnn_rnn_layer_backward / cuDNN): BPTT of one layer, fully fused.
+//
+// One tile (128 sequences) per CTA at a time; per step t = T-1 .. 0 the tensor pipe runs three GEMM groups that
+// share operand images in shared memory:
+//   recompute  a_t   [128 x 256]  = [x_t | h_{t-1}] * Wcat^T            (two N = 128 halves; K = KX + 64)
+//   dgrad      [dx_t | dh_{t-1}]  = da_t * Wcat                          (Wcat image read MN-major; accumulated over
+//                                                                          four 64-column quarters of da_t)
+//   wgrad      dWcat^T [128 x 256] += [x_t | h_{t-1}]^T * da_t           (both images read MN-major; accumulator stays
+//                                                                          in TMEM for the whole launch)
+// TMEM (512 columns): dWcat^T 256 | a half 128 | [dx | dh] 128.
+// Gate columns are "packed": n = (u / 32) * 128 + gate * 32 + u % 32, so that each recompute half and each
+// 16-unit quarter holds all four gates of its units.  A quarter of da_t is written by the epilogue warps as a
+// [128 x 64] operand image (column kk = gate * 16 + u % 16); the dgrad K-steps of a quarter are the four 16-row
+// runs of Wcat that hold those columns; the wgrad accumulator columns are quarter * 64 + kk.
+// Warp roles: 8 epilogue warps (thread = one sequence x 8 units per quarter; gates, cell derivative, da, bias-gradient
+// butterfly, dh/dx read-back), 2 loader warps ([x_t | h_{t-1}] image from the fp32 stash, dropout applied),
+// 1 MMA warp.  Barriers: xh_full/xh_free, a_full/a_free, da_full/da_free, d_full/d_free.
+constexpr int BW_EPI_WARPS = 8;
+constexpr int BW_THREADS = 32 * (BW_EPI_WARPS + LOADER_WARPS + 1);
+constexpr uint32_t TMEM_DW = 0, TMEM_A = 256, TMEM_D = 384;
+
+__host__ __device__ constexpr int packed_row(int gate, int u) { return (u >> 5) * 128 + gate * 32 + (u & 31); }
+
+__host__ __device__ inline size_t bwd_pack_bytes(bool layer0) {
+    return 2 * (size_t)op_bytes(TG, kx_of(layer0) + TH) + TG * sizeof(float);
+}
+
+// Wcat images (hi, lo): row = packed gate column, col = [x part (KX, zero padded) | h part (64)]; then bias'
+__global__ void __launch_bounds__(256)
+tc_pack_bwd_weights_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, const float* __restrict__ b_ih,
+                           const float* __restrict__ b_hh, int kin, int kx, uint8_t* __restrict__ out) {
+    const int KC = kx + TH;
+    const uint32_t wb = op_bytes(TG, KC);
+    uint8_t* w_hi = out;
+    uint8_t* w_lo = out + wb;
+    float* biasp = reinterpret_cast<float*>(out + 2 * wb);
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+    for (int i = tid; i < TG * KC; i += nthr) {
+        const int j = i / KC, k = i - j * KC;
+        float v = 0.f;
+        if (k < kx) { if (k < kin) v = w_ih[j * kin + k]; }
+        else v = w_hh[j * TH + (k - kx)];
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
+        const uint32_t o = op_offset(packed_row(j / TH, j % TH), k, KC);
+        *reinterpret_cast<__nv_bfloat16*>(w_hi + o) = h;
+        *reinterpret_cast<__nv_bfloat16*>(w_lo + o) = l;
+    }
+    for (int j = tid; j < TG; j += nthr) {
+        const float b = b_ih[j] + b_hh[j];
+        biasp[j] = (j / TH) == 2 ? 2.0f * LOG2E * b : -LOG2E * b;
+    }
+}
+
+template <int NSPLIT, bool LAYER0, int XB, int DB>
+struct BwdSmem {
+    static constexpr int KX = kx_of(LAYER0), KC = KX + TH;
+    static constexpr uint32_t WB = op_bytes(TG, KC), XHB = op_bytes(TM, KC), DAB = op_bytes(TM, 64);
+    static constexpr uint32_t off_w = 0;                                   // [NSPLIT]
+    static constexpr uint32_t off_xh = off_w + NSPLIT * WB;                // [XB][NSPLIT]
+    static constexpr uint32_t off_da = off_xh + XB * NSPLIT * XHB;         // [DB][NSPLIT]
+    static constexpr uint32_t off_pad = off_da + DB * NSPLIT * DAB;        // MN-major reads of a KC = 80 image run past its end
+    static constexpr uint32_t off_bias = off_pad + (LAYER0 ? 1024 : 0);
+    static constexpr uint32_t off_bar = off_bias + TG * 4;
+    static constexpr int NBAR = 2 * XB + 2 * DB + 4;
+    static constexpr uint32_t off_tmem = off_bar + NBAR * 8;
+    static constexpr uint32_t total = off_tmem + 16 + 128;
+};
+
+// sum over the 32 lanes (rows) of 32 per-lane values; lane L ends up with the total of value index L
+__device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16, half = 16; off > 0; off >>= 1, half >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k < half) {
+                const float keep = up ? v[half + k] : v[k];
+                const float send = up ? v[k] : v[half + k];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+    }
+    return v[0];
+}
+
+__device__ __forceinline__ void ld_global_v8(const float* p, float (&v)[8]) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+}
+
+template <int NSPLIT, bool LAYER0, int XB, int DB>
+__global__ void __launch_bounds__(BW_THREADS, 1)
+lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
+                   const float* __restrict__ h_st, const float* __restrict__ c_st, const float* __restrict__ d_out,
+                   const float* __restrict__ dhT, float* __restrict__ d_in, float* __restrict__ wpart,
+                   float* __restrict__ bpart, int layer, bool drop, uint64_t seed, float p) {
+    using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
+    constexpr int KX = S::KX, KC = S::KC;
+    constexpr uint32_t SBO_W = sbo_of(KC), SBO_DA = sbo_of(64);
+    constexpr int DH_COL0 = LAYER0 ? 0 : TH;                 // column of dh inside the d region
+    constexpr int ND = LAYER0 ? TH : 2 * TH;                  // dgrad N
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    uint64_t* xh_full = bars;               // [XB]
+    uint64_t* xh_free = xh_full + XB;       // [XB]
+    uint64_t* da_full = xh_free + XB;       // [DB]
+    uint64_t* da_free = da_full + DB;       // [DB]
+    uint64_t* a_full = da_free + DB;
+    uint64_t* a_free = a_full + 1;
+    uint64_t* d_full = a_free + 1;
+    uint64_t* d_free = d_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    {   // weights -> smem
+        const uint4* src = reinterpret_cast<const uint4*>(packed);
+        uint4* dst = reinterpret_cast<uint4*>(smem + S::off_w);
+        for (uint32_t i = threadIdx.x; i < (NSPLIT * S::WB) / 16; i += blockDim.x) dst[i] = src[i];
+        const float* bsrc = reinterpret_cast<const float*>(packed + 2 * S::WB);
+        for (int i = threadIdx.x; i < TG; i += blockDim.x) bias_s[i] = bsrc[i];
+        if (LAYER0) for (int i = threadIdx.x; i < 256; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + S::off_pad)[i] = 0u;
+    }
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], LOADER_WARPS); mbar_init(&xh_free[b], 1); }
+        for (int b = 0; b < DB; ++b) { mbar_init(&da_full[b], BW_EPI_WARPS); mbar_init(&da_free[b], 1); }
+        mbar_init(a_full, 1); mbar_init(a_free, BW_EPI_WARPS); mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS);
+        fence_barrier_init();
+    }
+    if (warp == BW_EPI_WARPS + LOADER_WARPS) tmem_alloc(tmem_slot, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int64_t ntiles = (N + TM - 1) / TM;
+    const int64_t my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t total_steps = my_tiles * T;
+
+    if (warp < BW_EPI_WARPS) {
+        // ===================================== epilogue warps =====================================================
+        const int grp = warp >> 2, wq = warp & 3;
+        const int r = wq * 32 + lane;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(wq * 32) << 16);
+        const uint32_t row_off = (uint32_t)(r >> 3) * SBO_DA + (uint32_t)(r & 7) * 16;
+        const uint32_t thr = dropout_threshold(p);
+        const float inv_keep = 1.0f / (1.0f - p);
+        float dc[4][8], dh[4][8], db[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) db[q] = 0.f;
+        int64_t g = 0;
+        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int64_t row = tile * TM + r;
+            const bool live = row < N;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int i = 0; i < 8; ++i) dc[q][i] = dh[q][i] = 0.f;
+            for (int t = T - 1; t >= 0; --t, ++g) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int u0 = 16 * q + 8 * grp;                         // first hidden unit of this thread's slice
+                    // global operands of this quarter (issued before the TMEM wait so that they overlap it)
+                    float ct[8], cp[8], dq[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) ct[i] = cp[i] = dq[i] = 0.f;
+                    if (live) {
+                        const int64_t o = ((int64_t)t * N + row) * TH + u0;
+                        ld_global_v8(c_st + o, ct);
+                        if (t > 0) ld_global_v8(c_st + o - N * TH, cp);
+                        if (d_out) ld_global_v8(d_out + o, dq);
+                        else if (t == T - 1) ld_global_v8(dhT + row * TH + u0, dq);
+                    }
+                    if ((q & 1) == 0) mbar_wait(a_full, (uint32_t)((2 * g + (q >> 1)) & 1));
+                    tc_fence_after();
+                    float av[4][8];
+                    const uint32_t acol = TMEM_A + 16 * (q & 1) + 8 * grp;
+#pragma unroll
+                    for (int gate = 0; gate < 4; ++gate) tmem_ld8(lane_addr + acol + gate * 32, av[gate]);
+                    tmem_ld_wait();
+                    if (q & 1) {                                              // this half of `a` is drained
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(a_free);
+                    }
+                    float da[32];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int u = u0 + i;
+                        const float ei = exp2f(fmaf(av[0][i], -LOG2E, bias_s[0 * TH + u]));
+                        const float ef = exp2f(fmaf(av[1][i], -LOG2E, bias_s[1 * TH + u]));
+                        const float eg = exp2f(fmaf(av[2][i], 2.f * LOG2E, bias_s[2 * TH + u]));
+                        const float eo = exp2f(fmaf(av[3][i], -LOG2E, bias_s[3 * TH + u]));
+                        const float ig = __fdividef(1.f, 1.f + ei), fg = __fdividef(1.f, 1.f + ef);
+                        const float gg = 1.f - __fdividef(2.f, 1.f + eg), og = __fdividef(1.f, 1.f + eo);
+                        const float tc = 1.f - __fdividef(2.f, 1.f + exp2f(2.f * LOG2E * ct[i]));
+                        const float dhv = dh[q][i] + dq[i];
+                        const float d_o = dhv * tc;
+                        const float dcc = dc[q][i] + dhv * og * (1.f - tc * tc);
+                        dc[q][i] = dcc * fg;
+                        const float a_i = dcc * gg * ig * (1.f - ig);
+                        const float a_f = dcc * cp[i] * fg * (1.f - fg);
+                        const float a_g = dcc * ig * (1.f - gg * gg);
+                        const float a_o = d_o * og * (1.f - og);
+                        da[0 * 8 + i] = live ? a_i : 0.f;
+                        da[1 * 8 + i] = live ? a_f : 0.f;
+                        da[2 * 8 + i] = live ? a_g : 0.f;
+                        da[3 * 8 + i] = live ? a_o : 0.f;
+                    }
+                    // operand image of this quarter: column kk = gate * 16 + 8 * grp + i  ->  16-byte chunk gate * 2 + grp
+                    const int64_t qi = 4 * g + q;                              // running quarter index
+                    const int buf = (int)(qi % DB);
+                    if (qi >= DB) mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
+                    uint8_t* da_hi = smem + S::off_da + (buf * NSPLIT) * S::DAB;
+                    uint8_t* da_lo = da_hi + S::DAB;
+#pragma unroll
+                    for (int gate = 0; gate < 4; ++gate) {
+                        uint4 hi4, lo4;
+                        split2(da[gate * 8 + 0], da[gate * 8 + 1], hi4.x, lo4.x);
+                        split2(da[gate * 8 + 2], da[gate * 8 + 3], hi4.y, lo4.y);
+                        split2(da[gate * 8 + 4], da[gate * 8 + 5], hi4.z, lo4.z);
+                        split2(da[gate * 8 + 6], da[gate * 8 + 7], hi4.w, lo4.w);
+                        const uint32_t o = row_off + (uint32_t)(gate * 2 + grp) * LBO_BYTES;
+                        *reinterpret_cast<uint4*>(da_hi + o) = hi4;
+                        if (NSPLIT == 2) *reinterpret_cast<uint4*>(da_lo + o) = lo4;
+                    }
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&da_full[buf]);
+                    db[q] += warp_transpose_sum32(da, lane);                  // bias gradient: sum over the warp's 32 rows
+                }
+                // ---- read back dh_{t-1} (and dx_t) -------------------------------------------------------------
+                mbar_wait(d_full, (uint32_t)(g & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) tmem_ld8(lane_addr + TMEM_D + DH_COL0 + 16 * q + 8 * grp, dh[q]);
+                if (!LAYER0) {
+                    float dx[4][8];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) tmem_ld8(lane_addr + TMEM_D + 32 * grp + 8 * c, dx[c]);
+                    tmem_ld_wait();
+                    if (live) {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const int u = 32 * grp + 8 * c;
+                            if (drop) {
+                                U4 b = dropout_block(seed, layer, row, t, u >> 3);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) dx[c][i] = dropout_lane16(b, i) >= thr ? dx[c][i] * inv_keep : 0.f;
+                            }
+                            st_global_v8(d_in + ((int64_t)t * N + row) * TH + u, dx[c]);
+                        }
+                    }
+                } else {
+                    tmem_ld_wait();
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(d_free);
+            }
+        }
+        // ---- final: bias-gradient partials and the weight-gradient accumulator ---------------------------------------
+        {
+            float* bp = bpart + ((int64_t)blockIdx.x * 4 + wq) * TG;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) bp[(lane >> 3) * TH + 16 * q + 8 * grp + (lane & 7)] = db[q];
+        }
+        // all MMAs of this CTA have completed once the last d_full/da_free phases were observed; the MMA warp commits a
+        // final barrier phase on a_full for the accumulator read-back
+        mbar_wait(a_full, (uint32_t)((2 * total_steps) & 1));
+        tc_fence_after();
+        {
+            const int kcat = r;                                               // TMEM lane = row of dWcat^T
+            float* wp = wpart + (int64_t)blockIdx.x * TG * 128;
+            for (int c0 = grp * 128; c0 < grp * 128 + 128; c0 += 8) {
+                float v[8];
+                tmem_ld8(lane_addr + TMEM_DW + c0, v);
+                tmem_ld_wait();
+                if (kcat < KC) {
+                    const int q = c0 >> 6, kk = c0 & 63, gate = kk >> 4, i0 = kk & 15;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) wp[(gate * TH + 16 * q + i0 + i) * 128 + kcat] = my_tiles > 0 ? v[i] : 0.f;
+                }
+            }
+        }
+    } else if (warp < BW_EPI_WARPS + LOADER_WARPS) {
+        // ===================================== loader warps =======================================================
+        const int lw = warp - BW_EPI_WARPS;
+        const uint32_t thr = dropout_threshold(p);
+        const float inv_keep = 1.0f / (1.0f - p);
+        const int rg_r = lane >> 2, qq = lane & 3;
+        int64_t g = 0;
+        for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            for (int t = T - 1; t >= 0; --t, ++g) {
+                const int buf = (int)(g % XB);
+                if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
+                uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
+                uint8_t* xh_lo = xh_hi + S::XHB;
+#pragma unroll 2
+                for (int rgi = 0; rgi < 8; ++rgi) {
+                    const int rg = lw * 8 + rgi;
+                    const int rr = rg * 8 + rg_r;
+                    const int64_t row = tile * TM + rr;
+                    const bool live = row < N;
+                    const uint32_t base_o = (uint32_t)rg * SBO_W + (uint32_t)rg_r * 16;
+                    // ---- x part ----
+                    if (LAYER0) {
+                        // 16 columns: lane quarter qq covers columns 4qq .. 4qq+3
+                        float v[4] = {0.f, 0.f, 0.f, 0.f};
+                        if (live) {
+                            const float* src = xin + ((int64_t)t * N + row) * kin;
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) if (4 * qq + i < kin) v[i] = src[4 * qq + i];
+                        }
+                        uint2 hi2, lo2;
+                        split2(v[0], v[1], hi2.x, lo2.x);
+                        split2(v[2], v[3], hi2.y, lo2.y);
+                        const int k = 4 * qq;
+                        const uint32_t o = base_o + (uint32_t)(k >> 3) * LBO_BYTES + (uint32_t)(k & 7) * 2;
+                        *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
+                        if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
+                    } else {
+                        const float* src = xin + ((int64_t)t * N + row) * TH;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int k = 4 * qq + 16 * i;
+                            float4 v = live ? *reinterpret_cast<const float4*>(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (drop) {
+                                U4 b = dropout_block(seed, layer, row, t, k >> 3);
+                                const int j0 = k & 7;
+                                v.x = dropout_lane16(b, j0 + 0) >= thr ? v.x * inv_keep : 0.f;
+                                v.y = dropout_lane16(b, j0 + 1) >= thr ? v.y * inv_keep : 0.f;
+                                v.z = dropout_lane16(b, j0 + 2) >= thr ? v.z * inv_keep : 0.f;
+                                v.w = dropout_lane16(b, j0 + 3) >= thr ? v.w * inv_keep : 0.f;
+                            }
+                            uint2 hi2, lo2;
+                            split2(v.x, v.y, hi2.x, lo2.x);
+                            split2(v.z, v.w, hi2.y, lo2.y);
+                            const uint32_t o = base_o + (uint32_t)(k >> 3) * LBO_BYTES + (uint32_t)(k & 7) * 2;
+                            *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
+                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
+                        }
+                    }
+                    // ---- h_{t-1} part ----
+                    {
+                        const float* src = h_st + ((int64_t)(t - 1) * N + row) * TH;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int k = 4 * qq + 16 * i;
+                            float4 v = (live && t > 0) ? *reinterpret_cast<const float4*>(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            uint2 hi2, lo2;
+                            split2(v.x, v.y, hi2.x, lo2.x);
+                            split2(v.z, v.w, hi2.y, lo2.y);
+                            const int kc = KX + k;
+                            const uint32_t o = base_o + (uint32_t)(kc >> 3) * LBO_BYTES + (uint32_t)(kc & 7) * 2;
+                            *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
+                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
+                        }
+                    }
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&xh_full[buf]);
+            }
+        }
+    } else {
+        // ===================================== MMA issuer =========================================================
+        if (lane == 0) {
+            constexpr uint32_t idesc_a = make_idesc_bf16(TM, 128, 0, 0);      // recompute half
+            constexpr uint32_t idesc_d = make_idesc_bf16(TM, ND, 0, 1);       // dgrad: A K-major, B MN-major
+            constexpr uint32_t idesc_w = make_idesc_bf16(TM, 64, 1, 1);       // wgrad: both MN-major
+            const uint32_t s_base = smem_u32(smem);
+            const uint32_t w_hi = s_base + S::off_w, w_lo = w_hi + S::WB;
+            auto issue_recompute = [&](int half, uint32_t xh_hi, uint32_t xh_lo) {
+                const uint32_t d = tmem_base + TMEM_A;
+                const uint32_t wrow = (uint32_t)(half * 128 / 8) * SBO_W;
+                uint32_t acc = 0;
+#pragma unroll
+                for (int ks = 0; ks < KC / 16; ++ks) {
+                    const uint32_t ko = ks * 2 * LBO_BYTES;
+                    umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, acc);
+                    acc = 1;
+                    if (NSPLIT == 2) {
+                        umma_bf16(d, make_desc(xh_lo + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, 1);
+                        umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_lo + wrow + ko, LBO_BYTES, SBO_W), idesc_a, 1);
+                    }
+                }
+                umma_commit(a_full);
+            };
+            int64_t a_free_waits = 0;                                         // number of a_free phases consumed so far
+            bool pre_issued = false;
+            for (int64_t g = 0; g < total_steps; ++g) {
+                const int xb = (int)(g % XB);
+                const uint32_t xh_hi = s_base + S::off_xh + (xb * NSPLIT) * S::XHB, xh_lo = xh_hi + S::XHB;
+                if (!pre_issued) {
+                    mbar_wait(&xh_full[xb], (uint32_t)((g / XB) & 1));
+                    if (g > 0) { mbar_wait(a_free, (uint32_t)(a_free_waits & 1)); ++a_free_waits; }
+                    tc_fence_after();
+                    issue_recompute(0, xh_hi, xh_lo);
+                }
+                pre_issued = false;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (q == 2) {
+                        mbar_wait(a_free, (uint32_t)(a_free_waits & 1)); ++a_free_waits;
+                        tc_fence_after();
+                        issue_recompute(1, xh_hi, xh_lo);
+                    }
+                    if (q == 3 && XB == 2 && g + 1 < total_steps) {
+                        // next step's first recompute half ahead of this step's last quarter (off the dh critical path)
+                        const int nb = (int)((g + 1) % XB);
+                        const uint32_t nh = s_base + S::off_xh + (nb * NSPLIT) * S::XHB;
+                        mbar_wait(&xh_full[nb], (uint32_t)(((g + 1) / XB) & 1));
+                        mbar_wait(a_free, (uint32_t)(a_free_waits & 1)); ++a_free_waits;
+                        tc_fence_after();
+                        issue_recompute(0, nh, nh + S::XHB);
+                        pre_issued = true;
+                    }
+                    const int64_t qi = 4 * g + q;
+                    const int buf = (int)(qi % DB);
+                    mbar_wait(&da_full[buf], (uint32_t)((qi / DB) & 1));
+                    if (q == 0 && g > 0) mbar_wait(d_free, (uint32_t)((g - 1) & 1));
+                    tc_fence_after();
+                    const uint32_t da_hi = s_base + S::off_da + (buf * NSPLIT) * S::DAB, da_lo = da_hi + S::DAB;
+                    // dgrad partial: K = the four 16-column runs (one per gate) of this quarter
+                    {
+                        const uint32_t d = tmem_base + TMEM_D;
+                        const uint32_t mn_off = LAYER0 ? (uint32_t)(KX / 8) * LBO_BYTES : 0u;   // layer 0: only the h columns of Wcat
+#pragma unroll
+                        for (int gate = 0; gate < 4; ++gate) {
+                            const int n0 = (q >> 1) * 128 + gate * 32 + 16 * (q & 1);
+                            const uint32_t wk = (uint32_t)(n0 / 8) * SBO_W + mn_off;
+                            const uint32_t ak = gate * 2 * LBO_BYTES;
+                            const uint32_t acc = (q > 0 || gate > 0) ? 1u : 0u;
+                            umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, acc);
+                            if (NSPLIT == 2) {
+                                umma_bf16(d, make_desc(da_lo + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, 1);
+                                umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_lo + wk, SBO_W, LBO_BYTES), idesc_d, 1);
+                            }
+                        }
+                        if (q == 3) umma_commit(d_full);
+                    }
+                    // wgrad partial: dWcat^T[:, quarter columns] += xh^T * da_quarter, K = the 128 rows of the tile
+                    {
+                        const uint32_t d = tmem_base + TMEM_DW + q * 64;
+                        const uint32_t acc = g > 0 ? 1u : 0u;
+#pragma unroll
+                        for (int ks = 0; ks < TM / 16; ++ks) {
+                            const uint32_t xo = ks * 2 * SBO_W, dao = ks * 2 * SBO_DA;
+                            umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, (acc | (ks > 0)) ? 1u : 0u);
+                            if (NSPLIT == 2) {
+                                umma_bf16(d, make_desc(xh_lo + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
+                                umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_lo + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
+                            }
+                        }
+                        umma_commit(&da_free[buf]);
+                        if (q == 3) umma_commit(&xh_free[xb]);
+                    }
+                }
+            }
+            umma_commit(a_full);              // final phase: every MMA of this CTA is complete
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == BW_EPI_WARPS + LOADER_WARPS) tmem_dealloc(tmem_base, 512);
+}
+
+// --------------------------------------------------------------------------------------------- self test
+// One GEMM through exactly the descriptors, instruction and TMEM load path of the LSTM kernels.
+//   variant 0: D[128][256] = A[128][K] * B[256][K]^T          both operands K-major (forward gate GEMM)
+//   variant 1: D[128][Nn]  = A[128][K] * W[K][Nn]             B = image of W (rows = K index) read MN-major (dgrad)
+//   variant 2: D[128][Nn]  = X[K][128]^T * Y[K][Nn]           A and B images (rows = K index) read MN-major (wgrad)
+// Images are always "rows x cols, 8x8 core matrices, cols contiguous" (op_offset); MN-major reads swap the
+// roles of the two strides: LBO = stride between 8-row groups (the K direction), SBO = 128 (next 8 columns).
+__global__ void __launch_bounds__(128, 1)
+tc_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B, int variant, int K, int Nn, float* __restrict__ D) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    // image shapes (rows, cols)
+    const int a_rows = variant == 2 ? K : TM, a_cols = variant == 2 ? TM : K;
+    const int b_rows = variant == 0 ? Nn : K, b_cols = variant == 0 ? K : Nn;
     uint8_t* a_hi = smem;
-    uint8_t* a_lo = a_hi + op_bytes(TM, K);
-    uint8_t* b_hi = a_lo + op_bytes(TM, K);
-    uint8_t* b_lo = b_hi + op_bytes(TG, K);
-    uint64_t* bar = reinterpret_cast<uint64_t*>(b_lo + op_bytes(TG, K));
+    uint8_t* a_lo = a_hi + op_bytes(a_rows, a_cols);
+    uint8_t* b_hi = a_lo + op_bytes(a_rows, a_cols);
+    uint8_t* b_lo = b_hi + op_bytes(b_rows, b_cols);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(b_lo + op_bytes(b_rows, b_cols));
     uint32_t* tslot = reinterpret_cast<uint32_t*>(bar + 1);
-    for (int i = threadIdx.x; i < TM * K; i += blockDim.x) {
-        const int r = i / K, k = i - r * K;
+    for (int i = threadIdx.x; i < a_rows * a_cols; i += blockDim.x) {
+        const int r = i / a_cols, k = i - r * a_cols;
         const float v = A[i];
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
-        *reinterpret_cast<__nv_bfloat16*>(a_hi + op_offset(r, k, K)) = h;
-        *reinterpret_cast<__nv_bfloat16*>(a_lo + op_offset(r, k, K)) = __float2bfloat16_rn(v - __bfloat162float(h));
+        *reinterpret_cast<__nv_bfloat16*>(a_hi + op_offset(r, k, a_cols)) = h;
+        *reinterpret_cast<__nv_bfloat16*>(a_lo + op_offset(r, k, a_cols)) = __float2bfloat16_rn(v - __bfloat162float(h));
     }
-    for (int i = threadIdx.x; i < TG * K; i += blockDim.x) {
-        const int r = i / K, k = i - r * K;
+    for (int i = threadIdx.x; i < b_rows * b_cols; i += blockDim.x) {
+        const int r = i / b_cols, k = i - r * b_cols;
         const float v = B[i];
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
-        *reinterpret_cast<__nv_bfloat16*>(b_hi + op_offset(r, k, K)) = h;
-        *reinterpret_cast<__nv_bfloat16*>(b_lo + op_offset(r, k, K)) = __float2bfloat16_rn(v - __bfloat162float(h));
+        *reinterpret_cast<__nv_bfloat16*>(b_hi + op_offset(r, k, b_cols)) = h;
+        *reinterpret_cast<__nv_bfloat16*>(b_lo + op_offset(r, k, b_cols)) = __float2bfloat16_rn(v - __bfloat162float(h));
     }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) { mbar_init(bar, 1); fence_barrier_init(); }
-    if (warp == 0) tmem_alloc(tslot, TG);
+    if (warp == 0) tmem_alloc(tslot, 256);
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tslot;
     if (threadIdx.x == 0) {
-        constexpr uint32_t idesc = make_idesc_bf16(TM, TG);
+        const uint32_t idesc = make_idesc_bf16(TM, Nn, variant == 2 ? 1 : 0, variant == 0 ? 0 : 1);
+        // K-major read of an image: LBO = 128, SBO = row-group stride, K-step = +256 B
+        // MN-major read: LBO = row-group stride (K direction), SBO = 128, K-step = +2 row groups
+        const uint32_t a_lbo = variant == 2 ? sbo_of(a_cols) : LBO_BYTES, a_sbo = variant == 2 ? LBO_BYTES : sbo_of(a_cols);
+        const uint32_t b_lbo = variant == 0 ? LBO_BYTES : sbo_of(b_cols), b_sbo = variant == 0 ? sbo_of(b_cols) : LBO_BYTES;
+        const uint32_t a_step = variant == 2 ? 2 * sbo_of(a_cols) : 2 * LBO_BYTES;
+        const uint32_t b_step = variant == 0 ? 2 * LBO_BYTES : 2 * sbo_of(b_cols);
         uint32_t acc = 0;
         for (int ks = 0; ks < K / 16; ++ks) {
-            const uint32_t ko = ks * 2 * LBO_BYTES;
-            umma_bf16(tmem_base, make_desc(smem_u32(a_hi) + ko, LBO_BYTES, sbo_of(K)), make_desc(smem_u32(b_hi) + ko, LBO_BYTES, sbo_of(K)), idesc, acc);
+            const uint32_t ah = smem_u32(a_hi) + ks * a_step, al = smem_u32(a_lo) + ks * a_step;
+            const uint32_t bh = smem_u32(b_hi) + ks * b_step, bl = smem_u32(b_lo) + ks * b_step;
+            umma_bf16(tmem_base, make_desc(ah, a_lbo, a_sbo), make_desc(bh, b_lbo, b_sbo), idesc, acc);
             acc = 1;
-            umma_bf16(tmem_base, make_desc(smem_u32(a_lo) + ko, LBO_BYTES, sbo_of(K)), make_desc(smem_u32(b_hi) + ko, LBO_BYTES, sbo_of(K)), idesc, 1);
-            umma_bf16(tmem_base, make_desc(smem_u32(a_hi) + ko, LBO_BYTES, sbo_of(K)), make_desc(smem_u32(b_lo) + ko, LBO_BYTES, sbo_of(K)), idesc, 1);
+            umma_bf16(tmem_base, make_desc(al, a_lbo, a_sbo), make_desc(bh, b_lbo, b_sbo), idesc, 1);
+            umma_bf16(tmem_base, make_desc(ah, a_lbo, a_sbo), make_desc(bl, b_lbo, b_sbo), idesc, 1);
         }
         umma_commit(bar);
     }
     mbar_wait(bar, 0);
     tc_fence_after();
     const int r = warp * 32 + lane;
-    for (int c0 = 0; c0 < TG; c0 += 8) {
+    for (int c0 = 0; c0 < Nn; c0 += 8) {
         float v[8];
         tmem_ld8(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
         tmem_ld_wait();
-        for (int j = 0; j < 8; ++j) D[r * TG + c0 + j] = v[j];
+        for (int j = 0; j < 8; ++j) D[r * Nn + c0 + j] = v[j];
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem_base, TG);
+    if (warp == 0) tmem_dealloc(tmem_base, 256);
 }
 
 // --------------------------------------------------------------------------------------------- host side
 size_t ffma_workspace_bytes(int64_t N, int T, int L);
-int ffma_bwd_layer(int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
-                   const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
-                   int training, void* workspace, size_t ws_bytes, cudaStream_t st);
 
 bool tc_available() { return true; }
 
-static size_t tc_pack_total(int L) {
+int ffma_ws_pointers(int64_t N, int T, int L, void* workspace, size_t ws_bytes, float** dx0, float** dx1, float** wpart,
+                     float** bpart, int* nsplit);
+int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float* gw_ih,
+                       float* gw_hh, float* gb_ih, float* gb_hh, cudaStream_t st);
+
+// tail of the workspace: forward packs of every layer, then one backward pack (rebuilt per layer)
+static size_t tc_fwd_pack_total(int L) {
     size_t tot = 0;
     for (int l = 0; l < L; ++l) tot += (pack_bytes(l == 0) + 255) & ~(size_t)255;
     return tot;
 }
+static size_t tc_pack_total(int L) { return tc_fwd_pack_total(L) + ((bwd_pack_bytes(false) + 255) & ~(size_t)255); }
 
-// workspace = [FFMA backward workspace][packed weights of every layer]
+// workspace = [dx buffers, partial gradients (layout shared with the CUDA-core engine)][packed weights]
 size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L) {
     (void)mode; (void)F; (void)H;
     return ((ffma_workspace_bytes(N, T, L) + 255) & ~(size_t)255) + tc_pack_total(L);
@@ -493,26 +986,82 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
     return B200_OK;
 }
 
+template <int NSPLIT, bool LAYER0, int XB, int DB>
+static int launch_bwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, const float* h_st, const float* c_st,
+                      const float* d_out, const float* dhT, float* d_in, float* wpart, float* bpart, int layer, bool drop,
+                      uint64_t seed, float p, int grid, cudaStream_t st) {
+    using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
+    auto kern = lstm_tc_bwd_kernel<NSPLIT, LAYER0, XB, DB>;
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
+    {
+        TimedLaunch _t("lstm_tc_bwd_kernel", st);
+        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, drop, seed, p);
+    }
+    B200_LAUNCH_CHECK("lstm_tc_bwd_kernel");
+    return B200_OK;
+}
+
 int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
                  const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
                  int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
-    (void)mode;
-    // backward currently runs on the fp32 CUDA-core engine (same stash format); reserve the packed-weight tail
+    if (H != TH) { set_error("tcgen05 engine supports hidden=64 only, got %d", H); return B200_ERR_UNSUPPORTED; }
     const size_t tail = tc_pack_total(L);
-    const size_t usable = ws_bytes > tail ? (ws_bytes - tail) & ~(size_t)255 : 0;
-    return ffma_bwd_layer(layer, params, F, H, L, x, N, T, stash_h, stash_c, dhT, grads, p, seed, training, workspace, usable, st);
+    B200_CHECK_ARG(ws_bytes > tail, "lstm_bwd (tcgen05): workspace too small");
+    const size_t usable = (ws_bytes - tail) & ~(size_t)255;
+    float *dx0, *dx1, *wpart, *bpart;
+    int nsplit;
+    int rc = ffma_ws_pointers(N, T, L, workspace, usable, &dx0, &dx1, &wpart, &bpart, &nsplit);
+    if (rc) return rc;
+    float* dx[2] = {dx0, dx1};
+    uint8_t* pk = (uint8_t*)workspace + usable + tc_fwd_pack_total(L);
+    const bool layer0 = layer == 0;
+    const int kin = layer0 ? F : TH;
+    const float* base = params + b200_param_offset(F, TH, L, layer);
+    const float* w_ih = base;
+    const float* w_hh = w_ih + (int64_t)TG * kin;
+    const float* b_ih = w_hh + (int64_t)TG * TH;
+    const float* b_hh = b_ih + TG;
+    { TimedLaunch _t("tc_pack_bwd_weights_kernel", st); tc_pack_bwd_weights_kernel<<<32, 256, 0, st>>>(w_ih, w_hh, b_ih, b_hh, kin, kx_of(layer0), pk); }
+    B200_LAUNCH_CHECK("tc_pack_bwd_weights_kernel");
+    const bool drop = training && p > 0.f;
+    const int64_t lsz = (int64_t)T * N * TH;
+    const float* xin = layer0 ? x : stash_h + (layer - 1) * lsz;
+    const float* h_st = stash_h + layer * lsz;
+    const float* c_st = stash_c + layer * lsz;
+    const float* d_out = layer == L - 1 ? nullptr : dx[(layer + 1) & 1];
+    float* d_in = layer0 ? nullptr : dx[layer & 1];
+    const int64_t ntiles = (N + TM - 1) / TM;
+    const int grid = (int)(ntiles < nsplit ? ntiles : nsplit);
+    const bool precise = mode == B200_MODE_TC_PRECISE;
+    if (layer0)
+        rc = precise ? launch_bwd<2, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, false, seed, p, grid, st)
+                     : launch_bwd<1, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, false, seed, p, grid, st);
+    else
+        rc = precise ? launch_bwd<2, false, 1, 1>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, drop, seed, p, grid, st)
+                     : launch_bwd<1, false, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, drop, seed, p, grid, st);
+    if (rc) return rc;
+    float* gbase = grads + b200_param_offset(F, TH, L, layer);
+    float* gw_ih = gbase;
+    float* gw_hh = gw_ih + (int64_t)TG * kin;
+    float* gb_ih = gw_hh + (int64_t)TG * TH;
+    float* gb_hh = gb_ih + TG;
+    return launch_grad_reduce(wpart, grid, bpart, grid * 4, kin, kx_of(layer0), gw_ih, gw_hh, gb_ih, gb_hh, st);
 }
 
 }  // namespace b200
 
 using namespace b200;
 
-// D[128][256] = A[128][K] * B[256][K]^T through the tcgen05 path (bf16x3 split); K multiple of 16, K <= 64.
-extern "C" int b200_tc_selftest(const float* A, const float* B, int K, float* D, void* stream) {
-    B200_CHECK_ARG(A && B && D && K >= 16 && K <= 64 && K % 16 == 0, "tc_selftest: bad arguments");
-    const size_t smem = 2 * (size_t)op_bytes(TM, K) + 2 * (size_t)op_bytes(TG, K) + 64 + 128;
+// see tc_selftest_kernel; fp32 in/out, bf16x3 split inside
+extern "C" int b200_tc_selftest(const float* A, const float* B, int variant, int K, int Nn, float* D, void* stream) {
+    B200_CHECK_ARG(A && B && D && variant >= 0 && variant <= 2, "tc_selftest: bad arguments");
+    B200_CHECK_ARG(K >= 16 && K <= 256 && K % 16 == 0 && Nn >= 16 && Nn <= 256 && Nn % 16 == 0, "tc_selftest: bad K/N");
+    const int a_rows = variant == 2 ? K : TM, a_cols = variant == 2 ? TM : K;
+    const int b_rows = variant == 0 ? Nn : K, b_cols = variant == 0 ? K : Nn;
+    const size_t smem = 2 * (size_t)op_bytes(a_rows, a_cols) + 2 * (size_t)op_bytes(b_rows, b_cols) + 64 + 128;
+    B200_CHECK_ARG(smem <= 220 * 1024, "tc_selftest: operands do not fit shared memory");
     B200_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, K, D);
+    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, variant, K, Nn, D);
     B200_LAUNCH_CHECK("tc_selftest_kernel");
     return B200_OK;
 }

@@ -177,17 +177,24 @@ def test_clip_and_adam_vs_torch(count, clip):
     assert float(dp[count:].abs().sum()) == 0.0
 
 
-@pytest.mark.parametrize("K", [16, 64])
-def test_tcgen05_gemm_selftest(K):
-    """UMMA descriptors / instruction descriptor / TMEM load mapping: a 128x256xK product with the bf16x3 split
-    must agree with the fp32 product to ~1e-5 relative."""
+@pytest.mark.parametrize("variant,K,N", [(0, 16, 256), (0, 64, 256), (0, 128, 128), (1, 64, 128), (1, 256, 64),
+                                         (1, 128, 128), (2, 128, 64), (2, 128, 256), (2, 64, 128)])
+def test_tcgen05_gemm_selftest(variant, K, N):
+    """UMMA descriptors (K-major and MN-major reads of the interleaved image), instruction descriptor and the
+    TMEM load mapping: a 128xNxK product with the bf16x3 split must agree with the fp64 product to ~1e-5."""
     lib = load()
-    g = torch.Generator().manual_seed(K)
-    A = torch.randn(128, K, generator=g)
-    Bm = torch.randn(256, K, generator=g) * 0.125
-    D = torch.zeros(128, 256, device=DEV)
+    g = torch.Generator().manual_seed(variant * 1000 + K + N)
+    if variant == 0:
+        A, Bm = torch.randn(128, K, generator=g), torch.randn(N, K, generator=g) * 0.125
+        want = A.double() @ Bm.double().T
+    elif variant == 1:
+        A, Bm = torch.randn(128, K, generator=g), torch.randn(K, N, generator=g) * 0.125
+        want = A.double() @ Bm.double()
+    else:
+        A, Bm = torch.randn(K, 128, generator=g), torch.randn(K, N, generator=g) * 0.125
+        want = A.double().T @ Bm.double()
+    D = torch.zeros(128, N, device=DEV)
     dA, dB = A.to(DEV), Bm.to(DEV)          # keep the device tensors alive across the call
-    check(lib.b200_tc_selftest(ptr(dA), ptr(dB), K, ptr(D), None), "tc_selftest")
+    check(lib.b200_tc_selftest(ptr(dA), ptr(dB), variant, K, N, ptr(D), None), "tc_selftest")
     torch.cuda.synchronize()
-    want = (A.double() @ Bm.double().T).numpy()
-    assert rel_err(D.cpu().numpy(), want) < 2e-5
+    assert rel_err(D.cpu().numpy(), want.numpy()) < 2e-5

@@ -78,9 +78,13 @@ def test_training_steps_vs_reference_golden(engine, kind, data, golden_dir):
         assert float(losses[2]) == pytest.approx(float(g["losses"][s]), rel=LOSS_RTOL)
         if s == 0:
             assert float(torch.sqrt(e.sqnorm)) == pytest.approx(float(g["gnorm0"]), rel=GRAD_RTOL)
-    # Adam normalises the gradient, so a parameter whose gradient is ~0 may move by a different fraction of
-    # lr = 1e-4 per step; 3 steps move a parameter by at most 3e-4
-    np.testing.assert_allclose(e.params[: e.P].cpu().numpy(), g["final"], rtol=0, atol=2e-6 if engine == "ffma" else 2e-5)
+    # Adam divides by sqrt(v): a parameter whose gradient is ~0 turns a 1e-7 gradient difference into a different
+    # fraction of the lr = 1e-4 step, so the bound is on the bulk (99.9% within 2e-6) plus a cap far below 3 * lr
+    diff = np.abs(e.params[: e.P].cpu().numpy() - g["final"])
+    if engine == "ffma":
+        assert diff.max() < 2e-6
+    else:
+        assert np.mean(diff > 2e-6) < 1e-3 and diff.max() < 1e-4
     # validation / test semantics (batch of one window each)
     vb = B.DeviceBatch.from_reference(ref_batch(data, 4, 6), DEV)
     for w in (0, 1):
