@@ -268,9 +268,13 @@ def main():
     ap.add_argument("--batch", type=int, default=4096, help="windows per GPU per step")
     ap.add_argument("--cpu-batch", type=int, default=64, help="windows per step of the CPU sample")
     ap.add_argument("--cpu-steps", type=int, default=6)
+    ap.add_argument("--dropout", type=float, default=None, help="override the model's inter-layer dropout (diagnostics)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.dropout is not None:
+        h, l, _ = MODELS[args.model]
+        MODELS[args.model] = (h, l, args.dropout)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -21,12 +21,17 @@
 //
 // The stash format is the same transparent fp32 [L][T][N][H] as the CUDA-core engine, so backward can
 // run on either engine.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
 namespace b200 {
 
 using namespace tc;
+
+// tuning switches (host sets them from the environment once; 1 = on)
+__constant__ int c_tc_prefetch = 1;
 
 constexpr int TH = 64;              // hidden size of this engine
 constexpr int TG = 4 * TH;          // gate columns = UMMA N
@@ -91,10 +96,81 @@ tc_pack_weights_kernel(const float* __restrict__ w_ih, const float* __restrict__
         *reinterpret_cast<__nv_bfloat16*>(whh_hi + o) = h;
         *reinterpret_cast<__nv_bfloat16*>(whh_lo + o) = l;
     }
-    for (int j = tid; j < TG; j += nthr) {
+    for (int j = tid; j < TG; j += nthr) {          // stored [unit][gate] so that one 16-byte load fetches a unit's four biases
         const float b = b_ih[j] + b_hh[j];
-        const int gate = j / TH;
-        biasp[j] = gate == 2 ? 2.0f * LOG2E * b : -LOG2E * b;
+        const int gate = j / TH, u = j % TH;
+        biasp[u * 4 + gate] = gate == 2 ? 2.0f * LOG2E * b : -LOG2E * b;
+    }
+}
+
+// --------------------------------------------------------------------------------------------- loader helpers
+// Inter-layer dropout keep bits: bit u of bits[t * N + row] = keep(unit u) for the input of one layer; built once
+// per step by tc_dropout_bits_kernel (same Philox blocks as b200_dropout_mask) so that the loaders and the dx
+// epilogue read 8 bytes per (row, step) instead of re-running Philox.
+__global__ void __launch_bounds__(256)
+tc_dropout_bits_kernel(uint64_t seed, int layer, int64_t N, int T, uint32_t thr, uint64_t* __restrict__ bits) {
+    const int64_t total = (int64_t)T * N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i % N;
+        const int t = (int)(i / N);
+        uint64_t m = 0;
+#pragma unroll
+        for (int ub = 0; ub < TH / 8; ++ub) {
+            const U4 b = dropout_block(seed, layer, row, t, ub);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m |= (uint64_t)(dropout_lane16(b, j) >= thr ? 1u : 0u) << (ub * 8 + j);
+        }
+        bits[i] = m;
+    }
+}
+
+// A loader warp (lw = 0,1) owns 8 of the 16 row groups of a [128 x 64] fp32 tile; lane = (row in group, quarter q):
+// element block (rgi, i) is the float4 at row (lw*8 + rgi)*8 + lane/4, columns 4q + 16i .. +3.
+// tile_load issues all 32 loads first (one latency per tile), tile_store converts and writes the operand image.
+__device__ __forceinline__ void tile_load(float4 (&v)[8][4], const float* __restrict__ tile_base, int64_t rows_live, int lw, int lane) {
+    const int rr = lane >> 2, q = lane & 3;
+#pragma unroll
+    for (int rgi = 0; rgi < 8; ++rgi) {
+        const int r = (lw * 8 + rgi) * 8 + rr;
+        const float* src = tile_base + (int64_t)r * TH + 4 * q;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[rgi][i] = r < rows_live ? *reinterpret_cast<const float4*>(src + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+__device__ __forceinline__ void tile_load_bits(uint64_t (&m)[8], const uint64_t* __restrict__ bits_base, int64_t rows_live, int lw, int lane) {
+    const int rr = lane >> 2;
+#pragma unroll
+    for (int rgi = 0; rgi < 8; ++rgi) {
+        const int r = (lw * 8 + rgi) * 8 + rr;
+        m[rgi] = r < rows_live ? bits_base[r] : 0ull;
+    }
+}
+template <int NSPLIT>
+__device__ __forceinline__ void tile_store(const float4 (&v)[8][4], uint8_t* img_hi, uint8_t* img_lo, uint32_t sbo, int kcol0,
+                                           int lw, int lane, bool drop, const uint64_t (&m)[8], float inv_keep) {
+    const int rr = lane >> 2, q = lane & 3;
+#pragma unroll
+    for (int rgi = 0; rgi < 8; ++rgi) {
+        const int rg = lw * 8 + rgi;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int k = 4 * q + 16 * i;
+            float4 x = v[rgi][i];
+            if (drop) {
+                const uint32_t b = (uint32_t)(m[rgi] >> k) & 0xFu;
+                x.x = (b & 1u) ? x.x * inv_keep : 0.f;
+                x.y = (b & 2u) ? x.y * inv_keep : 0.f;
+                x.z = (b & 4u) ? x.z * inv_keep : 0.f;
+                x.w = (b & 8u) ? x.w * inv_keep : 0.f;
+            }
+            uint2 hi2, lo2;
+            split2(x.x, x.y, hi2.x, lo2.x);
+            split2(x.z, x.w, hi2.y, lo2.y);
+            const int kc = kcol0 + k;
+            const uint32_t o = (uint32_t)rg * sbo + (uint32_t)(kc >> 3) * LBO_BYTES + (uint32_t)rr * 16 + (uint32_t)(kc & 7) * 2;
+            *reinterpret_cast<uint2*>(img_hi + o) = hi2;
+            if (NSPLIT == 2) *reinterpret_cast<uint2*>(img_lo + o) = lo2;
+        }
     }
 }
 
@@ -118,7 +194,7 @@ struct FwdSmem {
 template <int NSPLIT, int NTILE, bool LAYER0>
 __global__ void __launch_bounds__(32 * (4 * NTILE + LOADER_WARPS + 1), 1)
 lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
-                   float* __restrict__ h_out, float* __restrict__ c_out, int layer, bool drop, uint64_t seed, float p) {
+                   float* __restrict__ h_out, float* __restrict__ c_out, const uint64_t* __restrict__ drop_bits, float p) {
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     constexpr int KX = S::KX;
     constexpr int EPI_WARPS = 4 * NTILE;
@@ -193,24 +269,45 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     tmem_ld8(taddr + 2 * TH + uc * 8, ag);
                     tmem_ld8(taddr + 3 * TH + uc * 8, ao);
                     tmem_ld_wait();
-                    float hv[8], cv[8];
+                    // E_i = 2^(-log2e a_i - log2e b_i) etc. (bias folded into bias_s); with D = 1 + E:
+                    //   c = f c' + i g = [c' D_i D_g + (E_g - 1) D_f] / (D_f D_i D_g),  h = o tanh(c) = (E_c - 1) / (D_o (E_c + 1))
+                    // -> 5 ex2 + 2 rcp per hidden unit.  Written stage by stage over the 8 units of the chunk so that
+                    // every MUFU / FMA stage issues 8..32 independent instructions back to back.
+                    float hv[8], cv[8], num[8], den[8], Do[8];
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        const int u = uc * 8 + j;
-                        // sigma(x) = 1/(1 + 2^(-log2e x)),  tanh(x) = 1 - 2/(1 + 2^(2 log2e x)); bias folded into bias_s
-                        const float ei = exp2f(fmaf(ai[j], -LOG2E, bias_s[0 * TH + u]));
-                        const float ef = exp2f(fmaf(af[j], -LOG2E, bias_s[1 * TH + u]));
-                        const float eg = exp2f(fmaf(ag[j], 2.f * LOG2E, bias_s[2 * TH + u]));
-                        const float eo = exp2f(fmaf(ao[j], -LOG2E, bias_s[3 * TH + u]));
-                        const float ig = __fdividef(1.f, 1.f + ei), fg = __fdividef(1.f, 1.f + ef);
-                        const float gg = 1.f - __fdividef(2.f, 1.f + eg), og = __fdividef(1.f, 1.f + eo);
-                        const float c = fmaf(fg, cst[u], ig * gg);
-                        const float ec = exp2f(2.f * LOG2E * c);
-                        const float h = og * (1.f - __fdividef(2.f, 1.f + ec));
-                        cst[u] = c;
-                        hv[j] = h;
-                        cv[j] = c;
+                        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (uc * 8 + j));
+                        ai[j] = fminf(fmaf(ai[j], -LOG2E, b4.x), EXP_CLAMP);
+                        af[j] = fminf(fmaf(af[j], -LOG2E, b4.y), EXP_CLAMP);
+                        ag[j] = fminf(fmaf(ag[j], 2.f * LOG2E, b4.z), EXP_CLAMP);
+                        ao[j] = fminf(fmaf(ao[j], -LOG2E, b4.w), EXP_CLAMP);
                     }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { ai[j] = ex2a(ai[j]); af[j] = ex2a(af[j]); ag[j] = ex2a(ag[j]); ao[j] = ex2a(ao[j]); }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float Di = 1.f + ai[j], Df = 1.f + af[j], Dg = 1.f + ag[j];
+                        const float DiDg = Di * Dg;
+                        Do[j] = 1.f + ao[j];
+                        num[j] = fmaf(cst[uc * 8 + j], DiDg, (ag[j] - 1.f) * Df);
+                        den[j] = Df * DiDg;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) den[j] = rcpa(den[j]);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        cv[j] = num[j] * den[j];
+                        cst[uc * 8 + j] = cv[j];
+                        num[j] = fminf(2.f * LOG2E * cv[j], EXP_CLAMP);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) num[j] = ex2a(num[j]);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) den[j] = Do[j] * (num[j] + 1.f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) den[j] = rcpa(den[j]);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) hv[j] = (num[j] - 1.f) * den[j];
                     uint4 hi4, lo4;
                     split2(hv[0], hv[1], hi4.x, lo4.x);
                     split2(hv[2], hv[3], hi4.y, lo4.y);
@@ -232,17 +329,36 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     } else if (warp < EPI_WARPS + LOADER_WARPS) {
         // ================================ loader: x_t operand of every slot ==================================
         const int lw = warp - EPI_WARPS;
-        const uint32_t thr = dropout_threshold(p);
+        const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
         int64_t g = 0;
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             for (int t = 0; t < T; ++t, ++g) {
+                if (c_tc_prefetch && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
+                    // next step's input rows of both slots -> L2 (the tiles of a group are consecutive)
+                    const int64_t r0 = grp * NTILE * TM;
+                    if (r0 < N) {
+                        const int64_t nrow = (N - r0) < NTILE * TM ? (N - r0) : NTILE * TM;
+                        prefetch_l2(xin + ((int64_t)(t + 1) * N + r0) * TH, (uint32_t)nrow * TH * 4);
+                    }
+                }
 #pragma unroll
                 for (int slot = 0; slot < NTILE; ++slot) {
                     const int64_t tile = grp * NTILE + slot;
                     uint8_t* x_hi = smem + S::off_x + (slot * NSPLIT) * S::XB;
                     uint8_t* x_lo = x_hi + S::XB;
-                    if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));   // MMA of the previous step consumed x
+                    if (!LAYER0) {
+                        // all global loads of the tile are issued before the wait for the x buffer
+                        const int64_t r0 = tile * TM;
+                        const int64_t rows_live = tile < ntiles ? N - r0 : 0;
+                        float4 v[8][4];
+                        uint64_t m[8];
+                        tile_load(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw, lane);
+                        if (drop) tile_load_bits(m, drop_bits + (int64_t)t * N + r0, rows_live, lw, lane);
+                        if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));   // MMA of the previous step consumed x
+                        tile_store<NSPLIT>(v, x_hi, x_lo, sbo_of(KX), 0, lw, lane, drop, m, inv_keep);
+                    }
+                    if (LAYER0 && g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));
                     if (LAYER0) {
                         // 128 rows x [x0..x_{kin-1}, 0...]: lane handles rows lw*64 + lane and +32
 #pragma unroll
@@ -268,37 +384,6 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                             if (NSPLIT == 2) {
                                 *reinterpret_cast<uint4*>(x_lo + ro) = lo4;
                                 *reinterpret_cast<uint4*>(x_lo + ro + LBO_BYTES) = z;
-                            }
-                        }
-                    } else {
-                        // 16 row groups of 8 rows; this warp takes 8 of them.  lane = (row in group, quarter)
-                        const int rg_r = lane >> 2, q = lane & 3;
-#pragma unroll 2
-                        for (int rgi = 0; rgi < 8; ++rgi) {
-                            const int rg = lw * 8 + rgi;
-                            const int r = rg * 8 + rg_r;
-                            const int64_t row = tile * TM + r;
-                            const bool live = tile < ntiles && row < N;
-                            const float* src = xin + ((int64_t)t * N + row) * TH;
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const int k = 4 * q + 16 * i;
-                                float4 v = live ? *reinterpret_cast<const float4*>(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-                                if (drop) {
-                                    U4 b = dropout_block(seed, layer, row, t, k >> 3);
-                                    const int j0 = k & 7;
-                                    v.x = dropout_lane16(b, j0 + 0) >= thr ? v.x * inv_keep : 0.f;
-                                    v.y = dropout_lane16(b, j0 + 1) >= thr ? v.y * inv_keep : 0.f;
-                                    v.z = dropout_lane16(b, j0 + 2) >= thr ? v.z * inv_keep : 0.f;
-                                    v.w = dropout_lane16(b, j0 + 3) >= thr ? v.w * inv_keep : 0.f;
-                                }
-                                uint2 hi2, lo2;
-                                split2(v.x, v.y, hi2.x, lo2.x);
-                                split2(v.z, v.w, hi2.y, lo2.y);
-                                const uint32_t o = (uint32_t)rg * sbo_of(KX) + (uint32_t)(k >> 3) * LBO_BYTES + (uint32_t)rg_r * 16 +
-                                                   (uint32_t)(k & 7) * 2;
-                                *reinterpret_cast<uint2*>(x_hi + o) = hi2;
-                                if (NSPLIT == 2) *reinterpret_cast<uint2*>(x_lo + o) = lo2;
                             }
                         }
                     }
@@ -408,9 +493,10 @@ tc_pack_bwd_weights_kernel(const float* __restrict__ w_ih, const float* __restri
         *reinterpret_cast<__nv_bfloat16*>(w_hi + o) = h;
         *reinterpret_cast<__nv_bfloat16*>(w_lo + o) = l;
     }
-    for (int j = tid; j < TG; j += nthr) {
+    for (int j = tid; j < TG; j += nthr) {          // [unit][gate]
         const float b = b_ih[j] + b_hh[j];
-        biasp[j] = (j / TH) == 2 ? 2.0f * LOG2E * b : -LOG2E * b;
+        const int gate = j / TH, u = j % TH;
+        biasp[u * 4 + gate] = gate == 2 ? 2.0f * LOG2E * b : -LOG2E * b;
     }
 }
 
@@ -457,7 +543,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
 lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
                    const float* __restrict__ h_st, const float* __restrict__ c_st, const float* __restrict__ d_out,
                    const float* __restrict__ dhT, float* __restrict__ d_in, float* __restrict__ wpart,
-                   float* __restrict__ bpart, int layer, bool drop, uint64_t seed, float p) {
+                   float* __restrict__ bpart, const uint64_t* __restrict__ drop_bits, float p) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     constexpr int KX = S::KX, KC = S::KC;
     constexpr uint32_t SBO_W = sbo_of(KC), SBO_DA = sbo_of(64);
@@ -509,7 +595,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const int r = wq * 32 + lane;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(wq * 32) << 16);
         const uint32_t row_off = (uint32_t)(r >> 3) * SBO_DA + (uint32_t)(r & 7) * 16;
-        const uint32_t thr = dropout_threshold(p);
+        const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
         float dc[4][8], dh[4][8], db[4];
 #pragma unroll
@@ -549,17 +635,36 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         __syncwarp();
                         if (lane == 0) mbar_arrive(a_free);
                     }
-                    float da[32];
+                    // gates and tanh(c_t) from 5 ex2 + 2 rcp per unit (batch inversion of (D_i, D_f, D_g) and of (D_o, D_c)),
+                    // written stage by stage over the 8 units so that each MUFU / FMA stage is 8..40 independent instructions
+                    float da[32], Ec[8], r1[8], r2[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const int u = u0 + i;
-                        const float ei = exp2f(fmaf(av[0][i], -LOG2E, bias_s[0 * TH + u]));
-                        const float ef = exp2f(fmaf(av[1][i], -LOG2E, bias_s[1 * TH + u]));
-                        const float eg = exp2f(fmaf(av[2][i], 2.f * LOG2E, bias_s[2 * TH + u]));
-                        const float eo = exp2f(fmaf(av[3][i], -LOG2E, bias_s[3 * TH + u]));
-                        const float ig = __fdividef(1.f, 1.f + ei), fg = __fdividef(1.f, 1.f + ef);
-                        const float gg = 1.f - __fdividef(2.f, 1.f + eg), og = __fdividef(1.f, 1.f + eo);
-                        const float tc = 1.f - __fdividef(2.f, 1.f + exp2f(2.f * LOG2E * ct[i]));
+                        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (u0 + i));
+                        av[0][i] = fminf(fmaf(av[0][i], -LOG2E, b4.x), EXP_CLAMP);
+                        av[1][i] = fminf(fmaf(av[1][i], -LOG2E, b4.y), EXP_CLAMP);
+                        av[2][i] = fminf(fmaf(av[2][i], 2.f * LOG2E, b4.z), EXP_CLAMP);
+                        av[3][i] = fminf(fmaf(av[3][i], -LOG2E, b4.w), EXP_CLAMP);
+                        Ec[i] = fminf(2.f * LOG2E * ct[i], EXP_CLAMP);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        av[0][i] = ex2a(av[0][i]); av[1][i] = ex2a(av[1][i]); av[2][i] = ex2a(av[2][i]); av[3][i] = ex2a(av[3][i]);
+                        Ec[i] = ex2a(Ec[i]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        r1[i] = (1.f + av[0][i]) * (1.f + av[1][i]) * (1.f + av[2][i]);
+                        r2[i] = (1.f + av[3][i]) * (1.f + Ec[i]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { r1[i] = rcpa(r1[i]); r2[i] = rcpa(r2[i]); }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float Di = 1.f + av[0][i], Df = 1.f + av[1][i], Dg = 1.f + av[2][i], Do = 1.f + av[3][i], Dc = 1.f + Ec[i];
+                        const float t1 = r1[i] * Dg;
+                        const float ig = t1 * Df, fg = t1 * Di, gg = (av[2][i] - 1.f) * (r1[i] * (Di * Df));
+                        const float og = r2[i] * Dc, tc = (Ec[i] - 1.f) * (r2[i] * Do);
                         const float dhv = dh[q][i] + dq[i];
                         const float d_o = dhv * tc;
                         const float dcc = dc[q][i] + dhv * og * (1.f - tc * tc);
@@ -606,13 +711,13 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     for (int c = 0; c < 4; ++c) tmem_ld8(lane_addr + TMEM_D + 32 * grp + 8 * c, dx[c]);
                     tmem_ld_wait();
                     if (live) {
+                        const uint32_t mb = drop ? (uint32_t)(drop_bits[(int64_t)t * N + row] >> (32 * grp)) : 0xFFFFFFFFu;
 #pragma unroll
                         for (int c = 0; c < 4; ++c) {
                             const int u = 32 * grp + 8 * c;
                             if (drop) {
-                                U4 b = dropout_block(seed, layer, row, t, u >> 3);
 #pragma unroll
-                                for (int i = 0; i < 8; ++i) dx[c][i] = dropout_lane16(b, i) >= thr ? dx[c][i] * inv_keep : 0.f;
+                                for (int i = 0; i < 8; ++i) dx[c][i] = ((mb >> (8 * c + i)) & 1u) ? dx[c][i] * inv_keep : 0.f;
                             }
                             st_global_v8(d_in + ((int64_t)t * N + row) * TH + u, dx[c]);
                         }
@@ -652,77 +757,66 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     } else if (warp < BW_EPI_WARPS + LOADER_WARPS) {
         // ===================================== loader warps =======================================================
         const int lw = warp - BW_EPI_WARPS;
-        const uint32_t thr = dropout_threshold(p);
+        const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
         const int rg_r = lane >> 2, qq = lane & 3;
         int64_t g = 0;
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int64_t r0 = tile * TM;
+            const int64_t rows_live = N - r0;
             for (int t = T - 1; t >= 0; --t, ++g) {
+                if (c_tc_prefetch && lw == 0 && lane == 0 && t >= 1) {
+                    // pull the NEXT step's rows (x_{t-1}, h_{t-2}, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
+                    const int64_t nrow = rows_live < TM ? rows_live : TM;
+                    const uint32_t rb = (uint32_t)nrow * TH * 4;
+                    if (!LAYER0) prefetch_l2(xin + ((int64_t)(t - 1) * N + r0) * TH, rb);
+                    if (t >= 2) {
+                        prefetch_l2(h_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
+                        prefetch_l2(c_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
+                    }
+                    if (d_out) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
+                }
                 const int buf = (int)(g % XB);
-                if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
-#pragma unroll 2
-                for (int rgi = 0; rgi < 8; ++rgi) {
-                    const int rg = lw * 8 + rgi;
-                    const int rr = rg * 8 + rg_r;
-                    const int64_t row = tile * TM + rr;
-                    const bool live = row < N;
-                    const uint32_t base_o = (uint32_t)rg * SBO_W + (uint32_t)rg_r * 16;
-                    // ---- x part ----
-                    if (LAYER0) {
-                        // 16 columns: lane quarter qq covers columns 4qq .. 4qq+3
-                        float v[4] = {0.f, 0.f, 0.f, 0.f};
-                        if (live) {
-                            const float* src = xin + ((int64_t)t * N + row) * kin;
+                uint64_t m[8];
+                float4 v[8][4];
+                // first half of the image: the loads are in flight while we wait for the buffer
+                if (LAYER0) {
+                    // h_{t-1} part
+                    if (t > 0) tile_load(v, h_st + ((int64_t)(t - 1) * N + r0) * TH, rows_live, lw, lane);
+                    else tile_load(v, h_st, 0, lw, lane);
+                } else {
+                    tile_load(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw, lane);
+                    if (drop) tile_load_bits(m, drop_bits + (int64_t)t * N + r0, rows_live, lw, lane);
+                }
+                if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
+                if (LAYER0) {
+                    tile_store<NSPLIT>(v, xh_hi, xh_lo, SBO_W, KX, lw, lane, false, m, 1.f);
+                    // x part: 16 columns, lane quarter qq covers columns 4qq .. 4qq+3 of its row
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) if (4 * qq + i < kin) v[i] = src[4 * qq + i];
+                    for (int rgi = 0; rgi < 8; ++rgi) {
+                        const int rg = lw * 8 + rgi;
+                        const int rr = rg * 8 + rg_r;
+                        float x4[4] = {0.f, 0.f, 0.f, 0.f};
+                        if (rr < rows_live) {
+                            const float* src = xin + ((int64_t)t * N + r0 + rr) * kin;
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) if (4 * qq + i < kin) x4[i] = src[4 * qq + i];
                         }
                         uint2 hi2, lo2;
-                        split2(v[0], v[1], hi2.x, lo2.x);
-                        split2(v[2], v[3], hi2.y, lo2.y);
+                        split2(x4[0], x4[1], hi2.x, lo2.x);
+                        split2(x4[2], x4[3], hi2.y, lo2.y);
                         const int k = 4 * qq;
-                        const uint32_t o = base_o + (uint32_t)(k >> 3) * LBO_BYTES + (uint32_t)(k & 7) * 2;
+                        const uint32_t o = (uint32_t)rg * SBO_W + (uint32_t)(k >> 3) * LBO_BYTES + (uint32_t)rg_r * 16 + (uint32_t)(k & 7) * 2;
                         *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
                         if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
-                    } else {
-                        const float* src = xin + ((int64_t)t * N + row) * TH;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const int k = 4 * qq + 16 * i;
-                            float4 v = live ? *reinterpret_cast<const float4*>(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (drop) {
-                                U4 b = dropout_block(seed, layer, row, t, k >> 3);
-                                const int j0 = k & 7;
-                                v.x = dropout_lane16(b, j0 + 0) >= thr ? v.x * inv_keep : 0.f;
-                                v.y = dropout_lane16(b, j0 + 1) >= thr ? v.y * inv_keep : 0.f;
-                                v.z = dropout_lane16(b, j0 + 2) >= thr ? v.z * inv_keep : 0.f;
-                                v.w = dropout_lane16(b, j0 + 3) >= thr ? v.w * inv_keep : 0.f;
-                            }
-                            uint2 hi2, lo2;
-                            split2(v.x, v.y, hi2.x, lo2.x);
-                            split2(v.z, v.w, hi2.y, lo2.y);
-                            const uint32_t o = base_o + (uint32_t)(k >> 3) * LBO_BYTES + (uint32_t)(k & 7) * 2;
-                            *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
-                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
-                        }
                     }
-                    // ---- h_{t-1} part ----
-                    {
-                        const float* src = h_st + ((int64_t)(t - 1) * N + row) * TH;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const int k = 4 * qq + 16 * i;
-                            float4 v = (live && t > 0) ? *reinterpret_cast<const float4*>(src + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-                            uint2 hi2, lo2;
-                            split2(v.x, v.y, hi2.x, lo2.x);
-                            split2(v.z, v.w, hi2.y, lo2.y);
-                            const int kc = KX + k;
-                            const uint32_t o = base_o + (uint32_t)(kc >> 3) * LBO_BYTES + (uint32_t)(kc & 7) * 2;
-                            *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
-                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
-                        }
-                    }
+                } else {
+                    tile_store<NSPLIT>(v, xh_hi, xh_lo, SBO_W, 0, lw, lane, drop, m, inv_keep);
+                    if (t > 0) tile_load(v, h_st + ((int64_t)(t - 1) * N + r0) * TH, rows_live, lw, lane);
+                    else tile_load(v, h_st, 0, lw, lane);
+                    tile_store<NSPLIT>(v, xh_hi, xh_lo, SBO_W, KX, lw, lane, false, m, 1.f);
                 }
                 fence_proxy_async();
                 __syncwarp();
@@ -913,6 +1007,14 @@ size_t ffma_workspace_bytes(int64_t N, int T, int L);
 
 bool tc_available() { return true; }
 
+static void tc_apply_env() {
+    static bool done = false;
+    if (done) return;
+    done = true;
+    const char* e = getenv("B200_TC_PREFETCH");
+    if (e) { int v = atoi(e); cudaMemcpyToSymbol(c_tc_prefetch, &v, sizeof(int)); }
+}
+
 int ffma_ws_pointers(int64_t N, int T, int L, void* workspace, size_t ws_bytes, float** dx0, float** dx1, float** wpart,
                      float** bpart, int* nsplit);
 int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float* gw_ih,
@@ -924,17 +1026,38 @@ static size_t tc_fwd_pack_total(int L) {
     for (int l = 0; l < L; ++l) tot += (pack_bytes(l == 0) + 255) & ~(size_t)255;
     return tot;
 }
-static size_t tc_pack_total(int L) { return tc_fwd_pack_total(L) + ((bwd_pack_bytes(false) + 255) & ~(size_t)255); }
+static size_t tc_bits_bytes(int64_t N, int T) { return ((size_t)T * N * 8 + 255) & ~(size_t)255; }
+// tail of the workspace: dropout keep bits of layers 1..L-1, forward packs, one backward pack
+static size_t tc_tail_total(int64_t N, int T, int L) {
+    return (size_t)(L - 1) * tc_bits_bytes(N, T) + tc_fwd_pack_total(L) + ((bwd_pack_bytes(false) + 255) & ~(size_t)255);
+}
+struct TcTail {
+    uint64_t* bits;      // [L-1][T][N]
+    uint8_t* fwd_packs;
+    uint8_t* bwd_pack;
+    size_t usable;       // bytes in front of the tail (dx buffers, partial gradients)
+};
+static bool tc_tail(void* workspace, size_t ws_bytes, int64_t N, int T, int L, TcTail* t) {
+    const size_t tail = tc_tail_total(N, T, L);
+    if (ws_bytes <= tail + 256) return false;
+    t->usable = (ws_bytes - tail) & ~(size_t)255;
+    uint8_t* p = (uint8_t*)workspace + t->usable;
+    t->bits = (uint64_t*)p;
+    p += (size_t)(L - 1) * tc_bits_bytes(N, T);
+    t->fwd_packs = p;
+    t->bwd_pack = p + tc_fwd_pack_total(L);
+    return true;
+}
 
-// workspace = [dx buffers, partial gradients (layout shared with the CUDA-core engine)][packed weights]
+// workspace = [dx buffers, partial gradients (layout shared with the CUDA-core engine)][tail]
 size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L) {
     (void)mode; (void)F; (void)H;
-    return ((ffma_workspace_bytes(N, T, L) + 255) & ~(size_t)255) + tc_pack_total(L);
+    return ((ffma_workspace_bytes(N, T, L) + 255) & ~(size_t)255) + tc_tail_total(N, T, L) + 512;
 }
 
 template <int NSPLIT, int NTILE, bool LAYER0>
 static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, float* h_out, float* c_out,
-                      int layer, bool drop, uint64_t seed, float p, cudaStream_t st) {
+                      const uint64_t* drop_bits, float p, cudaStream_t st) {
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     auto kern = lstm_tc_fwd_kernel<NSPLIT, NTILE, LAYER0>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
@@ -942,8 +1065,8 @@ static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t 
     const int grid = (int)(ngroups < num_sms() ? ngroups : num_sms());
     const int threads = 32 * (4 * NTILE + LOADER_WARPS + 1);
     {
-        TimedLaunch _t("lstm_tc_fwd_kernel", st);
-        kern<<<grid, threads, S::total, st>>>(packed, xin, kin, N, T, h_out, c_out, layer, drop, seed, p);
+        TimedLaunch _t(LAYER0 ? "lstm_tc_fwd_kernel_l0" : "lstm_tc_fwd_kernel_lN", st);
+        kern<<<grid, threads, S::total, st>>>(packed, xin, kin, N, T, h_out, c_out, drop_bits, p);
     }
     B200_LAUNCH_CHECK("lstm_tc_fwd_kernel");
     return B200_OK;
@@ -952,11 +1075,11 @@ static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t 
 int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
            float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
     if (H != TH) { set_error("tcgen05 engine supports hidden=64 only, got %d", H); return B200_ERR_UNSUPPORTED; }
+    tc_apply_env();
     B200_CHECK_ARG(workspace != nullptr, "lstm_fwd (tcgen05): workspace required for the packed weights");
-    const size_t need = tc_pack_total(L);
-    B200_CHECK_ARG(ws_bytes >= need, "lstm_fwd (tcgen05): workspace too small (%zu < %zu)", ws_bytes, need);
-    // packed weights live at the END of the workspace so that the backward workspace layout is untouched
-    uint8_t* pk = (uint8_t*)workspace + ((ws_bytes - need) & ~(size_t)255);
+    TcTail tail;
+    B200_CHECK_ARG(tc_tail(workspace, ws_bytes, N, T, L, &tail), "lstm_fwd (tcgen05): workspace too small (%zu bytes)", ws_bytes);
+    uint8_t* pk = tail.fwd_packs;
     const bool drop = training && p > 0.f;
     const int64_t lsz = (int64_t)T * N * TH;
     const bool precise = mode == B200_MODE_TC_PRECISE;
@@ -972,13 +1095,20 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
         const float* xin = l == 0 ? x : stash_h + (l - 1) * lsz;
         float* ho = stash_h + l * lsz;
         float* co = stash_c + l * lsz;
+        const uint64_t* bits = nullptr;
+        if (l > 0 && drop) {
+            uint64_t* b = tail.bits + (size_t)(l - 1) * (tc_bits_bytes(N, T) / 8);
+            { TimedLaunch _t("tc_dropout_bits_kernel", st); tc_dropout_bits_kernel<<<num_sms() * 8, 256, 0, st>>>(seed, l, N, T, dropout_threshold(p), b); }
+            B200_LAUNCH_CHECK("tc_dropout_bits_kernel");
+            bits = b;
+        }
         int rc;
         if (l == 0) {
-            rc = precise ? launch_fwd<2, 2, true>(pk, xin, kin, N, T, ho, co, l, false, seed, p, st)
-                         : launch_fwd<1, 2, true>(pk, xin, kin, N, T, ho, co, l, false, seed, p, st);
+            rc = precise ? launch_fwd<2, 2, true>(pk, xin, kin, N, T, ho, co, nullptr, p, st)
+                         : launch_fwd<1, 2, true>(pk, xin, kin, N, T, ho, co, nullptr, p, st);
         } else {
-            rc = precise ? launch_fwd<2, 1, false>(pk, xin, kin, N, T, ho, co, l, drop, seed, p, st)
-                         : launch_fwd<1, 2, false>(pk, xin, kin, N, T, ho, co, l, drop, seed, p, st);
+            rc = precise ? launch_fwd<2, 1, false>(pk, xin, kin, N, T, ho, co, bits, p, st)
+                         : launch_fwd<1, 2, false>(pk, xin, kin, N, T, ho, co, bits, p, st);
         }
         if (rc) return rc;
         pk += (pack_bytes(l == 0) + 255) & ~(size_t)255;
@@ -988,14 +1118,14 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
 
 template <int NSPLIT, bool LAYER0, int XB, int DB>
 static int launch_bwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, const float* h_st, const float* c_st,
-                      const float* d_out, const float* dhT, float* d_in, float* wpart, float* bpart, int layer, bool drop,
-                      uint64_t seed, float p, int grid, cudaStream_t st) {
+                      const float* d_out, const float* dhT, float* d_in, float* wpart, float* bpart, const uint64_t* drop_bits,
+                      float p, int grid, cudaStream_t st) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     auto kern = lstm_tc_bwd_kernel<NSPLIT, LAYER0, XB, DB>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     {
-        TimedLaunch _t("lstm_tc_bwd_kernel", st);
-        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, drop, seed, p);
+        TimedLaunch _t(LAYER0 ? "lstm_tc_bwd_kernel_l0" : "lstm_tc_bwd_kernel_lN", st);
+        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, drop_bits, p);
     }
     B200_LAUNCH_CHECK("lstm_tc_bwd_kernel");
     return B200_OK;
@@ -1005,15 +1135,14 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
                  const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
                  int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
     if (H != TH) { set_error("tcgen05 engine supports hidden=64 only, got %d", H); return B200_ERR_UNSUPPORTED; }
-    const size_t tail = tc_pack_total(L);
-    B200_CHECK_ARG(ws_bytes > tail, "lstm_bwd (tcgen05): workspace too small");
-    const size_t usable = (ws_bytes - tail) & ~(size_t)255;
+    TcTail tail;
+    B200_CHECK_ARG(tc_tail(workspace, ws_bytes, N, T, L, &tail), "lstm_bwd (tcgen05): workspace too small (%zu bytes)", ws_bytes);
     float *dx0, *dx1, *wpart, *bpart;
     int nsplit;
-    int rc = ffma_ws_pointers(N, T, L, workspace, usable, &dx0, &dx1, &wpart, &bpart, &nsplit);
+    int rc = ffma_ws_pointers(N, T, L, workspace, tail.usable, &dx0, &dx1, &wpart, &bpart, &nsplit);
     if (rc) return rc;
     float* dx[2] = {dx0, dx1};
-    uint8_t* pk = (uint8_t*)workspace + usable + tc_fwd_pack_total(L);
+    uint8_t* pk = tail.bwd_pack;
     const bool layer0 = layer == 0;
     const int kin = layer0 ? F : TH;
     const float* base = params + b200_param_offset(F, TH, L, layer);
@@ -1033,12 +1162,15 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     const int64_t ntiles = (N + TM - 1) / TM;
     const int grid = (int)(ntiles < nsplit ? ntiles : nsplit);
     const bool precise = mode == B200_MODE_TC_PRECISE;
+    // keep bits of this layer's input were built by the forward pass of the same step (same workspace)
+    const uint64_t* bits = (!layer0 && drop) ? tail.bits + (size_t)(layer - 1) * (tc_bits_bytes(N, T) / 8) : nullptr;
+    (void)seed;
     if (layer0)
-        rc = precise ? launch_bwd<2, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, false, seed, p, grid, st)
-                     : launch_bwd<1, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, false, seed, p, grid, st);
+        rc = precise ? launch_bwd<2, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, grid, st)
+                     : launch_bwd<1, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, grid, st);
     else
-        rc = precise ? launch_bwd<2, false, 1, 1>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, drop, seed, p, grid, st)
-                     : launch_bwd<1, false, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, layer, drop, seed, p, grid, st);
+        rc = precise ? launch_bwd<2, false, 1, 1>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, grid, st)
+                     : launch_bwd<1, false, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, grid, st);
     if (rc) return rc;
     float* gbase = grads + b200_param_offset(F, TH, L, layer);
     float* gw_ih = gbase;

@@ -96,6 +96,18 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// ---- fast transcendental building blocks (MUFU): ex2.approx <= 2 ulp, rcp.approx <= 1 ulp ------
+__device__ __forceinline__ float ex2a(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcpa(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// Exponent arguments are clamped to 2^40 so that products of up to three (1 + 2^x) terms stay below
+// fp32 overflow; a saturated sigmoid then reads 9e-13 instead of a smaller number (absolute error < 1e-12).
+constexpr float EXP_CLAMP = 40.0f;
+
+// L2 prefetch of a contiguous global range (bytes multiple of 16), no registers, no completion tracking
+__device__ __forceinline__ void prefetch_l2(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // ---- bf16 hi/lo split ---------------------------------------------------------------------------
 // x ~= hi + lo with hi = bf16(x), lo = bf16(x - hi): |x - hi - lo| <= 2^-17 |x|
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
