@@ -124,34 +124,37 @@ tc_dropout_bits_kernel(uint64_t seed, int layer, int64_t N, int T, uint32_t thr,
     }
 }
 
-// A loader warp (lw = 0,1) owns 8 of the 16 row groups of a [128 x 64] fp32 tile; lane = (row in group, quarter q):
-// element block (rgi, i) is the float4 at row (lw*8 + rgi)*8 + lane/4, columns 4q + 16i .. +3.
-// tile_load issues all 32 loads first (one latency per tile), tile_store converts and writes the operand image.
-__device__ __forceinline__ void tile_load(float4 (&v)[8][4], const float* __restrict__ tile_base, int64_t rows_live, int lw, int lane) {
+// A loader warp handles NRG consecutive row groups (8 rows each) of a [128 x 64] fp32 tile per batch, starting at
+// row group rg0; lane = (row in group, quarter q): element block (rgi, i) is the float4 at row (rg0 + rgi)*8 + lane/4,
+// columns 4q + 16i .. +3.  tile_load issues all loads of the batch first (one latency per batch), tile_store
+// converts and writes the operand image.
+template <int NRG>
+__device__ __forceinline__ void tile_load(float4 (&v)[NRG][4], const float* __restrict__ tile_base, int64_t rows_live, int rg0, int lane) {
     const int rr = lane >> 2, q = lane & 3;
 #pragma unroll
-    for (int rgi = 0; rgi < 8; ++rgi) {
-        const int r = (lw * 8 + rgi) * 8 + rr;
+    for (int rgi = 0; rgi < NRG; ++rgi) {
+        const int r = (rg0 + rgi) * 8 + rr;
         const float* src = tile_base + (int64_t)r * TH + 4 * q;
 #pragma unroll
         for (int i = 0; i < 4; ++i) v[rgi][i] = r < rows_live ? *reinterpret_cast<const float4*>(src + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
-__device__ __forceinline__ void tile_load_bits(uint64_t (&m)[8], const uint64_t* __restrict__ bits_base, int64_t rows_live, int lw, int lane) {
+template <int NRG>
+__device__ __forceinline__ void tile_load_bits(uint64_t (&m)[NRG], const uint64_t* __restrict__ bits_base, int64_t rows_live, int rg0, int lane) {
     const int rr = lane >> 2;
 #pragma unroll
-    for (int rgi = 0; rgi < 8; ++rgi) {
-        const int r = (lw * 8 + rgi) * 8 + rr;
+    for (int rgi = 0; rgi < NRG; ++rgi) {
+        const int r = (rg0 + rgi) * 8 + rr;
         m[rgi] = r < rows_live ? bits_base[r] : 0ull;
     }
 }
-template <int NSPLIT>
-__device__ __forceinline__ void tile_store(const float4 (&v)[8][4], uint8_t* img_hi, uint8_t* img_lo, uint32_t sbo, int kcol0,
-                                           int lw, int lane, bool drop, const uint64_t (&m)[8], float inv_keep) {
+template <int NSPLIT, int NRG>
+__device__ __forceinline__ void tile_store(const float4 (&v)[NRG][4], uint8_t* img_hi, uint8_t* img_lo, uint32_t sbo, int kcol0,
+                                           int rg0, int lane, bool drop, const uint64_t (&m)[NRG], float inv_keep) {
     const int rr = lane >> 2, q = lane & 3;
 #pragma unroll
-    for (int rgi = 0; rgi < 8; ++rgi) {
-        const int rg = lw * 8 + rgi;
+    for (int rgi = 0; rgi < NRG; ++rgi) {
+        const int rg = rg0 + rgi;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int k = 4 * q + 16 * i;
@@ -353,10 +356,10 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         const int64_t rows_live = tile < ntiles ? N - r0 : 0;
                         float4 v[8][4];
                         uint64_t m[8];
-                        tile_load(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw, lane);
-                        if (drop) tile_load_bits(m, drop_bits + (int64_t)t * N + r0, rows_live, lw, lane);
+                        tile_load<8>(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw * 8, lane);
+                        if (drop) tile_load_bits<8>(m, drop_bits + (int64_t)t * N + r0, rows_live, lw * 8, lane);
                         if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));   // MMA of the previous step consumed x
-                        tile_store<NSPLIT>(v, x_hi, x_lo, sbo_of(KX), 0, lw, lane, drop, m, inv_keep);
+                        tile_store<NSPLIT, 8>(v, x_hi, x_lo, sbo_of(KX), 0, lw * 8, lane, drop, m, inv_keep);
                     }
                     if (LAYER0 && g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));
                     if (LAYER0) {
@@ -449,24 +452,29 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 //
 // One tile (128 sequences) per CTA at a time; per step t = T-1 .. 0 the tensor pipe runs three GEMM groups that
 // share operand images in shared memory:
-//   recompute  a_t   [128 x 256]  = [x_t | h_{t-1}] * Wcat^T            (two N = 128 halves; K = KX + 64)
+//   recompute  a_t   [128 x 256]  = [x_t | h_{t-1}] * Wcat^T            (four N = 64 quarters into two rotating
+//                                                                          TMEM slots; K = KX + 64)
 //   dgrad      [dx_t | dh_{t-1}]  = da_t * Wcat                          (Wcat image read MN-major; accumulated over
-//                                                                          four 64-column quarters of da_t)
+//                                                                          the four 64-column quarters of da_t)
 //   wgrad      dWcat^T [128 x 256] += [x_t | h_{t-1}]^T * da_t           (both images read MN-major; accumulator stays
 //                                                                          in TMEM for the whole launch)
-// TMEM (512 columns): dWcat^T 256 | a half 128 | [dx | dh] 128.
-// Gate columns are "packed": n = (u / 32) * 128 + gate * 32 + u % 32, so that each recompute half and each
-// 16-unit quarter holds all four gates of its units.  A quarter of da_t is written by the epilogue warps as a
-// [128 x 64] operand image (column kk = gate * 16 + u % 16); the dgrad K-steps of a quarter are the four 16-row
-// runs of Wcat that hold those columns; the wgrad accumulator columns are quarter * 64 + kk.
-// Warp roles: 8 epilogue warps (thread = one sequence x 8 units per quarter; gates, cell derivative, da, bias-gradient
-// butterfly, dh/dx read-back), 2 loader warps ([x_t | h_{t-1}] image from the fp32 stash, dropout applied),
-// 1 MMA warp.  Barriers: xh_full/xh_free, a_full/a_free, da_full/da_free, d_full/d_free.
+// TMEM (512 columns): dWcat^T 256 | gate quarters 2 x 64 | [dx | dh] 128.
+// Gate columns are "packed" quarter-major: n = (u / 16) * 64 + gate * 16 + u % 16, so that a quarter is 64 contiguous
+// rows of Wcat holding all four gates of 16 hidden units.  A quarter of da_t is written by the epilogue warps as a
+// [128 x 64] operand image (column kk = gate * 16 + u % 16); its dgrad K-steps are the four 16-row runs of that
+// quarter of Wcat; the wgrad accumulator columns are quarter * 64 + kk.
+// The epilogue of a quarter has a part that does not depend on the dh recurrence (gates and tanh(c_t) from the
+// recomputed pre-activations) and a part that does (da); the read-back of dh_{t} from the previous step's dgrad is
+// placed between the two, so that the dgrad latency of the last quarter hides behind the gate math of the next step.
+// The MMA warp issues, per quarter: dgrad (critical path) -> gate recompute two quarters ahead -> wgrad.
+// Warp roles: 8 epilogue warps (thread = one sequence x 8 units per quarter), 2 loader warps ([x_t | h_{t-1}] image
+// from the fp32 stash, dropout keep-bits applied), 1 MMA warp.
+// Barriers: xh_full/xh_free, a_full/a_free (per slot), da_full/da_free, d_full/d_free, done.
 constexpr int BW_EPI_WARPS = 8;
-constexpr int BW_THREADS = 32 * (BW_EPI_WARPS + LOADER_WARPS + 1);
-constexpr uint32_t TMEM_DW = 0, TMEM_A = 256, TMEM_D = 384;
+constexpr int BW_THREADS = 32 * (BW_EPI_WARPS + LOADER_WARPS + 2);   // 3 warpgroups: 2 epilogue, 1 = loaders + MMA + 1 idle warp
+constexpr uint32_t TMEM_DW = 0, TMEM_A = 256, TMEM_D = 384;    // dWcat^T | two 64-column gate-quarter slots | [dx | dh]
 
-__host__ __device__ constexpr int packed_row(int gate, int u) { return (u >> 5) * 128 + gate * 32 + (u & 31); }
+__host__ __device__ constexpr int packed_row(int gate, int u) { return (u >> 4) * 64 + gate * 16 + (u & 15); }
 
 __host__ __device__ inline size_t bwd_pack_bytes(bool layer0) {
     return 2 * (size_t)op_bytes(TG, kx_of(layer0) + TH) + TG * sizeof(float);
@@ -510,26 +518,45 @@ struct BwdSmem {
     static constexpr uint32_t off_pad = off_da + DB * NSPLIT * DAB;        // MN-major reads of a KC = 80 image run past its end
     static constexpr uint32_t off_bias = off_pad + (LAYER0 ? 1024 : 0);
     static constexpr uint32_t off_bar = off_bias + TG * 4;
-    static constexpr int NBAR = 2 * XB + 2 * DB + 4;
+    static constexpr int NBAR = 2 * XB + 2 * DB + 7;
     static constexpr uint32_t off_tmem = off_bar + NBAR * 8;
     static constexpr uint32_t total = off_tmem + 16 + 128;
 };
 
-// sum over the 32 lanes (rows) of 32 per-lane values; lane L ends up with the total of value index L
-__device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) {
+// sum over the 32 lanes (rows) of 32 per-lane values v[k / 8][k % 8]; lane L ends up with the total of value index L
+__device__ __forceinline__ float warp_transpose_sum32(float (&v)[4][8], int lane) {
 #pragma unroll
     for (int off = 16, half = 16; off > 0; off >>= 1, half >>= 1) {
         const bool up = (lane & off) != 0;
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             if (k < half) {
-                const float keep = up ? v[half + k] : v[k];
-                const float send = up ? v[k] : v[half + k];
-                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                const float lo = v[k >> 3][k & 7], hi = v[(half + k) >> 3][(half + k) & 7];
+                const float keep = up ? hi : lo;
+                const float send = up ? lo : hi;
+                v[k >> 3][k & 7] = keep + __shfl_xor_sync(0xffffffffu, send, off);
             }
         }
     }
-    return v[0];
+    return v[0][0];
+}
+
+// sum over the 32 lanes (rows) of 16 per-lane values v[k / 4][k % 4]; lanes 2m and 2m+1 both end up with the total of index m
+__device__ __forceinline__ float warp_transpose_sum16(float (&v)[4][4], int lane) {
+#pragma unroll
+    for (int off = 16, half = 8; half > 0; off >>= 1, half >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (k < half) {
+                const float lo = v[k >> 2][k & 3], hi = v[(half + k) >> 2][(half + k) & 3];
+                const float keep = up ? hi : lo;
+                const float send = up ? lo : hi;
+                v[k >> 2][k & 3] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+    }
+    return v[0][0] + __shfl_xor_sync(0xffffffffu, v[0][0], 1);
 }
 
 __device__ __forceinline__ void ld_global_v8(const float* p, float (&v)[8]) {
@@ -553,14 +580,15 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
     float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::off_bar);
-    uint64_t* xh_full = bars;               // [XB]
-    uint64_t* xh_free = xh_full + XB;       // [XB]
-    uint64_t* da_full = xh_free + XB;       // [DB]
-    uint64_t* da_free = da_full + DB;       // [DB]
-    uint64_t* a_full = da_free + DB;
-    uint64_t* a_free = a_full + 1;
-    uint64_t* d_full = a_free + 1;
-    uint64_t* d_free = d_full + 1;
+    uint64_t* xh_full = bars;               // [XB]   loader -> MMA: [x_t | h_{t-1}] image staged
+    uint64_t* xh_free = xh_full + XB;       // [XB]   MMA -> loader: every MMA reading the image has completed
+    uint64_t* da_full = xh_free + XB;       // [DB]   epilogue -> MMA: da quarter image written
+    uint64_t* da_free = da_full + DB;       // [DB]   MMA -> epilogue: dgrad + wgrad of the quarter completed
+    uint64_t* a_full = da_free + DB;        // [2]    MMA -> epilogue: recomputed gate quarter in TMEM slot
+    uint64_t* a_free = a_full + 2;          // [2]    epilogue -> MMA: slot read out
+    uint64_t* d_full = a_free + 2;          //        MMA -> epilogue: [dx | dh] of the step complete
+    uint64_t* d_free = d_full + 1;          //        epilogue -> MMA: [dx | dh] read out
+    uint64_t* done = d_free + 1;            //        MMA -> epilogue: every MMA of the CTA complete
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -575,7 +603,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     if (threadIdx.x == 0) {
         for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], LOADER_WARPS); mbar_init(&xh_free[b], 1); }
         for (int b = 0; b < DB; ++b) { mbar_init(&da_full[b], BW_EPI_WARPS); mbar_init(&da_free[b], 1); }
-        mbar_init(a_full, 1); mbar_init(a_free, BW_EPI_WARPS); mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS);
+        for (int b = 0; b < 2; ++b) { mbar_init(&a_full[b], 1); mbar_init(&a_free[b], BW_EPI_WARPS); }
+        mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS); mbar_init(done, 1);
         fence_barrier_init();
     }
     if (warp == BW_EPI_WARPS + LOADER_WARPS) tmem_alloc(tmem_slot, 512);
@@ -588,6 +617,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     const int64_t ntiles = (N + TM - 1) / TM;
     const int64_t my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const int64_t total_steps = my_tiles * T;
+    const int64_t total_q = 4 * total_steps;
+
+    // register rebalancing between warpgroups: the loader/MMA group releases registers, the two epilogue groups take them
+    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
 
     if (warp < BW_EPI_WARPS) {
         // ===================================== epilogue warps =====================================================
@@ -597,9 +631,40 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const uint32_t row_off = (uint32_t)(r >> 3) * SBO_DA + (uint32_t)(r & 7) * 16;
         const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
-        float dc[4][8], dh[4][8], db[4];
+        float dc[4][8], dh[4][8], db[4][2];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) db[q] = 0.f;
+        for (int q = 0; q < 4; ++q) db[q][0] = db[q][1] = 0.f;
+
+        // read back [dx | dh] of step (tile row, t_done): dh -> registers, dx -> masked store; then release d
+        auto read_back = [&](int64_t g_done, int64_t row, bool live, int t_done) {
+            mbar_wait(d_full, (uint32_t)(g_done & 1));
+            tc_fence_after();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) tmem_ld8(lane_addr + TMEM_D + DH_COL0 + 16 * q + 8 * grp, dh[q]);
+            if (!LAYER0) {
+                float dx[4][8];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) tmem_ld8(lane_addr + TMEM_D + 32 * grp + 8 * c, dx[c]);
+                tmem_ld_wait();
+                if (live) {
+                    const uint32_t mb = drop ? (uint32_t)(drop_bits[(int64_t)t_done * N + row] >> (32 * grp)) : 0xFFFFFFFFu;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        if (drop) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) dx[c][i] = ((mb >> (8 * c + i)) & 1u) ? dx[c][i] * inv_keep : 0.f;
+                        }
+                        st_global_v8(d_in + ((int64_t)t_done * N + row) * TH + 32 * grp + 8 * c, dx[c]);
+                    }
+                }
+            } else {
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(d_free);
+        };
+
         int64_t g = 0;
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int64_t row = tile * TM + r;
@@ -608,137 +673,123 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             for (int q = 0; q < 4; ++q)
 #pragma unroll
                 for (int i = 0; i < 8; ++i) dc[q][i] = dh[q][i] = 0.f;
+            // software pipeline of the per-quarter global operands: (c_t, c_{t-1}, d_out) of the NEXT quarter are in flight
+            float nct[8], ncp[8], ndq[8];
+            auto issue_loads = [&](int t, int q) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) nct[i] = ncp[i] = ndq[i] = 0.f;
+                if (live && t >= 0) {
+                    const int64_t o = ((int64_t)t * N + row) * TH + 16 * q + 8 * grp;
+                    ld_global_v8(c_st + o, nct);
+                    if (t > 0) ld_global_v8(c_st + o - N * TH, ncp);
+                    if (d_out) ld_global_v8(d_out + o, ndq);
+                    else if (t == T - 1) ld_global_v8(dhT + row * TH + 16 * q + 8 * grp, ndq);
+                }
+            };
+            issue_loads(T - 1, 0);
             for (int t = T - 1; t >= 0; --t, ++g) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int u0 = 16 * q + 8 * grp;                         // first hidden unit of this thread's slice
-                    // global operands of this quarter (issued before the TMEM wait so that they overlap it)
+                    const int64_t qi = 4 * g + q;                              // running quarter index
+                    const int slot = q & 1;
                     float ct[8], cp[8], dq[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) ct[i] = cp[i] = dq[i] = 0.f;
-                    if (live) {
-                        const int64_t o = ((int64_t)t * N + row) * TH + u0;
-                        ld_global_v8(c_st + o, ct);
-                        if (t > 0) ld_global_v8(c_st + o - N * TH, cp);
-                        if (d_out) ld_global_v8(d_out + o, dq);
-                        else if (t == T - 1) ld_global_v8(dhT + row * TH + u0, dq);
-                    }
-                    if ((q & 1) == 0) mbar_wait(a_full, (uint32_t)((2 * g + (q >> 1)) & 1));
+                    for (int i = 0; i < 8; ++i) { ct[i] = nct[i]; cp[i] = ncp[i]; dq[i] = ndq[i]; }
+                    mbar_wait(&a_full[slot], (uint32_t)((qi >> 1) & 1));
                     tc_fence_after();
-                    float av[4][8];
-                    const uint32_t acol = TMEM_A + 16 * (q & 1) + 8 * grp;
-#pragma unroll
-                    for (int gate = 0; gate < 4; ++gate) tmem_ld8(lane_addr + acol + gate * 32, av[gate]);
-                    tmem_ld_wait();
-                    if (q & 1) {                                              // this half of `a` is drained
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(a_free);
-                    }
-                    // gates and tanh(c_t) from 5 ex2 + 2 rcp per unit (batch inversion of (D_i, D_f, D_g) and of (D_o, D_c)),
-                    // written stage by stage over the 8 units so that each MUFU / FMA stage is 8..40 independent instructions
-                    float da[32], Ec[8], r1[8], r2[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (u0 + i));
-                        av[0][i] = fminf(fmaf(av[0][i], -LOG2E, b4.x), EXP_CLAMP);
-                        av[1][i] = fminf(fmaf(av[1][i], -LOG2E, b4.y), EXP_CLAMP);
-                        av[2][i] = fminf(fmaf(av[2][i], 2.f * LOG2E, b4.z), EXP_CLAMP);
-                        av[3][i] = fminf(fmaf(av[3][i], -LOG2E, b4.w), EXP_CLAMP);
-                        Ec[i] = fminf(2.f * LOG2E * ct[i], EXP_CLAMP);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        av[0][i] = ex2a(av[0][i]); av[1][i] = ex2a(av[1][i]); av[2][i] = ex2a(av[2][i]); av[3][i] = ex2a(av[3][i]);
-                        Ec[i] = ex2a(Ec[i]);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        r1[i] = (1.f + av[0][i]) * (1.f + av[1][i]) * (1.f + av[2][i]);
-                        r2[i] = (1.f + av[3][i]) * (1.f + Ec[i]);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) { r1[i] = rcpa(r1[i]); r2[i] = rcpa(r2[i]); }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float Di = 1.f + av[0][i], Df = 1.f + av[1][i], Dg = 1.f + av[2][i], Do = 1.f + av[3][i], Dc = 1.f + Ec[i];
-                        const float t1 = r1[i] * Dg;
-                        const float ig = t1 * Df, fg = t1 * Di, gg = (av[2][i] - 1.f) * (r1[i] * (Di * Df));
-                        const float og = r2[i] * Dc, tc = (Ec[i] - 1.f) * (r2[i] * Do);
-                        const float dhv = dh[q][i] + dq[i];
-                        const float d_o = dhv * tc;
-                        const float dcc = dc[q][i] + dhv * og * (1.f - tc * tc);
-                        dc[q][i] = dcc * fg;
-                        const float a_i = dcc * gg * ig * (1.f - ig);
-                        const float a_f = dcc * cp[i] * fg * (1.f - fg);
-                        const float a_g = dcc * ig * (1.f - gg * gg);
-                        const float a_o = d_o * og * (1.f - og);
-                        da[0 * 8 + i] = live ? a_i : 0.f;
-                        da[1 * 8 + i] = live ? a_f : 0.f;
-                        da[2 * 8 + i] = live ? a_g : 0.f;
-                        da[3 * 8 + i] = live ? a_o : 0.f;
-                    }
-                    // operand image of this quarter: column kk = gate * 16 + 8 * grp + i  ->  16-byte chunk gate * 2 + grp
-                    const int64_t qi = 4 * g + q;                              // running quarter index
                     const int buf = (int)(qi % DB);
-                    if (qi >= DB) mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
                     uint8_t* da_hi = smem + S::off_da + (buf * NSPLIT) * S::DAB;
                     uint8_t* da_lo = da_hi + S::DAB;
+                    // the 8 units of the slice are processed as two passes of 4 (register budget); each pass has a part that
+                    // does not depend on the dh recurrence (A: gates, tanh(c_t)) and a part that does (B: da)
 #pragma unroll
-                    for (int gate = 0; gate < 4; ++gate) {
-                        uint4 hi4, lo4;
-                        split2(da[gate * 8 + 0], da[gate * 8 + 1], hi4.x, lo4.x);
-                        split2(da[gate * 8 + 2], da[gate * 8 + 3], hi4.y, lo4.y);
-                        split2(da[gate * 8 + 4], da[gate * 8 + 5], hi4.z, lo4.z);
-                        split2(da[gate * 8 + 6], da[gate * 8 + 7], hi4.w, lo4.w);
-                        const uint32_t o = row_off + (uint32_t)(gate * 2 + grp) * LBO_BYTES;
-                        *reinterpret_cast<uint4*>(da_hi + o) = hi4;
-                        if (NSPLIT == 2) *reinterpret_cast<uint4*>(da_lo + o) = lo4;
-                    }
-                    fence_proxy_async();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&da_full[buf]);
-                    db[q] += warp_transpose_sum32(da, lane);                  // bias gradient: sum over the warp's 32 rows
-                }
-                // ---- read back dh_{t-1} (and dx_t) -------------------------------------------------------------
-                mbar_wait(d_full, (uint32_t)(g & 1));
-                tc_fence_after();
+                    for (int hp = 0; hp < 2; ++hp) {
+                        float av[4][4];
+                        const uint32_t acol = TMEM_A + 64 * slot + 8 * grp + 4 * hp;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) tmem_ld8(lane_addr + TMEM_D + DH_COL0 + 16 * q + 8 * grp, dh[q]);
-                if (!LAYER0) {
-                    float dx[4][8];
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) tmem_ld8(lane_addr + TMEM_D + 32 * grp + 8 * c, dx[c]);
-                    tmem_ld_wait();
-                    if (live) {
-                        const uint32_t mb = drop ? (uint32_t)(drop_bits[(int64_t)t * N + row] >> (32 * grp)) : 0xFFFFFFFFu;
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const int u = 32 * grp + 8 * c;
-                            if (drop) {
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) dx[c][i] = ((mb >> (8 * c + i)) & 1u) ? dx[c][i] * inv_keep : 0.f;
-                            }
-                            st_global_v8(d_in + ((int64_t)t * N + row) * TH + u, dx[c]);
+                        for (int gate = 0; gate < 4; ++gate) tmem_ld4(lane_addr + acol + gate * 16, av[gate]);
+                        tmem_ld_wait();
+                        if (hp == 1) {                       // slot fully read out
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&a_free[slot]);
+                            if (q < 3) issue_loads(t, q + 1); else issue_loads(t - 1, 0);
                         }
+                        float Ec[4], r1[4], r2[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (u0 + 4 * hp + i));
+                            av[0][i] = fminf(fmaf(av[0][i], -LOG2E, b4.x), EXP_CLAMP);
+                            av[1][i] = fminf(fmaf(av[1][i], -LOG2E, b4.y), EXP_CLAMP);
+                            av[2][i] = fminf(fmaf(av[2][i], 2.f * LOG2E, b4.z), EXP_CLAMP);
+                            av[3][i] = fminf(fmaf(av[3][i], -LOG2E, b4.w), EXP_CLAMP);
+                            Ec[i] = fminf(2.f * LOG2E * ct[4 * hp + i], EXP_CLAMP);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            av[0][i] = ex2a(av[0][i]); av[1][i] = ex2a(av[1][i]); av[2][i] = ex2a(av[2][i]); av[3][i] = ex2a(av[3][i]);
+                            Ec[i] = ex2a(Ec[i]);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            r1[i] = (1.f + av[0][i]) * (1.f + av[1][i]) * (1.f + av[2][i]);
+                            r2[i] = (1.f + av[3][i]) * (1.f + Ec[i]);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) { r1[i] = rcpa(r1[i]); r2[i] = rcpa(r2[i]); }
+                        // dh of this step arrives from the previous step's dgrad (first pass of the first quarter only)
+                        if (q == 0 && hp == 0 && t < T - 1) read_back(g - 1, row, live, t + 1);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int ii = 4 * hp + i;
+                            const float Di = 1.f + av[0][i], Df = 1.f + av[1][i], Dg = 1.f + av[2][i], Do = 1.f + av[3][i], Dc = 1.f + Ec[i];
+                            const float t1 = r1[i] * Dg;
+                            const float ig = t1 * Df, fg = t1 * Di, gg = (av[2][i] - 1.f) * (r1[i] * (Di * Df));
+                            const float og = r2[i] * Dc, tc = (Ec[i] - 1.f) * (r2[i] * Do);
+                            const float dhv = dh[q][ii] + dq[ii];
+                            const float d_o = dhv * tc;
+                            const float dcc = dc[q][ii] + dhv * og * (1.f - tc * tc);
+                            dc[q][ii] = dcc * fg;
+                            av[0][i] = live ? dcc * gg * ig * (1.f - ig) : 0.f;
+                            av[1][i] = live ? dcc * cp[ii] * fg * (1.f - fg) : 0.f;
+                            av[2][i] = live ? dcc * ig * (1.f - gg * gg) : 0.f;
+                            av[3][i] = live ? d_o * og * (1.f - og) : 0.f;
+                        }
+                        // operand image: column kk = gate * 16 + 8 * grp + 4 * hp + i -> 16-byte chunk gate * 2 + grp, 8-byte half hp
+                        if (hp == 0 && qi >= DB) mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
+#pragma unroll
+                        for (int gate = 0; gate < 4; ++gate) {
+                            uint2 hi2, lo2;
+                            split2x2(av[gate][0], av[gate][1], av[gate][2], av[gate][3], hi2, lo2);
+                            const uint32_t o = row_off + (uint32_t)(gate * 2 + grp) * LBO_BYTES + 8 * hp;
+                            *reinterpret_cast<uint2*>(da_hi + o) = hi2;
+                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(da_lo + o) = lo2;
+                        }
+                        if (hp == 1) {
+                            fence_proxy_async();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&da_full[buf]);
+                        }
+                        db[q][hp] += warp_transpose_sum16(av, lane);          // bias gradient over the warp's 32 rows
                     }
-                } else {
-                    tmem_ld_wait();
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(d_free);
             }
+            read_back(g - 1, row, live, 0);                 // dx_0 of this tile; releases d for the next tile
         }
         // ---- final: bias-gradient partials and the weight-gradient accumulator ---------------------------------------
         {
             float* bp = bpart + ((int64_t)blockIdx.x * 4 + wq) * TG;
+            // lane pair (2m, 2m+1) holds value index m = gate * 4 + i of each 4-unit pass
+            if ((lane & 1) == 0) {
+                const int m = lane >> 1, gate = m >> 2, i = m & 3;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) bp[(lane >> 3) * TH + 16 * q + 8 * grp + (lane & 7)] = db[q];
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int hp = 0; hp < 2; ++hp) bp[gate * TH + 16 * q + 8 * grp + 4 * hp + i] = db[q][hp];
+            }
         }
-        // all MMAs of this CTA have completed once the last d_full/da_free phases were observed; the MMA warp commits a
-        // final barrier phase on a_full for the accumulator read-back
-        mbar_wait(a_full, (uint32_t)((2 * total_steps) & 1));
+        mbar_wait(done, 0u);
         tc_fence_after();
         {
             const int kcat = r;                                               // TMEM lane = row of dWcat^T
@@ -779,20 +830,17 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
-                uint64_t m[8];
-                float4 v[8][4];
-                // first half of the image: the loads are in flight while we wait for the buffer
+                // batches of 4 row groups (64 registers); the first batch is in flight while we wait for the buffer
+                uint64_t m[4];
+                float4 v[4][4];
+                const float* hsrc = h_st + ((int64_t)(t > 0 ? t - 1 : 0) * N + r0) * TH;
+                const int64_t h_live = t > 0 ? rows_live : 0;
                 if (LAYER0) {
-                    // h_{t-1} part
-                    if (t > 0) tile_load(v, h_st + ((int64_t)(t - 1) * N + r0) * TH, rows_live, lw, lane);
-                    else tile_load(v, h_st, 0, lw, lane);
-                } else {
-                    tile_load(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw, lane);
-                    if (drop) tile_load_bits(m, drop_bits + (int64_t)t * N + r0, rows_live, lw, lane);
-                }
-                if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
-                if (LAYER0) {
-                    tile_store<NSPLIT>(v, xh_hi, xh_lo, SBO_W, KX, lw, lane, false, m, 1.f);
+                    tile_load<4>(v, hsrc, h_live, lw * 8, lane);
+                    if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
+                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8, lane, false, m, 1.f);
+                    tile_load<4>(v, hsrc, h_live, lw * 8 + 4, lane);
+                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8 + 4, lane, false, m, 1.f);
                     // x part: 16 columns, lane quarter qq covers columns 4qq .. 4qq+3 of its row
 #pragma unroll
                     for (int rgi = 0; rgi < 8; ++rgi) {
@@ -813,112 +861,113 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
                     }
                 } else {
-                    tile_store<NSPLIT>(v, xh_hi, xh_lo, SBO_W, 0, lw, lane, drop, m, inv_keep);
-                    if (t > 0) tile_load(v, h_st + ((int64_t)(t - 1) * N + r0) * TH, rows_live, lw, lane);
-                    else tile_load(v, h_st, 0, lw, lane);
-                    tile_store<NSPLIT>(v, xh_hi, xh_lo, SBO_W, KX, lw, lane, false, m, 1.f);
+                    const float* xsrc = xin + ((int64_t)t * N + r0) * TH;
+                    const uint64_t* bsrc = drop_bits + (int64_t)t * N + r0;
+                    tile_load<4>(v, xsrc, rows_live, lw * 8, lane);
+                    if (drop) tile_load_bits<4>(m, bsrc, rows_live, lw * 8, lane);
+                    if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
+                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8, lane, drop, m, inv_keep);
+                    tile_load<4>(v, xsrc, rows_live, lw * 8 + 4, lane);
+                    if (drop) tile_load_bits<4>(m, bsrc, rows_live, lw * 8 + 4, lane);
+                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8 + 4, lane, drop, m, inv_keep);
+                    tile_load<4>(v, hsrc, h_live, lw * 8, lane);
+                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8, lane, false, m, 1.f);
+                    tile_load<4>(v, hsrc, h_live, lw * 8 + 4, lane);
+                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8 + 4, lane, false, m, 1.f);
                 }
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&xh_full[buf]);
             }
         }
-    } else {
+    } else if (warp == BW_EPI_WARPS + LOADER_WARPS) {
         // ===================================== MMA issuer =========================================================
-        if (lane == 0) {
-            constexpr uint32_t idesc_a = make_idesc_bf16(TM, 128, 0, 0);      // recompute half
+        if (lane == 0 && total_q > 0) {
+            constexpr uint32_t idesc_a = make_idesc_bf16(TM, 64, 0, 0);       // recompute of one quarter
             constexpr uint32_t idesc_d = make_idesc_bf16(TM, ND, 0, 1);       // dgrad: A K-major, B MN-major
             constexpr uint32_t idesc_w = make_idesc_bf16(TM, 64, 1, 1);       // wgrad: both MN-major
             const uint32_t s_base = smem_u32(smem);
             const uint32_t w_hi = s_base + S::off_w, w_lo = w_hi + S::WB;
-            auto issue_recompute = [&](int half, uint32_t xh_hi, uint32_t xh_lo) {
-                const uint32_t d = tmem_base + TMEM_A;
-                const uint32_t wrow = (uint32_t)(half * 128 / 8) * SBO_W;
-                uint32_t acc = 0;
+            auto xh_of = [&](int64_t step) { return s_base + S::off_xh + ((uint32_t)(step % XB) * NSPLIT) * S::XHB; };
+            // gates of running quarter nq -> TMEM slot nq & 1 (waits for the slot to be read out and for the image of its step)
+            auto issue_recompute = [&](int64_t nq) {
+                const int64_t ng = nq >> 2;
+                const int q = (int)(nq & 3), slot = (int)(nq & 1);
+                if (q == 0 || (XB == 1 && q == 1)) mbar_wait(&xh_full[ng % XB], (uint32_t)((ng / XB) & 1));
+                if (nq >= 2) mbar_wait(&a_free[slot], (uint32_t)(((nq >> 1) - 1) & 1));
+                tc_fence_after();
+                const uint32_t xh_hi = xh_of(ng), xh_lo = xh_hi + S::XHB;
+                const uint32_t d = tmem_base + TMEM_A + 64 * slot;
+                const uint32_t wrow = (uint32_t)(q * 64 / 8) * SBO_W;
 #pragma unroll
                 for (int ks = 0; ks < KC / 16; ++ks) {
                     const uint32_t ko = ks * 2 * LBO_BYTES;
-                    umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, acc);
-                    acc = 1;
+                    umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, ks > 0 ? 1u : 0u);
                     if (NSPLIT == 2) {
                         umma_bf16(d, make_desc(xh_lo + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, 1);
                         umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_lo + wrow + ko, LBO_BYTES, SBO_W), idesc_a, 1);
                     }
                 }
-                umma_commit(a_full);
+                umma_commit(&a_full[slot]);
             };
-            int64_t a_free_waits = 0;                                         // number of a_free phases consumed so far
-            bool pre_issued = false;
-            for (int64_t g = 0; g < total_steps; ++g) {
-                const int xb = (int)(g % XB);
-                const uint32_t xh_hi = s_base + S::off_xh + (xb * NSPLIT) * S::XHB, xh_lo = xh_hi + S::XHB;
-                if (!pre_issued) {
-                    mbar_wait(&xh_full[xb], (uint32_t)((g / XB) & 1));
-                    if (g > 0) { mbar_wait(a_free, (uint32_t)(a_free_waits & 1)); ++a_free_waits; }
-                    tc_fence_after();
-                    issue_recompute(0, xh_hi, xh_lo);
+            issue_recompute(0);
+            issue_recompute(1);
+            for (int64_t qi = 0; qi < total_q; ++qi) {
+                const int64_t g = qi >> 2;
+                const int q = (int)(qi & 3);
+                const uint32_t xh_hi = xh_of(g), xh_lo = xh_hi + S::XHB;
+                const int buf = (int)(qi % DB);
+                mbar_wait(&da_full[buf], (uint32_t)((qi / DB) & 1));
+                if (q == 0 && g > 0) mbar_wait(d_free, (uint32_t)((g - 1) & 1));
+                tc_fence_after();
+                const uint32_t da_hi = s_base + S::off_da + (buf * NSPLIT) * S::DAB, da_lo = da_hi + S::DAB;
+                // ---- dgrad partial (on the dh critical path: issued first).  K = the four 16-row runs of this quarter
+                {
+                    const uint32_t d = tmem_base + TMEM_D;
+                    const uint32_t mn_off = LAYER0 ? (uint32_t)(KX / 8) * LBO_BYTES : 0u;   // layer 0: only the h columns of Wcat
+#pragma unroll
+                    for (int gate = 0; gate < 4; ++gate) {
+                        const uint32_t wk = (uint32_t)((q * 64 + gate * 16) / 8) * SBO_W + mn_off;
+                        const uint32_t ak = gate * 2 * LBO_BYTES;
+                        const uint32_t acc = (q > 0 || gate > 0) ? 1u : 0u;
+                        umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, acc);
+                        if (NSPLIT == 2) {
+                            umma_bf16(d, make_desc(da_lo + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, 1);
+                            umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_lo + wk, SBO_W, LBO_BYTES), idesc_d, 1);
+                        }
+                    }
+                    if (q == 3) umma_commit(d_full);
                 }
-                pre_issued = false;
+                // ---- gates two quarters ahead (same step, or the next step when its image is already staged) ----------
+                {
+                    const int64_t nq = qi + 2;
+                    if (nq < total_q && (q < 2 || XB == 2)) issue_recompute(nq);
+                }
+                // ---- wgrad partial: dWcat^T[:, quarter columns] += xh^T * da_quarter, K = the 128 rows of the tile ----
+                {
+                    const uint32_t d = tmem_base + TMEM_DW + q * 64;
+                    const uint32_t acc = g > 0 ? 1u : 0u;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (q == 2) {
-                        mbar_wait(a_free, (uint32_t)(a_free_waits & 1)); ++a_free_waits;
-                        tc_fence_after();
-                        issue_recompute(1, xh_hi, xh_lo);
-                    }
-                    if (q == 3 && XB == 2 && g + 1 < total_steps) {
-                        // next step's first recompute half ahead of this step's last quarter (off the dh critical path)
-                        const int nb = (int)((g + 1) % XB);
-                        const uint32_t nh = s_base + S::off_xh + (nb * NSPLIT) * S::XHB;
-                        mbar_wait(&xh_full[nb], (uint32_t)(((g + 1) / XB) & 1));
-                        mbar_wait(a_free, (uint32_t)(a_free_waits & 1)); ++a_free_waits;
-                        tc_fence_after();
-                        issue_recompute(0, nh, nh + S::XHB);
-                        pre_issued = true;
-                    }
-                    const int64_t qi = 4 * g + q;
-                    const int buf = (int)(qi % DB);
-                    mbar_wait(&da_full[buf], (uint32_t)((qi / DB) & 1));
-                    if (q == 0 && g > 0) mbar_wait(d_free, (uint32_t)((g - 1) & 1));
-                    tc_fence_after();
-                    const uint32_t da_hi = s_base + S::off_da + (buf * NSPLIT) * S::DAB, da_lo = da_hi + S::DAB;
-                    // dgrad partial: K = the four 16-column runs (one per gate) of this quarter
-                    {
-                        const uint32_t d = tmem_base + TMEM_D;
-                        const uint32_t mn_off = LAYER0 ? (uint32_t)(KX / 8) * LBO_BYTES : 0u;   // layer 0: only the h columns of Wcat
-#pragma unroll
-                        for (int gate = 0; gate < 4; ++gate) {
-                            const int n0 = (q >> 1) * 128 + gate * 32 + 16 * (q & 1);
-                            const uint32_t wk = (uint32_t)(n0 / 8) * SBO_W + mn_off;
-                            const uint32_t ak = gate * 2 * LBO_BYTES;
-                            const uint32_t acc = (q > 0 || gate > 0) ? 1u : 0u;
-                            umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, acc);
-                            if (NSPLIT == 2) {
-                                umma_bf16(d, make_desc(da_lo + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, 1);
-                                umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_lo + wk, SBO_W, LBO_BYTES), idesc_d, 1);
-                            }
+                    for (int ks = 0; ks < TM / 16; ++ks) {
+                        const uint32_t xo = ks * 2 * SBO_W, dao = ks * 2 * SBO_DA;
+                        umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, (acc | (ks > 0)) ? 1u : 0u);
+                        if (NSPLIT == 2) {
+                            umma_bf16(d, make_desc(xh_lo + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
+                            umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_lo + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
                         }
-                        if (q == 3) umma_commit(d_full);
                     }
-                    // wgrad partial: dWcat^T[:, quarter columns] += xh^T * da_quarter, K = the 128 rows of the tile
-                    {
-                        const uint32_t d = tmem_base + TMEM_DW + q * 64;
-                        const uint32_t acc = g > 0 ? 1u : 0u;
-#pragma unroll
-                        for (int ks = 0; ks < TM / 16; ++ks) {
-                            const uint32_t xo = ks * 2 * SBO_W, dao = ks * 2 * SBO_DA;
-                            umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, (acc | (ks > 0)) ? 1u : 0u);
-                            if (NSPLIT == 2) {
-                                umma_bf16(d, make_desc(xh_lo + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
-                                umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_lo + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
-                            }
-                        }
-                        umma_commit(&da_free[buf]);
-                        if (q == 3) umma_commit(&xh_free[xb]);
-                    }
+                    umma_commit(&da_free[buf]);
+                    if (q == 3) umma_commit(&xh_free[g % XB]);
+                }
+                // single-buffered image: the next step's first two quarters can only be recomputed after the reload
+                if (XB == 1 && q == 3 && qi + 1 < total_q) {
+                    issue_recompute(qi + 1);
+                    issue_recompute(qi + 2);
                 }
             }
-            umma_commit(a_full);              // final phase: every MMA of this CTA is complete
+            umma_commit(done);
+        } else if (lane == 0) {
+            mbar_arrive(done);
         }
         __syncwarp();
     }

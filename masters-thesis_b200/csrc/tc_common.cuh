@@ -79,6 +79,14 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float (&v)[4]) {
+    uint32_t r[4];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- descriptors ------------------------------------------------------------------------------
@@ -116,6 +124,11 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
     __nv_bfloat162 l = __floats2bfloat162_rn(ra, rb);
     hi = *reinterpret_cast<uint32_t*>(&h);
     lo = *reinterpret_cast<uint32_t*>(&l);
+}
+
+__device__ __forceinline__ void split2x2(float a, float b, float c, float d, uint2& hi, uint2& lo) {
+    split2(a, b, hi.x, lo.x);
+    split2(c, d, hi.y, lo.y);
 }
 
 __device__ __forceinline__ void st_global_v8(float* p, const float (&v)[8]) {
