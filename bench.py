@@ -224,6 +224,9 @@ def run_b200(args):
                "d2h_bytes_per_step": 4, "steps": e2e_steps,
                "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> cudaMemcpyAsync -> B200Trainer.training_step -> loss.item()"}
 
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     # ---- roofline of the dominant kernel (live CUDA-event durations from the timed region) -------

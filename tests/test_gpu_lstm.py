@@ -163,6 +163,25 @@ def test_chunked_backward_equals_unchunked(engine, data):
         assert rel_err(e.grads[: e.P].cpu().numpy(), full.cpu().numpy()) < 1e-5
 
 
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("kind", ["mse", "nll"])
+def test_data_parallel_semantics_emulated_two_ranks(engine, kind, data):
+    """What the 2-rank data-parallel step computes, emulated on one GPU: each rank's local-batch gradient pre-scaled
+    by 1/W, summed (the NCCL all-reduce) -- against the oracle's emulated DDP (mean of per-rank gradients)."""
+    torch.manual_seed(21)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    e = make_engine(O.flat_params(m), 2, 0.0, engine)
+    total = torch.zeros(e.P, device=DEV)
+    for rank in range(2):
+        batch = B.DeviceBatch.from_reference(ref_batch(data, 2 * rank, 2 * rank + 2), DEV)
+        e.forward(batch, training=True)
+        e.heads(batch, kind, 100.0, None, 0.5, True)
+        e.backward(batch, True)
+        total += e.grads[: e.P]
+    O.ddp_mean_grads(m, [ref_batch(data, 0, 2), ref_batch(data, 2, 4)], kind)
+    assert rel_err(total.cpu().numpy(), O.flat_grads(m).numpy()) < GRAD_RTOL
+
+
 def test_trainer_fit_matches_oracle_loop():
     """End to end through B200Trainer (the trainer=b200 object): 6 steps of batch 2 on device-generated
     windows, then validation and test -- against the oracle loop fed the SAME windows."""
