@@ -137,6 +137,10 @@ B200_API int b200_lstm_bwd(int mode, const float* params, int n_features, int hi
  * K, N multiples of 16, <= 256. */
 B200_API int b200_tc_selftest(const float* A, const float* B, int variant, int K, int N, float* D, void* stream);
 
+/* Debug hook (no counterpart in the reference): event trace of CTA 0 of the tcgen05 backward kernel.  The buffer
+ * holds 4 roles x 8192 records of {tag, clock64}; NULL switches tracing off.  See tools/trace_bwd.py. */
+B200_API int b200_debug_trace(void* device_buffer);
+
 /* ---------------------------------------------------------------- heads + objective
  * Replaces alpha_head/beta_head (src/model.py:107-108, addmm), the decoder arithmetic of
  * _shared_step (src/model.py:192-202, 234-249, 286-306), torchmetrics MeanSquaredError,

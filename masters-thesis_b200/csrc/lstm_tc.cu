@@ -33,6 +33,19 @@ using namespace tc;
 // tuning switches (host sets them from the environment once; 1 = on)
 __constant__ int c_tc_prefetch = 1;
 
+// Optional event trace of CTA 0 (b200_debug_trace): record = {role << 24 | event << 16 | quarter << 8 | 0, step, clock64};
+// four roles x TRACE_CAP records.  Null pointer = off (one uniform predicate per site).
+__constant__ unsigned long long* c_trace = nullptr;
+constexpr int TRACE_CAP = 8192;
+__device__ __forceinline__ void trace_ev(int role, int ev, int q, long long step, int& n) {
+    if (c_trace != nullptr && blockIdx.x == 0 && n < TRACE_CAP) {
+        unsigned long long* rec = c_trace + ((size_t)role * TRACE_CAP + n) * 2;
+        rec[0] = ((unsigned long long)(unsigned)((role << 24) | (ev << 16) | (q << 8)) << 32) | (unsigned long long)(unsigned)step;
+        rec[1] = (unsigned long long)clock64();
+        ++n;
+    }
+}
+
 constexpr int TH = 64;              // hidden size of this engine
 constexpr int TG = 4 * TH;          // gate columns = UMMA N
 constexpr int TM = 128;             // sequences per tile = UMMA M
@@ -576,6 +589,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     constexpr uint32_t SBO_W = sbo_of(KC), SBO_DA = sbo_of(64);
     constexpr int DH_COL0 = LAYER0 ? 0 : TH;                 // column of dh inside the d region
     constexpr int ND = LAYER0 ? TH : 2 * TH;                  // dgrad N
+    // With a single image buffer the reload sits on the critical path between two steps, exactly when the eight
+    // epilogue warps are idle: they then stage the next image themselves (2 row groups each, loads issued before the
+    // buffer is released) and the loader warps only prefetch into L2.
+    constexpr bool EPI_LOADS = (XB == 1) && !LAYER0;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
     float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
@@ -601,10 +618,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         if (LAYER0) for (int i = threadIdx.x; i < 256; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + S::off_pad)[i] = 0u;
     }
     if (threadIdx.x == 0) {
-        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], LOADER_WARPS); mbar_init(&xh_free[b], 1); }
-        for (int b = 0; b < DB; ++b) { mbar_init(&da_full[b], BW_EPI_WARPS); mbar_init(&da_free[b], 1); }
+        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], EPI_LOADS ? BW_EPI_WARPS : LOADER_WARPS); mbar_init(&xh_free[b], 2); }
+        for (int b = 0; b < DB; ++b) { mbar_init(&da_full[b], BW_EPI_WARPS); mbar_init(&da_free[b], 2); }
         for (int b = 0; b < 2; ++b) { mbar_init(&a_full[b], 1); mbar_init(&a_free[b], BW_EPI_WARPS); }
-        mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS); mbar_init(done, 1);
+        mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS); mbar_init(done, 2);
         fence_barrier_init();
     }
     if (warp == BW_EPI_WARPS + LOADER_WARPS) tmem_alloc(tmem_slot, 512);
@@ -666,6 +683,28 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         };
 
         int64_t g = 0;
+        int ntr = 0;
+        const bool tracer = warp == 0 && lane == 0;
+        // EPI_LOADS: this warp stages row groups 2*warp, 2*warp+1 of the [x | h] image of step (tile_n, t_n); the image of
+        // running step g_n may be written once the MMAs of step g_n - 1 have released the (single) buffer
+        auto stage_image = [&](int64_t tile_n, int t_n, int64_t g_n) {
+            const int64_t r0 = tile_n * TM;
+            const int64_t rows_live = N - r0;
+            uint8_t* xh_hi = smem + S::off_xh;
+            uint8_t* xh_lo = xh_hi + S::XHB;
+            float4 vx[2][4], vh[2][4];
+            uint64_t m[2] = {0ull, 0ull};
+            tile_load<2>(vx, xin + ((int64_t)t_n * N + r0) * TH, rows_live, 2 * warp, lane);
+            tile_load<2>(vh, h_st + ((int64_t)(t_n > 0 ? t_n - 1 : 0) * N + r0) * TH, t_n > 0 ? rows_live : 0, 2 * warp, lane);
+            if (drop) tile_load_bits<2>(m, drop_bits + (int64_t)t_n * N + r0, rows_live, 2 * warp, lane);
+            if (g_n > 0) mbar_wait(&xh_free[0], (uint32_t)((g_n - 1) & 1));
+            tile_store<NSPLIT, 2>(vx, xh_hi, xh_lo, SBO_W, 0, 2 * warp, lane, drop, m, inv_keep);
+            tile_store<NSPLIT, 2>(vh, xh_hi, xh_lo, SBO_W, KX, 2 * warp, lane, false, m, 1.f);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&xh_full[0]);
+        };
+        if (EPI_LOADS && blockIdx.x < ntiles) stage_image(blockIdx.x, T - 1, 0);
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int64_t row = tile * TM + r;
             const bool live = row < N;
@@ -696,8 +735,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     float ct[8], cp[8], dq[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) { ct[i] = nct[i]; cp[i] = ncp[i]; dq[i] = ndq[i]; }
+                    if (tracer) trace_ev(0, 0, q, g, ntr);
                     mbar_wait(&a_full[slot], (uint32_t)((qi >> 1) & 1));
                     tc_fence_after();
+                    if (tracer) trace_ev(0, 1, q, g, ntr);
                     const int buf = (int)(qi % DB);
                     uint8_t* da_hi = smem + S::off_da + (buf * NSPLIT) * S::DAB;
                     uint8_t* da_lo = da_hi + S::DAB;
@@ -739,7 +780,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 #pragma unroll
                         for (int i = 0; i < 4; ++i) { r1[i] = rcpa(r1[i]); r2[i] = rcpa(r2[i]); }
                         // dh of this step arrives from the previous step's dgrad (first pass of the first quarter only)
-                        if (q == 0 && hp == 0 && t < T - 1) read_back(g - 1, row, live, t + 1);
+                        if (q == 0 && hp == 0 && t < T - 1) {
+                            if (tracer) trace_ev(0, 2, q, g, ntr);
+                            read_back(g - 1, row, live, t + 1);
+                            if (tracer) trace_ev(0, 3, q, g, ntr);
+                        }
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
                             const int ii = 4 * hp + i;
@@ -757,7 +802,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                             av[3][i] = live ? d_o * og * (1.f - og) : 0.f;
                         }
                         // operand image: column kk = gate * 16 + 8 * grp + 4 * hp + i -> 16-byte chunk gate * 2 + grp, 8-byte half hp
-                        if (hp == 0 && qi >= DB) mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
+                        if (hp == 0 && qi >= DB) {
+                            if (tracer) trace_ev(0, 4, q, g, ntr);
+                            mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
+                            if (tracer) trace_ev(0, 5, q, g, ntr);
+                        }
 #pragma unroll
                         for (int gate = 0; gate < 4; ++gate) {
                             uint2 hi2, lo2;
@@ -770,9 +819,15 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                             fence_proxy_async();
                             __syncwarp();
                             if (lane == 0) mbar_arrive(&da_full[buf]);
+                            if (tracer) trace_ev(0, 6, q, g, ntr);
                         }
                         db[q][hp] += warp_transpose_sum16(av, lane);          // bias gradient over the warp's 32 rows
                     }
+                    if (tracer) trace_ev(0, 7, q, g, ntr);
+                }
+                if (EPI_LOADS) {
+                    if (t > 0) stage_image(tile, t - 1, g + 1);
+                    else if (tile + gridDim.x < ntiles) stage_image(tile + gridDim.x, T - 1, g + 1);
                 }
             }
             read_back(g - 1, row, live, 0);                 // dx_0 of this tile; releases d for the next tile
@@ -812,10 +867,13 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const float inv_keep = 1.0f / (1.0f - p);
         const int rg_r = lane >> 2, qq = lane & 3;
         int64_t g = 0;
+        int ntr = 0;
+        const bool tracer = lw == 0 && lane == 0;
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int64_t r0 = tile * TM;
             const int64_t rows_live = N - r0;
             for (int t = T - 1; t >= 0; --t, ++g) {
+                if (tracer) trace_ev(1, 0, 0, g, ntr);
                 if (c_tc_prefetch && lw == 0 && lane == 0 && t >= 1) {
                     // pull the NEXT step's rows (x_{t-1}, h_{t-2}, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
                     const int64_t nrow = rows_live < TM ? rows_live : TM;
@@ -827,6 +885,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     }
                     if (d_out) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
                 }
+                if (EPI_LOADS) continue;               // the epilogue warps stage the image; this warp only prefetches
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
@@ -866,6 +925,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     tile_load<4>(v, xsrc, rows_live, lw * 8, lane);
                     if (drop) tile_load_bits<4>(m, bsrc, rows_live, lw * 8, lane);
                     if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
+                    if (tracer) trace_ev(1, 1, 0, g, ntr);
                     tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8, lane, drop, m, inv_keep);
                     tile_load<4>(v, xsrc, rows_live, lw * 8 + 4, lane);
                     if (drop) tile_load_bits<4>(m, bsrc, rows_live, lw * 8 + 4, lane);
@@ -878,17 +938,25 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&xh_full[buf]);
+                if (tracer) trace_ev(1, 2, 0, g, ntr);
             }
         }
     } else if (warp == BW_EPI_WARPS + LOADER_WARPS) {
-        // ===================================== MMA issuer =========================================================
+        // ===================================== MMA issuer A: dgrad + gate recompute ===============================
+        // Descriptors are built once; per MMA only a 64-bit add of a compile-time offset remains (the single issuing
+        // thread is on the critical path of the recurrence).
         if (lane == 0 && total_q > 0) {
             constexpr uint32_t idesc_a = make_idesc_bf16(TM, 64, 0, 0);       // recompute of one quarter
             constexpr uint32_t idesc_d = make_idesc_bf16(TM, ND, 0, 1);       // dgrad: A K-major, B MN-major
-            constexpr uint32_t idesc_w = make_idesc_bf16(TM, 64, 1, 1);       // wgrad: both MN-major
             const uint32_t s_base = smem_u32(smem);
-            const uint32_t w_hi = s_base + S::off_w, w_lo = w_hi + S::WB;
-            auto xh_of = [&](int64_t step) { return s_base + S::off_xh + ((uint32_t)(step % XB) * NSPLIT) * S::XHB; };
+            const uint32_t mn_off = LAYER0 ? (uint32_t)(KX / 8) * LBO_BYTES : 0u;   // layer 0 dgrad: only the h columns of Wcat
+            const uint64_t wk_hi = make_desc(s_base + S::off_w, LBO_BYTES, SBO_W), wk_lo = wk_hi + (S::WB >> 4);
+            const uint64_t wm_hi = make_desc(s_base + S::off_w + mn_off, SBO_W, LBO_BYTES), wm_lo = wm_hi + (S::WB >> 4);
+            uint64_t xk_hi[XB], dak_hi[DB];
+#pragma unroll
+            for (int b = 0; b < XB; ++b) xk_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, LBO_BYTES, SBO_W);
+#pragma unroll
+            for (int b = 0; b < DB; ++b) dak_hi[b] = make_desc(s_base + S::off_da + (b * NSPLIT) * S::DAB, LBO_BYTES, SBO_DA);
             // gates of running quarter nq -> TMEM slot nq & 1 (waits for the slot to be read out and for the image of its step)
             auto issue_recompute = [&](int64_t nq) {
                 const int64_t ng = nq >> 2;
@@ -896,74 +964,103 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 if (q == 0 || (XB == 1 && q == 1)) mbar_wait(&xh_full[ng % XB], (uint32_t)((ng / XB) & 1));
                 if (nq >= 2) mbar_wait(&a_free[slot], (uint32_t)(((nq >> 1) - 1) & 1));
                 tc_fence_after();
-                const uint32_t xh_hi = xh_of(ng), xh_lo = xh_hi + S::XHB;
+                const uint64_t xh = xk_hi[ng % XB], xl = xh + (S::XHB >> 4);
                 const uint32_t d = tmem_base + TMEM_A + 64 * slot;
-                const uint32_t wrow = (uint32_t)(q * 64 / 8) * SBO_W;
+                const uint64_t wrow = (uint64_t)(((uint32_t)(q * 64 / 8) * SBO_W) >> 4);
+                const uint64_t wh = wk_hi + wrow, wl = wk_lo + wrow;
 #pragma unroll
                 for (int ks = 0; ks < KC / 16; ++ks) {
-                    const uint32_t ko = ks * 2 * LBO_BYTES;
-                    umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, ks > 0 ? 1u : 0u);
+                    const uint64_t ko = (uint64_t)((ks * 2 * LBO_BYTES) >> 4);
+                    umma_bf16(d, xh + ko, wh + ko, idesc_a, ks > 0 ? 1u : 0u);
                     if (NSPLIT == 2) {
-                        umma_bf16(d, make_desc(xh_lo + ko, LBO_BYTES, SBO_W), make_desc(w_hi + wrow + ko, LBO_BYTES, SBO_W), idesc_a, 1);
-                        umma_bf16(d, make_desc(xh_hi + ko, LBO_BYTES, SBO_W), make_desc(w_lo + wrow + ko, LBO_BYTES, SBO_W), idesc_a, 1);
+                        umma_bf16(d, xl + ko, wh + ko, idesc_a, 1);
+                        umma_bf16(d, xh + ko, wl + ko, idesc_a, 1);
                     }
                 }
                 umma_commit(&a_full[slot]);
+                if (q == 3) umma_commit(&xh_free[ng % XB]);     // this issuer's last read of the step's image
             };
+            int ntr = 0;
             issue_recompute(0);
             issue_recompute(1);
             for (int64_t qi = 0; qi < total_q; ++qi) {
                 const int64_t g = qi >> 2;
                 const int q = (int)(qi & 3);
-                const uint32_t xh_hi = xh_of(g), xh_lo = xh_hi + S::XHB;
                 const int buf = (int)(qi % DB);
+                trace_ev(2, 0, q, g, ntr);
                 mbar_wait(&da_full[buf], (uint32_t)((qi / DB) & 1));
                 if (q == 0 && g > 0) mbar_wait(d_free, (uint32_t)((g - 1) & 1));
                 tc_fence_after();
-                const uint32_t da_hi = s_base + S::off_da + (buf * NSPLIT) * S::DAB, da_lo = da_hi + S::DAB;
-                // ---- dgrad partial (on the dh critical path: issued first).  K = the four 16-row runs of this quarter
+                trace_ev(2, 1, q, g, ntr);
+                // ---- dgrad partial (on the dh critical path).  K = the four 16-row runs of this quarter of Wcat
                 {
                     const uint32_t d = tmem_base + TMEM_D;
-                    const uint32_t mn_off = LAYER0 ? (uint32_t)(KX / 8) * LBO_BYTES : 0u;   // layer 0: only the h columns of Wcat
+                    const uint64_t dah = dak_hi[buf], dal = dah + (S::DAB >> 4);
 #pragma unroll
                     for (int gate = 0; gate < 4; ++gate) {
-                        const uint32_t wk = (uint32_t)((q * 64 + gate * 16) / 8) * SBO_W + mn_off;
-                        const uint32_t ak = gate * 2 * LBO_BYTES;
-                        const uint32_t acc = (q > 0 || gate > 0) ? 1u : 0u;
-                        umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, acc);
+                        const uint64_t wk = (uint64_t)(((uint32_t)((q * 64 + gate * 16) / 8) * SBO_W) >> 4);
+                        const uint64_t ak = (uint64_t)((gate * 2 * LBO_BYTES) >> 4);
+                        umma_bf16(d, dah + ak, wm_hi + wk, idesc_d, (q > 0 || gate > 0) ? 1u : 0u);
                         if (NSPLIT == 2) {
-                            umma_bf16(d, make_desc(da_lo + ak, LBO_BYTES, SBO_DA), make_desc(w_hi + wk, SBO_W, LBO_BYTES), idesc_d, 1);
-                            umma_bf16(d, make_desc(da_hi + ak, LBO_BYTES, SBO_DA), make_desc(w_lo + wk, SBO_W, LBO_BYTES), idesc_d, 1);
+                            umma_bf16(d, dal + ak, wm_hi + wk, idesc_d, 1);
+                            umma_bf16(d, dah + ak, wm_lo + wk, idesc_d, 1);
                         }
                     }
                     if (q == 3) umma_commit(d_full);
+                    umma_commit(&da_free[buf]);           // first of two arrivals (the wgrad issuer gives the second)
                 }
+                trace_ev(2, 2, q, g, ntr);
                 // ---- gates two quarters ahead (same step, or the next step when its image is already staged) ----------
                 {
                     const int64_t nq = qi + 2;
                     if (nq < total_q && (q < 2 || XB == 2)) issue_recompute(nq);
                 }
-                // ---- wgrad partial: dWcat^T[:, quarter columns] += xh^T * da_quarter, K = the 128 rows of the tile ----
-                {
-                    const uint32_t d = tmem_base + TMEM_DW + q * 64;
-                    const uint32_t acc = g > 0 ? 1u : 0u;
-#pragma unroll
-                    for (int ks = 0; ks < TM / 16; ++ks) {
-                        const uint32_t xo = ks * 2 * SBO_W, dao = ks * 2 * SBO_DA;
-                        umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, (acc | (ks > 0)) ? 1u : 0u);
-                        if (NSPLIT == 2) {
-                            umma_bf16(d, make_desc(xh_lo + xo, SBO_W, LBO_BYTES), make_desc(da_hi + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
-                            umma_bf16(d, make_desc(xh_hi + xo, SBO_W, LBO_BYTES), make_desc(da_lo + dao, SBO_DA, LBO_BYTES), idesc_w, 1);
-                        }
-                    }
-                    umma_commit(&da_free[buf]);
-                    if (q == 3) umma_commit(&xh_free[g % XB]);
-                }
+                trace_ev(2, 3, q, g, ntr);
                 // single-buffered image: the next step's first two quarters can only be recomputed after the reload
                 if (XB == 1 && q == 3 && qi + 1 < total_q) {
                     issue_recompute(qi + 1);
                     issue_recompute(qi + 2);
+                    trace_ev(2, 5, q, g, ntr);
                 }
+            }
+            umma_commit(done);
+        } else if (lane == 0) {
+            mbar_arrive(done);
+        }
+        __syncwarp();
+    } else {
+        // ===================================== MMA issuer B: wgrad ==================================================
+        if (lane == 0 && total_q > 0) {
+            constexpr uint32_t idesc_w = make_idesc_bf16(TM, 64, 1, 1);       // wgrad: both MN-major
+            const uint32_t s_base = smem_u32(smem);
+            uint64_t xm_hi[XB], dam_hi[DB];
+#pragma unroll
+            for (int b = 0; b < XB; ++b) xm_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, SBO_W, LBO_BYTES);
+#pragma unroll
+            for (int b = 0; b < DB; ++b) dam_hi[b] = make_desc(s_base + S::off_da + (b * NSPLIT) * S::DAB, SBO_DA, LBO_BYTES);
+            int ntr = 0;
+            for (int64_t qi = 0; qi < total_q; ++qi) {
+                const int64_t g = qi >> 2;
+                const int q = (int)(qi & 3);
+                const int buf = (int)(qi % DB);
+                mbar_wait(&da_full[buf], (uint32_t)((qi / DB) & 1));
+                tc_fence_after();
+                // dWcat^T[:, quarter columns] += xh^T * da_quarter, K = the 128 rows of the tile
+                const uint32_t d = tmem_base + TMEM_DW + q * 64;
+                const uint64_t xh = xm_hi[g % XB], xl = xh + (S::XHB >> 4);
+                const uint64_t dah = dam_hi[buf], dal = dah + (S::DAB >> 4);
+#pragma unroll
+                for (int ks = 0; ks < TM / 16; ++ks) {
+                    const uint64_t xo = (uint64_t)((ks * 2 * SBO_W) >> 4), dao = (uint64_t)((ks * 2 * SBO_DA) >> 4);
+                    umma_bf16(d, xh + xo, dah + dao, idesc_w, (g > 0 || ks > 0) ? 1u : 0u);
+                    if (NSPLIT == 2) {
+                        umma_bf16(d, xl + xo, dah + dao, idesc_w, 1);
+                        umma_bf16(d, xh + xo, dal + dao, idesc_w, 1);
+                    }
+                }
+                umma_commit(&da_free[buf]);               // second arrival
+                if (q == 3) umma_commit(&xh_free[g % XB]);
+                trace_ev(3, 4, q, g, ntr);
             }
             umma_commit(done);
         } else if (lane == 0) {
@@ -1232,6 +1329,13 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
 }  // namespace b200
 
 using namespace b200;
+
+// Debug: trace buffer of 4 * TRACE_CAP * 16 bytes (device) or NULL to switch tracing off.
+extern "C" int b200_debug_trace(void* device_buffer) {
+    unsigned long long* p = (unsigned long long*)device_buffer;
+    B200_CUDA(cudaMemcpyToSymbol(c_trace, &p, sizeof(p)));
+    return B200_OK;
+}
 
 // see tc_selftest_kernel; fp32 in/out, bf16x3 split inside
 extern "C" int b200_tc_selftest(const float* A, const float* B, int variant, int K, int Nn, float* D, void* stream) {
