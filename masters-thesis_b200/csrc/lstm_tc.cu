@@ -648,9 +648,9 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const uint32_t row_off = (uint32_t)(r >> 3) * SBO_DA + (uint32_t)(r & 7) * 16;
         const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
-        float dc[4][8], dh[4][8], db[4][2];
+        float dc[4][8], dh[4][8], db[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) db[q][0] = db[q][1] = 0.f;
+        for (int q = 0; q < 4; ++q) db[q] = 0.f;
 
         // read back [dx | dh] of step (tile row, t_done): dh -> registers, dx -> masked store; then release d
         auto read_back = [&](int64_t g_done, int64_t row, bool live, int t_done) {
@@ -732,9 +732,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     const int u0 = 16 * q + 8 * grp;                         // first hidden unit of this thread's slice
                     const int64_t qi = 4 * g + q;                              // running quarter index
                     const int slot = q & 1;
-                    float ct[8], cp[8], dq[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) { ct[i] = nct[i]; cp[i] = ncp[i]; dq[i] = ndq[i]; }
                     if (tracer) trace_ev(0, 0, q, g, ntr);
                     mbar_wait(&a_full[slot], (uint32_t)((qi >> 1) & 1));
                     tc_fence_after();
@@ -742,87 +739,80 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     const int buf = (int)(qi % DB);
                     uint8_t* da_hi = smem + S::off_da + (buf * NSPLIT) * S::DAB;
                     uint8_t* da_lo = da_hi + S::DAB;
-                    // the 8 units of the slice are processed as two passes of 4 (register budget); each pass has a part that
-                    // does not depend on the dh recurrence (A: gates, tanh(c_t)) and a part that does (B: da)
+                    float av[4][8];
+                    const uint32_t acol = TMEM_A + 64 * slot + 8 * grp;
 #pragma unroll
-                    for (int hp = 0; hp < 2; ++hp) {
-                        float av[4][4];
-                        const uint32_t acol = TMEM_A + 64 * slot + 8 * grp + 4 * hp;
+                    for (int gate = 0; gate < 4; ++gate) tmem_ld8(lane_addr + acol + gate * 16, av[gate]);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&a_free[slot]);                // slot read out
+                    // ---- part A (independent of the dh recurrence): D = 1 + 2^(...) of the four gates and of c_t ------
+                    float Dc[8], r1[8], r2[8];
 #pragma unroll
-                        for (int gate = 0; gate < 4; ++gate) tmem_ld4(lane_addr + acol + gate * 16, av[gate]);
-                        tmem_ld_wait();
-                        if (hp == 1) {                       // slot fully read out
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(&a_free[slot]);
-                            if (q < 3) issue_loads(t, q + 1); else issue_loads(t - 1, 0);
-                        }
-                        float Ec[4], r1[4], r2[4];
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (u0 + 4 * hp + i));
-                            av[0][i] = fminf(fmaf(av[0][i], -LOG2E, b4.x), EXP_CLAMP);
-                            av[1][i] = fminf(fmaf(av[1][i], -LOG2E, b4.y), EXP_CLAMP);
-                            av[2][i] = fminf(fmaf(av[2][i], 2.f * LOG2E, b4.z), EXP_CLAMP);
-                            av[3][i] = fminf(fmaf(av[3][i], -LOG2E, b4.w), EXP_CLAMP);
-                            Ec[i] = fminf(2.f * LOG2E * ct[4 * hp + i], EXP_CLAMP);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            av[0][i] = ex2a(av[0][i]); av[1][i] = ex2a(av[1][i]); av[2][i] = ex2a(av[2][i]); av[3][i] = ex2a(av[3][i]);
-                            Ec[i] = ex2a(Ec[i]);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            r1[i] = (1.f + av[0][i]) * (1.f + av[1][i]) * (1.f + av[2][i]);
-                            r2[i] = (1.f + av[3][i]) * (1.f + Ec[i]);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) { r1[i] = rcpa(r1[i]); r2[i] = rcpa(r2[i]); }
-                        // dh of this step arrives from the previous step's dgrad (first pass of the first quarter only)
-                        if (q == 0 && hp == 0 && t < T - 1) {
-                            if (tracer) trace_ev(0, 2, q, g, ntr);
-                            read_back(g - 1, row, live, t + 1);
-                            if (tracer) trace_ev(0, 3, q, g, ntr);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const int ii = 4 * hp + i;
-                            const float Di = 1.f + av[0][i], Df = 1.f + av[1][i], Dg = 1.f + av[2][i], Do = 1.f + av[3][i], Dc = 1.f + Ec[i];
-                            const float t1 = r1[i] * Dg;
-                            const float ig = t1 * Df, fg = t1 * Di, gg = (av[2][i] - 1.f) * (r1[i] * (Di * Df));
-                            const float og = r2[i] * Dc, tc = (Ec[i] - 1.f) * (r2[i] * Do);
-                            const float dhv = dh[q][ii] + dq[ii];
-                            const float d_o = dhv * tc;
-                            const float dcc = dc[q][ii] + dhv * og * (1.f - tc * tc);
-                            dc[q][ii] = dcc * fg;
-                            av[0][i] = live ? dcc * gg * ig * (1.f - ig) : 0.f;
-                            av[1][i] = live ? dcc * cp[ii] * fg * (1.f - fg) : 0.f;
-                            av[2][i] = live ? dcc * ig * (1.f - gg * gg) : 0.f;
-                            av[3][i] = live ? d_o * og * (1.f - og) : 0.f;
-                        }
-                        // operand image: column kk = gate * 16 + 8 * grp + 4 * hp + i -> 16-byte chunk gate * 2 + grp, 8-byte half hp
-                        if (hp == 0 && qi >= DB) {
-                            if (tracer) trace_ev(0, 4, q, g, ntr);
-                            mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
-                            if (tracer) trace_ev(0, 5, q, g, ntr);
-                        }
-#pragma unroll
-                        for (int gate = 0; gate < 4; ++gate) {
-                            uint2 hi2, lo2;
-                            split2x2(av[gate][0], av[gate][1], av[gate][2], av[gate][3], hi2, lo2);
-                            const uint32_t o = row_off + (uint32_t)(gate * 2 + grp) * LBO_BYTES + 8 * hp;
-                            *reinterpret_cast<uint2*>(da_hi + o) = hi2;
-                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(da_lo + o) = lo2;
-                        }
-                        if (hp == 1) {
-                            fence_proxy_async();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(&da_full[buf]);
-                            if (tracer) trace_ev(0, 6, q, g, ntr);
-                        }
-                        db[q][hp] += warp_transpose_sum16(av, lane);          // bias gradient over the warp's 32 rows
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (u0 + i));
+                        av[0][i] = fminf(fmaf(av[0][i], -LOG2E, b4.x), EXP_CLAMP);
+                        av[1][i] = fminf(fmaf(av[1][i], -LOG2E, b4.y), EXP_CLAMP);
+                        av[2][i] = fminf(fmaf(av[2][i], 2.f * LOG2E, b4.z), EXP_CLAMP);
+                        av[3][i] = fminf(fmaf(av[3][i], -LOG2E, b4.w), EXP_CLAMP);
+                        Dc[i] = fminf(2.f * LOG2E * nct[i], EXP_CLAMP);
                     }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        av[0][i] = 1.f + ex2a(av[0][i]); av[1][i] = 1.f + ex2a(av[1][i]); av[2][i] = 1.f + ex2a(av[2][i]);
+                        av[3][i] = 1.f + ex2a(av[3][i]); Dc[i] = 1.f + ex2a(Dc[i]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) { r1[i] = rcpa(av[0][i] * av[1][i] * av[2][i]); r2[i] = rcpa(av[3][i] * Dc[i]); }
+                    // ---- dh of this step arrives from the previous step's dgrad (first quarter only) -----------------
+                    if (q == 0 && t < T - 1) {
+                        if (tracer) trace_ev(0, 2, q, g, ntr);
+                        read_back(g - 1, row, live, t + 1);
+                        if (tracer) trace_ev(0, 3, q, g, ntr);
+                    }
+                    // ---- part B: gates by batch inversion, cell/gate derivatives -> da quarter ---------------------------
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float Di = av[0][i], Df = av[1][i], Dg = av[2][i], Do = av[3][i];
+                        const float t1 = r1[i] * Dg;
+                        const float ig = t1 * Df, fg = t1 * Di, gg = (Dg - 2.f) * (r1[i] * (Di * Df));
+                        const float og = r2[i] * Dc[i], tc = (Dc[i] - 2.f) * (r2[i] * Do);
+                        const float dhv = dh[q][i] + ndq[i];
+                        const float d_o = dhv * tc;
+                        const float dcc = dc[q][i] + dhv * og * (1.f - tc * tc);
+                        dc[q][i] = dcc * fg;
+                        av[0][i] = live ? dcc * gg * ig * (1.f - ig) : 0.f;
+                        av[1][i] = live ? dcc * ncp[i] * fg * (1.f - fg) : 0.f;
+                        av[2][i] = live ? dcc * ig * (1.f - gg * gg) : 0.f;
+                        av[3][i] = live ? d_o * og * (1.f - og) : 0.f;
+                    }
+                    // the next quarter's global operands (this quarter's are consumed)
+                    if (q < 3) issue_loads(t, q + 1); else issue_loads(t - 1, 0);
+                    // operand image of this quarter: column kk = gate * 16 + 8 * grp + i  ->  16-byte chunk gate * 2 + grp
+                    if (qi >= DB) {
+                        if (tracer) trace_ev(0, 4, q, g, ntr);
+                        mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
+                        if (tracer) trace_ev(0, 5, q, g, ntr);
+                    }
+#pragma unroll
+                    for (int gate = 0; gate < 4; ++gate) {
+                        uint4 hi4, lo4;
+                        split2(av[gate][0], av[gate][1], hi4.x, lo4.x);
+                        split2(av[gate][2], av[gate][3], hi4.y, lo4.y);
+                        split2(av[gate][4], av[gate][5], hi4.z, lo4.z);
+                        split2(av[gate][6], av[gate][7], hi4.w, lo4.w);
+                        const uint32_t o = row_off + (uint32_t)(gate * 2 + grp) * LBO_BYTES;
+                        *reinterpret_cast<uint4*>(da_hi + o) = hi4;
+                        if (NSPLIT == 2) *reinterpret_cast<uint4*>(da_lo + o) = lo4;
+                    }
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&da_full[buf]);
+                    if (tracer) trace_ev(0, 6, q, g, ntr);
+                    // bias gradient: layer 0 gets it from the tensor core (constant-one column of the x image, see the
+                    // loader); other layers reduce da over the warp's 32 rows here
+                    if (!LAYER0) db[q] += warp_transpose_sum32(av, lane);
                     if (tracer) trace_ev(0, 7, q, g, ntr);
                 }
                 if (EPI_LOADS) {
@@ -835,13 +825,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         // ---- final: bias-gradient partials and the weight-gradient accumulator ---------------------------------------
         {
             float* bp = bpart + ((int64_t)blockIdx.x * 4 + wq) * TG;
-            // lane pair (2m, 2m+1) holds value index m = gate * 4 + i of each 4-unit pass
-            if ((lane & 1) == 0) {
-                const int m = lane >> 1, gate = m >> 2, i = m & 3;
+            // lane L holds value index L = gate * 8 + i of each quarter (layer 0: zeros, its bias gradient is row KIN_ONE
+            // of the weight-gradient accumulator and is written below)
+            if (!(LAYER0 && wq == 0)) {                 // layer 0, slot wq == 0 is written from the accumulator row below
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
-#pragma unroll
-                    for (int hp = 0; hp < 2; ++hp) bp[gate * TH + 16 * q + 8 * grp + 4 * hp + i] = db[q][hp];
+                for (int q = 0; q < 4; ++q) bp[(lane >> 3) * TH + 16 * q + 8 * grp + (lane & 7)] = db[q];
             }
         }
         mbar_wait(done, 0u);
@@ -857,6 +845,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     const int q = c0 >> 6, kk = c0 & 63, gate = kk >> 4, i0 = kk & 15;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) wp[(gate * TH + 16 * q + i0 + i) * 128 + kcat] = my_tiles > 0 ? v[i] : 0.f;
+                    if (LAYER0 && kcat == kin) {              // row of the constant-one column = sum over rows and steps of da
+                        float* bp = bpart + ((int64_t)blockIdx.x * 4 + wq) * TG;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) bp[gate * TH + 16 * q + i0 + i] = my_tiles > 0 ? v[i] : 0.f;
+                    }
                 }
             }
         }
@@ -909,7 +902,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         if (rr < rows_live) {
                             const float* src = xin + ((int64_t)t * N + r0 + rr) * kin;
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) if (4 * qq + i < kin) x4[i] = src[4 * qq + i];
+                            for (int i = 0; i < 4; ++i) {
+                                if (4 * qq + i < kin) x4[i] = src[4 * qq + i];
+                                else if (4 * qq + i == kin) x4[i] = 1.0f;      // constant-one column: its weight-gradient row is the bias gradient
+                            }
                         }
                         uint2 hi2, lo2;
                         split2(x4[0], x4[1], hi2.x, lo2.x);

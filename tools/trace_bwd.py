@@ -25,7 +25,7 @@ for layer in (1, 0):
     torch.cuda.synchronize()
     if layer == a.layer: rec = buf.cpu().numpy().view(np.uint64).reshape(4, CAP, 2).copy()
 check(lib.b200_debug_trace(None), "trace")
-names = {0: {0: "epi.wait_a", 1: "epi.a_ready", 2: "epi.rb_start", 3: "epi.rb_done", 4: "epi.wait_dafree", 5: "epi.dafree_ok", 6: "epi.da_full", 7: "epi.q_done"},
+names = {0: {0: "epi.wait_a", 1: "epi.a_ready", 2: "epi.rb_start", 3: "epi.rb_done", 4: "epi.wait_dafree", 5: "epi.dafree_ok", 6: "epi.da_full", 7: "epi.q_done", 8: "epi.hp1_ld_done", 9: "epi.hp1_loads_issued", 10: "epi.hp1_sts_done"},
          1: {0: "ld.begin", 1: "ld.xhfree_ok", 2: "ld.xh_full"},
          3: {4: "mmaB.wgrad_issued"},
          2: {0: "mma.wait_da", 1: "mma.da_ok", 2: "mma.dgrad_issued", 3: "mma.recomp_issued", 4: "mma.wgrad_issued", 5: "mma.next_recomp_issued"}}
