@@ -155,3 +155,12 @@ def test_grad_bucketer_world2_gloo(tmp_path):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "ok" in o
+
+
+def test_sweep_plan_assigns_one_gpu_per_job():
+    sys.path.insert(0, str(ROOT / "sweeps"))
+    import run_sweep
+    jobs = run_sweep.plan(["datamodule=synthetic", "model=small,medium,large", "loss=mse,nll,combined", "trainer=b200"], 8)
+    assert len(jobs) == 9
+    assert [j["gpu"] for j in jobs] == [0, 1, 2, 3, 4, 5, 6, 7, 0]
+    assert jobs[4]["overrides"] == ["datamodule=synthetic", "model=medium", "loss=nll", "trainer=b200"]
