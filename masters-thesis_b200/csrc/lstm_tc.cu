@@ -214,8 +214,9 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     constexpr int KX = S::KX;
     constexpr int EPI_WARPS = 4 * NTILE;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
+    // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
+    extern __shared__ __align__(1024) uint8_t smem[];
     float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::off_bar);      // [slot][0 x_full, 1 h_ready, 2 acc_full]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
@@ -593,8 +594,9 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // epilogue warps are idle: they then stage the next image themselves (2 row groups each, loads issued before the
     // buffer is released) and the loader warps only prefetch into L2.
     constexpr bool EPI_LOADS = (XB == 1) && !LAYER0;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
+    // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
+    extern __shared__ __align__(1024) uint8_t smem[];
     float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::off_bar);
     uint64_t* xh_full = bars;               // [XB]   loader -> MMA: [x_t | h_{t-1}] image staged
@@ -1078,8 +1080,9 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 // roles of the two strides: LBO = stride between 8-row groups (the K direction), SBO = 128 (next 8 columns).
 __global__ void __launch_bounds__(128, 1)
 tc_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B, int variant, int K, int Nn, float* __restrict__ D) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+    // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
+    // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
+    extern __shared__ __align__(1024) uint8_t smem[];
     // image shapes (rows, cols)
     const int a_rows = variant == 2 ? K : TM, a_cols = variant == 2 ? TM : K;
     const int b_rows = variant == 0 ? Nn : K, b_cols = variant == 0 ? K : Nn;
