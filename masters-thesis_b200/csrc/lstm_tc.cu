@@ -196,15 +196,18 @@ struct FwdSmem {
     static constexpr int KX = kx_of(LAYER0);
     static constexpr uint32_t WIN = op_bytes(TG, KX), WHH = op_bytes(TG, TH);
     static constexpr uint32_t XB = op_bytes(TM, KX), HB = op_bytes(TM, TH);
-    // offsets (bytes) from the 128-byte aligned base
+    // Two tiles of a precise-mode layer > 0 do not fit with an x buffer each (256 KB): they share ONE x buffer, which is
+    // only live between the loader's store and the completion of the tile's input-projection MMAs (x_free barrier).
+    static constexpr bool XSHARE = NTILE == 2 && NSPLIT == 2 && !LAYER0;
+    static constexpr int NXBUF = XSHARE ? 1 : NTILE;
     static constexpr uint32_t off_win = 0;                                  // [NSPLIT] images
     static constexpr uint32_t off_whh = off_win + NSPLIT * WIN;             // [NSPLIT]
-    static constexpr uint32_t off_x = off_whh + NSPLIT * WHH;               // [NTILE][NSPLIT]
-    static constexpr uint32_t off_h = off_x + NTILE * NSPLIT * XB;          // [NTILE][NSPLIT]
+    static constexpr uint32_t off_x = off_whh + NSPLIT * WHH;               // [NXBUF][NSPLIT]
+    static constexpr uint32_t off_h = off_x + NXBUF * NSPLIT * XB;          // [NTILE][NSPLIT]
     static constexpr uint32_t off_bias = off_h + NTILE * NSPLIT * HB;       // 256 floats
-    static constexpr uint32_t off_bar = off_bias + TG * 4;                  // 3 * NTILE mbarriers
-    static constexpr uint32_t off_tmem = off_bar + 3 * NTILE * 8;
-    static constexpr uint32_t total = off_tmem + 16 + 128;                  // + alignment slack
+    static constexpr uint32_t off_bar = off_bias + TG * 4;                  // 3 * NTILE + 1 mbarriers
+    static constexpr uint32_t off_tmem = off_bar + (3 * NTILE + 1) * 8;
+    static constexpr uint32_t total = off_tmem + 16 + 128;
 };
 
 template <int NSPLIT, int NTILE, bool LAYER0>
@@ -219,7 +222,9 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     extern __shared__ __align__(1024) uint8_t smem[];
     float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::off_bar);      // [slot][0 x_full, 1 h_ready, 2 acc_full]
+    uint64_t* x_free = bars + 3 * NTILE;                                  // XSHARE: input-projection MMAs of a tile-step done
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+    constexpr bool XSHARE = S::XSHARE;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -241,6 +246,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             mbar_init(&bars[s * 3 + 1], 4);
             mbar_init(&bars[s * 3 + 2], 1);
         }
+        mbar_init(x_free, 1);
         fence_barrier_init();
     }
     if (warp == EPI_WARPS + LOADER_WARPS) tmem_alloc(tmem_slot, NTILE * TG);
@@ -362,8 +368,9 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 #pragma unroll
                 for (int slot = 0; slot < NTILE; ++slot) {
                     const int64_t tile = grp * NTILE + slot;
-                    uint8_t* x_hi = smem + S::off_x + (slot * NSPLIT) * S::XB;
+                    uint8_t* x_hi = smem + S::off_x + ((XSHARE ? 0 : slot) * NSPLIT) * S::XB;
                     uint8_t* x_lo = x_hi + S::XB;
+                    const int64_t xuse = g * NTILE + slot;                     // running use index of the shared x buffer
                     if (!LAYER0) {
                         // all global loads of the tile are issued before the wait for the x buffer
                         const int64_t r0 = tile * TM;
@@ -372,7 +379,8 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         uint64_t m[8];
                         tile_load<8>(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw * 8, lane);
                         if (drop) tile_load_bits<8>(m, drop_bits + (int64_t)t * N + r0, rows_live, lw * 8, lane);
-                        if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));   // MMA of the previous step consumed x
+                        if (XSHARE) { if (xuse > 0) mbar_wait(x_free, (uint32_t)((xuse - 1) & 1)); }   // previous user's x MMAs done
+                        else if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));       // MMA of the previous step consumed x
                         tile_store<NSPLIT, 8>(v, x_hi, x_lo, sbo_of(KX), 0, lw * 8, lane, drop, m, inv_keep);
                     }
                     if (LAYER0 && g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));
@@ -415,6 +423,15 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc_bf16(TM, TG);
             const uint32_t s_base = smem_u32(smem);
+            // descriptors are built once; per MMA only 64-bit adds of compile-time offsets remain
+            const uint64_t win_hi = make_desc(s_base + S::off_win, LBO_BYTES, sbo_of(KX)), win_lo = win_hi + (S::WIN >> 4);
+            const uint64_t whh_hi = make_desc(s_base + S::off_whh, LBO_BYTES, sbo_of(TH)), whh_lo = whh_hi + (S::WHH >> 4);
+            uint64_t xd[NTILE], hd[NTILE];
+#pragma unroll
+            for (int sl = 0; sl < NTILE; ++sl) {
+                xd[sl] = make_desc(s_base + S::off_x + ((XSHARE ? 0 : sl) * NSPLIT) * S::XB, LBO_BYTES, sbo_of(KX));
+                hd[sl] = make_desc(s_base + S::off_h + (sl * NSPLIT) * S::HB, LBO_BYTES, sbo_of(TH));
+            }
             for (int64_t g = 0; g < total_steps; ++g) {
                 const bool first = (g % T) == 0;              // t == 0: h_{-1} = 0, skip the recurrent K-steps
 #pragma unroll
@@ -423,29 +440,26 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     if (g > 0) mbar_wait(&bars[slot * 3 + 1], (uint32_t)((g - 1) & 1));   // h_{t-1} staged, TMEM drained
                     tc_fence_after();
                     const uint32_t d = tmem_base + (uint32_t)(slot * TG);
-                    const uint32_t x_hi = s_base + S::off_x + (slot * NSPLIT) * S::XB, x_lo = x_hi + S::XB;
-                    const uint32_t h_hi = s_base + S::off_h + (slot * NSPLIT) * S::HB, h_lo = h_hi + S::HB;
-                    const uint32_t win_hi = s_base + S::off_win, win_lo = win_hi + S::WIN;
-                    const uint32_t whh_hi = s_base + S::off_whh, whh_lo = whh_hi + S::WHH;
-                    uint32_t acc = 0;
+                    const uint64_t x_hi = xd[slot], x_lo = x_hi + (S::XB >> 4);
+                    const uint64_t h_hi = hd[slot], h_lo = h_hi + (S::HB >> 4);
 #pragma unroll
                     for (int ks = 0; ks < KX / 16; ++ks) {
-                        const uint32_t ko = ks * 2 * LBO_BYTES;
-                        umma_bf16(d, make_desc(x_hi + ko, LBO_BYTES, sbo_of(KX)), make_desc(win_hi + ko, LBO_BYTES, sbo_of(KX)), idesc, acc);
-                        acc = 1;
+                        const uint64_t ko = (uint64_t)((ks * 2 * LBO_BYTES) >> 4);
+                        umma_bf16(d, x_hi + ko, win_hi + ko, idesc, ks > 0 ? 1u : 0u);
                         if (NSPLIT == 2) {
-                            umma_bf16(d, make_desc(x_lo + ko, LBO_BYTES, sbo_of(KX)), make_desc(win_hi + ko, LBO_BYTES, sbo_of(KX)), idesc, 1);
-                            umma_bf16(d, make_desc(x_hi + ko, LBO_BYTES, sbo_of(KX)), make_desc(win_lo + ko, LBO_BYTES, sbo_of(KX)), idesc, 1);
+                            umma_bf16(d, x_lo + ko, win_hi + ko, idesc, 1);
+                            umma_bf16(d, x_hi + ko, win_lo + ko, idesc, 1);
                         }
                     }
+                    if (XSHARE) umma_commit(x_free);          // the shared x buffer may be refilled for the other tile
                     if (!first) {
 #pragma unroll
                         for (int ks = 0; ks < TH / 16; ++ks) {
-                            const uint32_t ko = ks * 2 * LBO_BYTES;
-                            umma_bf16(d, make_desc(h_hi + ko, LBO_BYTES, sbo_of(TH)), make_desc(whh_hi + ko, LBO_BYTES, sbo_of(TH)), idesc, 1);
+                            const uint64_t ko = (uint64_t)((ks * 2 * LBO_BYTES) >> 4);
+                            umma_bf16(d, h_hi + ko, whh_hi + ko, idesc, 1);
                             if (NSPLIT == 2) {
-                                umma_bf16(d, make_desc(h_lo + ko, LBO_BYTES, sbo_of(TH)), make_desc(whh_hi + ko, LBO_BYTES, sbo_of(TH)), idesc, 1);
-                                umma_bf16(d, make_desc(h_hi + ko, LBO_BYTES, sbo_of(TH)), make_desc(whh_lo + ko, LBO_BYTES, sbo_of(TH)), idesc, 1);
+                                umma_bf16(d, h_lo + ko, whh_hi + ko, idesc, 1);
+                                umma_bf16(d, h_hi + ko, whh_lo + ko, idesc, 1);
                             }
                         }
                     }
@@ -1252,7 +1266,7 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
             rc = precise ? launch_fwd<2, 2, true>(pk, xin, kin, N, T, ho, co, nullptr, p, st)
                          : launch_fwd<1, 2, true>(pk, xin, kin, N, T, ho, co, nullptr, p, st);
         } else {
-            rc = precise ? launch_fwd<2, 1, false>(pk, xin, kin, N, T, ho, co, bits, p, st)
+            rc = precise ? launch_fwd<2, 2, false>(pk, xin, kin, N, T, ho, co, bits, p, st)
                          : launch_fwd<1, 2, false>(pk, xin, kin, N, T, ho, co, bits, p, st);
         }
         if (rc) return rc;
