@@ -200,29 +200,30 @@ def run_b200(args):
     # ---- end to end: reference-format batches in pinned host memory -> H2D -> step -> loss D2H ----
     e2e = None
     if not args.no_e2e:
-        ref = [t.cpu().pin_memory() for t in dm.source.generate(first_window=first, n_windows=args.batch).to_reference()]
-        h2d = sum(t.numel() * 4 for t in ref)
+        # two distinct batches in pinned host memory, alternated
+        refs = [[t.cpu().pin_memory() for t in dm.source.generate(first_window=first + i * args.batch, n_windows=args.batch).to_reference()]
+                for i in range(2)]
+        h2d = sum(t.numel() * 4 for t in refs[0])
         e2e_steps = max(2, min(args.steps, 5))
+        feeder = B.HostBatchFeeder(dev)
 
-        def e2e_step():
-            dev_ref = [t.to(dev, non_blocking=True) for t in ref]
-            b = B.DeviceBatch.from_reference(dev_ref, dev)
-            ls = tr.training_step(model, b, LR)
-            return float(ls[2])                      # device -> host read of the step's loss
+        def run_e2e(n):
+            last = None
+            for b in feeder.feed(refs[i % 2] for i in range(n)):
+                last = float(tr.training_step(model, b, LR)[2])     # device -> host read of every step's loss
+            return last
 
-        for _ in range(2):
-            e2e_step()
+        run_e2e(2)
         barrier()
         t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            e2e_step()
+        run_e2e(e2e_steps)
         barrier()
         dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.batch * world * e2e_steps / float(dt), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4, "steps": e2e_steps,
-               "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> cudaMemcpyAsync -> B200Trainer.training_step -> loss.item()"}
+               "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> HostBatchFeeder (cudaMemcpyAsync + layout conversion on a copy stream, one batch ahead) -> B200Trainer.training_step -> loss.item() every step"}
 
     if world > 1:
         dist.barrier()

@@ -7,11 +7,11 @@ CUDA library libb200lstm.so.  The directory name carries a hyphen; import it as
 from . import _lib
 from ._lib import B200Error, LOSS_KINDS, MODES
 from .config import compose_config
-from .data import DeviceBatch, FinancialLstmDataModule
+from .data import DeviceBatch, FinancialLstmDataModule, HostBatchFeeder
 from .engine import LstmEngine
 from .model import FinancialLstm, FinancialLstmCombined, FinancialLstmMse, FinancialLstmNll, get_model_class
 from .trainer import B200Trainer
 
 __all__ = ["B200Error", "B200Trainer", "DeviceBatch", "FinancialLstm", "FinancialLstmCombined",
-           "FinancialLstmDataModule", "FinancialLstmMse", "FinancialLstmNll", "LOSS_KINDS", "LstmEngine",
+           "FinancialLstmDataModule", "FinancialLstmMse", "HostBatchFeeder", "FinancialLstmNll", "LOSS_KINDS", "LstmEngine",
            "MODES", "compose_config", "get_model_class", "_lib"]

@@ -273,6 +273,8 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const uint32_t row_off = (uint32_t)(r >> 3) * sbo_of(TH) + (uint32_t)(r & 7) * 16;
         float cst[TH];
         int64_t g = 0;
+        int ntr = 0;
+        const bool tracer = warp == 0 && lane == 0;
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             const int64_t tile = grp * NTILE + slot;
             const int64_t row = tile * TM + r;
@@ -280,8 +282,10 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 #pragma unroll
             for (int u = 0; u < TH; ++u) cst[u] = 0.f;
             for (int t = 0; t < T; ++t, ++g) {
+                if (tracer) trace_ev(0, 0, 0, g, ntr);
                 mbar_wait(acc_full, (uint32_t)(g & 1));
                 tc_fence_after();
+                if (tracer) trace_ev(0, 1, 0, g, ntr);
                 float* hdst = h_out + ((int64_t)t * N + row) * TH;
                 float* cdst = c_out + ((int64_t)t * N + row) * TH;
 #pragma unroll
@@ -347,6 +351,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 fence_proxy_async();          // h_t visible to the tensor core
                 __syncwarp();
                 if (lane == 0) mbar_arrive(h_ready);
+                if (tracer) trace_ev(0, 6, 0, g, ntr);
             }
         }
     } else if (warp < EPI_WARPS + LOADER_WARPS) {
@@ -355,6 +360,8 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
         int64_t g = 0;
+        int ntr = 0;
+        const bool tracer = lw == 0 && lane == 0;
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             for (int t = 0; t < T; ++t, ++g) {
                 if (c_tc_prefetch && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
@@ -379,8 +386,10 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         uint64_t m[8];
                         tile_load<8>(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw * 8, lane);
                         if (drop) tile_load_bits<8>(m, drop_bits + (int64_t)t * N + r0, rows_live, lw * 8, lane);
+                        if (tracer) trace_ev(1, 0, slot, g, ntr);
                         if (XSHARE) { if (xuse > 0) mbar_wait(x_free, (uint32_t)((xuse - 1) & 1)); }   // previous user's x MMAs done
                         else if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));       // MMA of the previous step consumed x
+                        if (tracer) trace_ev(1, 1, slot, g, ntr);
                         tile_store<NSPLIT, 8>(v, x_hi, x_lo, sbo_of(KX), 0, lw * 8, lane, drop, m, inv_keep);
                     }
                     if (LAYER0 && g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));
@@ -415,6 +424,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     fence_proxy_async();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&bars[slot * 3 + 0]);
+                    if (tracer) trace_ev(1, 2, slot, g, ntr);
                 }
             }
         }
@@ -432,13 +442,17 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 xd[sl] = make_desc(s_base + S::off_x + ((XSHARE ? 0 : sl) * NSPLIT) * S::XB, LBO_BYTES, sbo_of(KX));
                 hd[sl] = make_desc(s_base + S::off_h + (sl * NSPLIT) * S::HB, LBO_BYTES, sbo_of(TH));
             }
+            int ntr = 0;
             for (int64_t g = 0; g < total_steps; ++g) {
                 const bool first = (g % T) == 0;              // t == 0: h_{-1} = 0, skip the recurrent K-steps
 #pragma unroll
                 for (int slot = 0; slot < NTILE; ++slot) {
+                    trace_ev(2, 0, slot, g, ntr);
                     mbar_wait(&bars[slot * 3 + 0], (uint32_t)(g & 1));                    // x_t staged
+                    trace_ev(2, 1, slot, g, ntr);
                     if (g > 0) mbar_wait(&bars[slot * 3 + 1], (uint32_t)((g - 1) & 1));   // h_{t-1} staged, TMEM drained
                     tc_fence_after();
+                    trace_ev(2, 2, slot, g, ntr);
                     const uint32_t d = tmem_base + (uint32_t)(slot * TG);
                     const uint64_t x_hi = xd[slot], x_lo = x_hi + (S::XB >> 4);
                     const uint64_t h_hi = hd[slot], h_lo = h_hi + (S::HB >> 4);
@@ -464,6 +478,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         }
                     }
                     umma_commit(&bars[slot * 3 + 2]);
+                    trace_ev(2, 3, slot, g, ntr);
                 }
             }
         }

@@ -92,6 +92,43 @@ class DeviceBatchSource:
         return a, b
 
 
+class HostBatchFeeder:
+    """Feeds batches that live in pinned HOST memory in the reference DataLoader's layout
+    ([X (B,S,T,F), y (B,S,n,4), factor (B,2), inv_psi (B,S)], src/data.py:236-238) to the device path: the
+    host->device copy and the layout conversion of batch k+1 run on a copy stream while batch k trains."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+
+    def _start(self, host_batch):
+        with torch.cuda.stream(self.copy_stream):
+            dev = [t.to(self.device, non_blocking=True) for t in host_batch]
+            b = DeviceBatch.from_reference(dev, self.device)
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        return b, ev
+
+    def _finish(self, started):
+        b, ev = started
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        for t in (b.x, b.y_stock, b.y_market, b.factor, b.inv_psi):
+            t.record_stream(cur)
+        return b
+
+    def feed(self, host_batches):
+        it = iter(host_batches)
+        try:
+            nxt = self._start(next(it))
+        except StopIteration:
+            return
+        for hb in it:
+            cur, nxt = nxt, self._start(hb)
+            yield self._finish(cur)
+        yield self._finish(nxt)
+
+
 class _Loader:
     """Iterable of DeviceBatch over a window range; mirrors DataLoader(batch_size, shuffle)."""
 
