@@ -34,6 +34,9 @@ def _stale(target: Path, deps) -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
+    flags = list(NVCC_FLAGS)
+    if os.environ.get("B200_TRACE") == "1":          # event tracing of the tcgen05 kernels (tools/trace_*.py); rebuild with --force
+        flags.append("-DB200_TRACE")
     srcs = sorted(CSRC.glob("*.cu"))
     hdrs = sorted(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "b200_lstm.h"]
     OBJ.mkdir(exist_ok=True)
@@ -42,7 +45,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     for s in srcs:
         o = OBJ / (s.stem + ".o")
         if force or _stale(o, [s] + hdrs):
-            cmd = [nvcc, *NVCC_FLAGS, "-c", str(s), "-o", str(o)]
+            cmd = [nvcc, *flags, "-c", str(s), "-o", str(o)]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)

@@ -37,13 +37,19 @@ __constant__ int c_tc_prefetch = 1;
 // four roles x TRACE_CAP records.  Null pointer = off (one uniform predicate per site).
 __constant__ unsigned long long* c_trace = nullptr;
 constexpr int TRACE_CAP = 8192;
+// Compiled in only with -DB200_TRACE (B200_TRACE=1 python masters-thesis_b200/build.py --force): even a never-taken
+// trace site costs issue slots on the single-thread MMA issue path.
 __device__ __forceinline__ void trace_ev(int role, int ev, int q, long long step, int& n) {
+#ifdef B200_TRACE
     if (c_trace != nullptr && blockIdx.x == 0 && n < TRACE_CAP) {
         unsigned long long* rec = c_trace + ((size_t)role * TRACE_CAP + n) * 2;
         rec[0] = ((unsigned long long)(unsigned)((role << 24) | (ev << 16) | (q << 8)) << 32) | (unsigned long long)(unsigned)step;
         rec[1] = (unsigned long long)clock64();
         ++n;
     }
+#else
+    (void)role; (void)ev; (void)q; (void)step; (void)n;
+#endif
 }
 
 constexpr int TH = 64;              // hidden size of this engine
@@ -513,8 +519,18 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 // Warp roles: 8 epilogue warps (thread = one sequence x 8 units per quarter), 2 loader warps ([x_t | h_{t-1}] image
 // from the fp32 stash, dropout keep-bits applied), 1 MMA warp.
 // Barriers: xh_full/xh_free, a_full/a_free (per slot), da_full/da_free, d_full/d_free, done.
-constexpr int BW_EPI_WARPS = 8;
-constexpr int BW_THREADS = 32 * (BW_EPI_WARPS + LOADER_WARPS + 2);   // 3 warpgroups: 2 epilogue, 1 = loaders + MMA + 1 idle warp
+// Epilogue geometry.  BW_EU = hidden units per epilogue thread per 16-unit quarter: 8 -> 8 epilogue warps (2 per SM
+// sub-partition), 4 -> 16 warps.  Measured on B200 (B = 4096, precise): EU = 8 is 15-20 % faster; with 16 warps the
+// per-quarter fixed costs (barrier hand-offs, fences, TMEM load waits) are amortised over half the work per warp.
+constexpr int BW_EU = 8;
+constexpr int BW_EPI_WARPS = 4 * (16 / BW_EU);
+constexpr int BW_THREADS = 32 * (BW_EPI_WARPS + LOADER_WARPS + 2);   // + one warpgroup: 2 loaders, 2 MMA issuers
+// setmaxnreg targets.  The pool is what the CTA was LAUNCHED with (threads x compiled registers), not the SM's 65,536;
+// asking for more than the pool blocks the last warpgroup forever.
+constexpr int BW_LAUNCH_REGS = BW_EU == 8 ? 168 : 96;      // 65,536 / threads rounded down to a multiple of 8
+constexpr int BW_EPI_REGS = BW_EU == 8 ? 200 : 104, BW_AUX_REGS = BW_EU == 8 ? 104 : 64;
+static_assert(BW_EPI_WARPS * 32 * BW_EPI_REGS + 4 * 32 * BW_AUX_REGS <= BW_THREADS * BW_LAUNCH_REGS,
+              "setmaxnreg targets exceed the CTA's register pool");
 constexpr uint32_t TMEM_DW = 0, TMEM_A = 256, TMEM_D = 384;    // dWcat^T | two 64-column gate-quarter slots | [dx | dh]
 
 __host__ __device__ constexpr int packed_row(int gate, int u) { return (u >> 4) * 64 + gate * 16 + (u & 15); }
@@ -602,10 +618,33 @@ __device__ __forceinline__ float warp_transpose_sum16(float (&v)[4][4], int lane
     return v[0][0] + __shfl_xor_sync(0xffffffffu, v[0][0], 1);
 }
 
+template <int EU>
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[4][EU], int lane);
+template <>
+__device__ __forceinline__ float warp_transpose_sum<8>(float (&v)[4][8], int lane) { return warp_transpose_sum32(v, lane); }
+template <>
+__device__ __forceinline__ float warp_transpose_sum<4>(float (&v)[4][4], int lane) { return warp_transpose_sum16(v, lane); }
+
+template <int W>
+__device__ __forceinline__ void tmem_ldn(uint32_t taddr, float (&v)[W]);
+template <>
+__device__ __forceinline__ void tmem_ldn<8>(uint32_t taddr, float (&v)[8]) { tmem_ld8(taddr, v); }
+template <>
+__device__ __forceinline__ void tmem_ldn<4>(uint32_t taddr, float (&v)[4]) { tmem_ld4(taddr, v); }
+
 __device__ __forceinline__ void ld_global_v8(const float* p, float (&v)[8]) {
     asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
                  : "l"(p));
+}
+
+template <int W>
+__device__ __forceinline__ void ld_global_vn(const float* p, float (&v)[W]);
+template <>
+__device__ __forceinline__ void ld_global_vn<8>(const float* p, float (&v)[8]) { ld_global_v8(p, v); }
+template <>
+__device__ __forceinline__ void ld_global_vn<4>(const float* p, float (&v)[4]) {
+    asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "l"(p));
 }
 
 template <int NSPLIT, bool LAYER0, int XB, int DB>
@@ -667,19 +706,22 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     const int64_t total_steps = my_tiles * T;
     const int64_t total_q = 4 * total_steps;
 
-    // register rebalancing between warpgroups: the loader/MMA group releases registers, the two epilogue groups take them
-    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
-    else asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
+    // register rebalancing between warpgroups: the loader/MMA group releases registers, the epilogue groups take them
+    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(BW_EPI_REGS));
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(BW_AUX_REGS));
 
     if (warp < BW_EPI_WARPS) {
         // ===================================== epilogue warps =====================================================
-        const int grp = warp >> 2, wq = warp & 3;
+        // warp = (sub, wq): TMEM lane quarter wq = warp % 4 (rows 32 wq .. +31), unit slice sub = warp / 4: EU hidden
+        // units of every 16-unit quarter
+        constexpr int EU = BW_EU;
+        const int sub = warp >> 2, wq = warp & 3;
         const int r = wq * 32 + lane;
         const uint32_t lane_addr = tmem_base + ((uint32_t)(wq * 32) << 16);
         const uint32_t row_off = (uint32_t)(r >> 3) * SBO_DA + (uint32_t)(r & 7) * 16;
         const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
-        float dc[4][8], dh[4][8], db[4];
+        float dc[4][EU], dh[4][EU], db[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) db[q] = 0.f;
 
@@ -688,21 +730,22 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             mbar_wait(d_full, (uint32_t)(g_done & 1));
             tc_fence_after();
 #pragma unroll
-            for (int q = 0; q < 4; ++q) tmem_ld8(lane_addr + TMEM_D + DH_COL0 + 16 * q + 8 * grp, dh[q]);
+            for (int q = 0; q < 4; ++q) tmem_ldn<EU>(lane_addr + TMEM_D + DH_COL0 + 16 * q + EU * sub, dh[q]);
             if (!LAYER0) {
-                float dx[4][8];
+                constexpr int DXC = TH / (16 / EU) / 8;                      // 8-column chunks of dx per thread
+                float dx[DXC][8];
 #pragma unroll
-                for (int c = 0; c < 4; ++c) tmem_ld8(lane_addr + TMEM_D + 32 * grp + 8 * c, dx[c]);
+                for (int c = 0; c < DXC; ++c) tmem_ld8(lane_addr + TMEM_D + 8 * DXC * sub + 8 * c, dx[c]);
                 tmem_ld_wait();
                 if (live) {
-                    const uint32_t mb = drop ? (uint32_t)(drop_bits[(int64_t)t_done * N + row] >> (32 * grp)) : 0xFFFFFFFFu;
+                    const uint32_t mb = drop ? (uint32_t)(drop_bits[(int64_t)t_done * N + row] >> (8 * DXC * sub)) : 0xFFFFFFFFu;
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
+                    for (int c = 0; c < DXC; ++c) {
                         if (drop) {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) dx[c][i] = ((mb >> (8 * c + i)) & 1u) ? dx[c][i] * inv_keep : 0.f;
                         }
-                        st_global_v8(d_in + ((int64_t)t_done * N + row) * TH + 32 * grp + 8 * c, dx[c]);
+                        st_global_v8(d_in + ((int64_t)t_done * N + row) * TH + 8 * DXC * sub + 8 * c, dx[c]);
                     }
                 }
             } else {
@@ -716,21 +759,24 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         int64_t g = 0;
         int ntr = 0;
         const bool tracer = warp == 0 && lane == 0;
-        // EPI_LOADS: this warp stages row groups 2*warp, 2*warp+1 of the [x | h] image of step (tile_n, t_n); the image of
+        // EPI_LOADS: this warp stages its share of the row groups of the [x | h] image of step (tile_n, t_n); the image of
         // running step g_n may be written once the MMAs of step g_n - 1 have released the (single) buffer
         auto stage_image = [&](int64_t tile_n, int t_n, int64_t g_n) {
+            constexpr int RG = 16 / BW_EPI_WARPS;                            // row groups per warp
             const int64_t r0 = tile_n * TM;
             const int64_t rows_live = N - r0;
             uint8_t* xh_hi = smem + S::off_xh;
             uint8_t* xh_lo = xh_hi + S::XHB;
-            float4 vx[2][4], vh[2][4];
-            uint64_t m[2] = {0ull, 0ull};
-            tile_load<2>(vx, xin + ((int64_t)t_n * N + r0) * TH, rows_live, 2 * warp, lane);
-            tile_load<2>(vh, h_st + ((int64_t)(t_n > 0 ? t_n - 1 : 0) * N + r0) * TH, t_n > 0 ? rows_live : 0, 2 * warp, lane);
-            if (drop) tile_load_bits<2>(m, drop_bits + (int64_t)t_n * N + r0, rows_live, 2 * warp, lane);
+            float4 vx[RG][4], vh[RG][4];
+            uint64_t m[RG];
+#pragma unroll
+            for (int i = 0; i < RG; ++i) m[i] = 0ull;
+            tile_load<RG>(vx, xin + ((int64_t)t_n * N + r0) * TH, rows_live, RG * warp, lane);
+            tile_load<RG>(vh, h_st + ((int64_t)(t_n > 0 ? t_n - 1 : 0) * N + r0) * TH, t_n > 0 ? rows_live : 0, RG * warp, lane);
+            if (drop) tile_load_bits<RG>(m, drop_bits + (int64_t)t_n * N + r0, rows_live, RG * warp, lane);
             if (g_n > 0) mbar_wait(&xh_free[0], (uint32_t)((g_n - 1) & 1));
-            tile_store<NSPLIT, 2>(vx, xh_hi, xh_lo, SBO_W, 0, 2 * warp, lane, drop, m, inv_keep);
-            tile_store<NSPLIT, 2>(vh, xh_hi, xh_lo, SBO_W, KX, 2 * warp, lane, false, m, 1.f);
+            tile_store<NSPLIT, RG>(vx, xh_hi, xh_lo, SBO_W, 0, RG * warp, lane, drop, m, inv_keep);
+            tile_store<NSPLIT, RG>(vh, xh_hi, xh_lo, SBO_W, KX, RG * warp, lane, false, m, 1.f);
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&xh_full[0]);
@@ -742,25 +788,26 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 #pragma unroll
             for (int q = 0; q < 4; ++q)
 #pragma unroll
-                for (int i = 0; i < 8; ++i) dc[q][i] = dh[q][i] = 0.f;
-            // software pipeline of the per-quarter global operands: (c_t, c_{t-1}, d_out) of the NEXT quarter are in flight
-            float nct[8], ncp[8], ndq[8];
+                for (int i = 0; i < EU; ++i) dc[q][i] = dh[q][i] = 0.f;
+            // software pipeline of the per-quarter global operands: (c_t, c_{t-1}, d_out) of the NEXT quarter are in flight.
+            // Rows beyond N keep zeros, which makes every da of such a row exactly zero (dh = dc = d_out = 0).
+            float nct[EU], ncp[EU], ndq[EU];
             auto issue_loads = [&](int t, int q) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) nct[i] = ncp[i] = ndq[i] = 0.f;
+                for (int i = 0; i < EU; ++i) nct[i] = ncp[i] = ndq[i] = 0.f;
                 if (live && t >= 0) {
-                    const int64_t o = ((int64_t)t * N + row) * TH + 16 * q + 8 * grp;
-                    ld_global_v8(c_st + o, nct);
-                    if (t > 0) ld_global_v8(c_st + o - N * TH, ncp);
-                    if (d_out) ld_global_v8(d_out + o, ndq);
-                    else if (t == T - 1) ld_global_v8(dhT + row * TH + 16 * q + 8 * grp, ndq);
+                    const int64_t o = ((int64_t)t * N + row) * TH + 16 * q + EU * sub;
+                    ld_global_vn<EU>(c_st + o, nct);
+                    if (t > 0) ld_global_vn<EU>(c_st + o - N * TH, ncp);
+                    if (d_out) ld_global_vn<EU>(d_out + o, ndq);
+                    else if (t == T - 1) ld_global_vn<EU>(dhT + row * TH + 16 * q + EU * sub, ndq);
                 }
             };
             issue_loads(T - 1, 0);
             for (int t = T - 1; t >= 0; --t, ++g) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const int u0 = 16 * q + 8 * grp;                         // first hidden unit of this thread's slice
+                    const int u0 = 16 * q + EU * sub;                        // first hidden unit of this thread's slice
                     const int64_t qi = 4 * g + q;                              // running quarter index
                     const int slot = q & 1;
                     if (tracer) trace_ev(0, 0, q, g, ntr);
@@ -770,18 +817,18 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     const int buf = (int)(qi % DB);
                     uint8_t* da_hi = smem + S::off_da + (buf * NSPLIT) * S::DAB;
                     uint8_t* da_lo = da_hi + S::DAB;
-                    float av[4][8];
-                    const uint32_t acol = TMEM_A + 64 * slot + 8 * grp;
+                    float av[4][EU];
+                    const uint32_t acol = TMEM_A + 64 * slot + EU * sub;
 #pragma unroll
-                    for (int gate = 0; gate < 4; ++gate) tmem_ld8(lane_addr + acol + gate * 16, av[gate]);
+                    for (int gate = 0; gate < 4; ++gate) tmem_ldn<EU>(lane_addr + acol + gate * 16, av[gate]);
                     tmem_ld_wait();
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&a_free[slot]);                // slot read out
                     // ---- part A (independent of the dh recurrence): D = 1 + 2^(...) of the four gates and of c_t ------
-                    float Dc[8], r1[8], r2[8];
+                    float Dc[EU], r1[EU], r2[EU];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
+                    for (int i = 0; i < EU; ++i) {
                         const float4 b4 = *reinterpret_cast<const float4*>(bias_s + 4 * (u0 + i));
                         av[0][i] = fminf(fmaf(av[0][i], -LOG2E, b4.x), EXP_CLAMP);
                         av[1][i] = fminf(fmaf(av[1][i], -LOG2E, b4.y), EXP_CLAMP);
@@ -790,12 +837,12 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         Dc[i] = fminf(2.f * LOG2E * nct[i], EXP_CLAMP);
                     }
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
+                    for (int i = 0; i < EU; ++i) {
                         av[0][i] = 1.f + ex2a(av[0][i]); av[1][i] = 1.f + ex2a(av[1][i]); av[2][i] = 1.f + ex2a(av[2][i]);
                         av[3][i] = 1.f + ex2a(av[3][i]); Dc[i] = 1.f + ex2a(Dc[i]);
                     }
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) { r1[i] = rcpa(av[0][i] * av[1][i] * av[2][i]); r2[i] = rcpa(av[3][i] * Dc[i]); }
+                    for (int i = 0; i < EU; ++i) { r1[i] = rcpa(av[0][i] * av[1][i] * av[2][i]); r2[i] = rcpa(av[3][i] * Dc[i]); }
                     // ---- dh of this step arrives from the previous step's dgrad (first quarter only) -----------------
                     if (q == 0 && t < T - 1) {
                         if (tracer) trace_ev(0, 2, q, g, ntr);
@@ -804,7 +851,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     }
                     // ---- part B: gates by batch inversion, cell/gate derivatives -> da quarter ---------------------------
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
+                    for (int i = 0; i < EU; ++i) {
                         const float Di = av[0][i], Df = av[1][i], Dg = av[2][i], Do = av[3][i];
                         const float t1 = r1[i] * Dg;
                         const float ig = t1 * Df, fg = t1 * Di, gg = (Dg - 2.f) * (r1[i] * (Di * Df));
@@ -813,14 +860,14 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         const float d_o = dhv * tc;
                         const float dcc = dc[q][i] + dhv * og * (1.f - tc * tc);
                         dc[q][i] = dcc * fg;
-                        av[0][i] = live ? dcc * gg * ig * (1.f - ig) : 0.f;
-                        av[1][i] = live ? dcc * ncp[i] * fg * (1.f - fg) : 0.f;
-                        av[2][i] = live ? dcc * ig * (1.f - gg * gg) : 0.f;
-                        av[3][i] = live ? d_o * og * (1.f - og) : 0.f;
+                        av[0][i] = dcc * gg * ig * (1.f - ig);
+                        av[1][i] = dcc * ncp[i] * fg * (1.f - fg);
+                        av[2][i] = dcc * ig * (1.f - gg * gg);
+                        av[3][i] = d_o * og * (1.f - og);
                     }
                     // the next quarter's global operands (this quarter's are consumed)
                     if (q < 3) issue_loads(t, q + 1); else issue_loads(t - 1, 0);
-                    // operand image of this quarter: column kk = gate * 16 + 8 * grp + i  ->  16-byte chunk gate * 2 + grp
+                    // operand image of this quarter: column kk = gate * 16 + EU * sub + i
                     if (qi >= DB) {
                         if (tracer) trace_ev(0, 4, q, g, ntr);
                         mbar_wait(&da_free[buf], (uint32_t)(((qi / DB) - 1) & 1));
@@ -828,14 +875,21 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     }
 #pragma unroll
                     for (int gate = 0; gate < 4; ++gate) {
-                        uint4 hi4, lo4;
-                        split2(av[gate][0], av[gate][1], hi4.x, lo4.x);
-                        split2(av[gate][2], av[gate][3], hi4.y, lo4.y);
-                        split2(av[gate][4], av[gate][5], hi4.z, lo4.z);
-                        split2(av[gate][6], av[gate][7], hi4.w, lo4.w);
-                        const uint32_t o = row_off + (uint32_t)(gate * 2 + grp) * LBO_BYTES;
-                        *reinterpret_cast<uint4*>(da_hi + o) = hi4;
-                        if (NSPLIT == 2) *reinterpret_cast<uint4*>(da_lo + o) = lo4;
+                        const uint32_t o = row_off + (uint32_t)((gate * 16 + EU * sub) >> 3) * LBO_BYTES + (uint32_t)((EU * sub) & 7) * 2;
+                        if (EU == 8) {
+                            uint4 hi4, lo4;
+                            split2(av[gate][0], av[gate][1], hi4.x, lo4.x);
+                            split2(av[gate][2], av[gate][3], hi4.y, lo4.y);
+                            split2(av[gate][EU - 4], av[gate][EU - 3], hi4.z, lo4.z);
+                            split2(av[gate][EU - 2], av[gate][EU - 1], hi4.w, lo4.w);
+                            *reinterpret_cast<uint4*>(da_hi + o) = hi4;
+                            if (NSPLIT == 2) *reinterpret_cast<uint4*>(da_lo + o) = lo4;
+                        } else {
+                            uint2 hi2, lo2;
+                            split2x2(av[gate][0], av[gate][1], av[gate][2], av[gate][3], hi2, lo2);
+                            *reinterpret_cast<uint2*>(da_hi + o) = hi2;
+                            if (NSPLIT == 2) *reinterpret_cast<uint2*>(da_lo + o) = lo2;
+                        }
                     }
                     fence_proxy_async();
                     __syncwarp();
@@ -843,7 +897,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     if (tracer) trace_ev(0, 6, q, g, ntr);
                     // bias gradient: layer 0 gets it from the tensor core (constant-one column of the x image, see the
                     // loader); other layers reduce da over the warp's 32 rows here
-                    if (!LAYER0) db[q] += warp_transpose_sum32(av, lane);
+                    if (!LAYER0) db[q] += warp_transpose_sum<EU>(av, lane);
                     if (tracer) trace_ev(0, 7, q, g, ntr);
                 }
                 if (EPI_LOADS) {
@@ -856,11 +910,14 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         // ---- final: bias-gradient partials and the weight-gradient accumulator ---------------------------------------
         {
             float* bp = bpart + ((int64_t)blockIdx.x * 4 + wq) * TG;
-            // lane L holds value index L = gate * 8 + i of each quarter (layer 0: zeros, its bias gradient is row KIN_ONE
-            // of the weight-gradient accumulator and is written below)
-            if (!(LAYER0 && wq == 0)) {                 // layer 0, slot wq == 0 is written from the accumulator row below
+            // after the transpose-reduce lane L (EU = 8) or lane pair L/2 (EU = 4) holds value index m = gate * EU + i of each
+            // quarter (layer 0: its bias gradient is a row of the weight-gradient accumulator, written below)
+            if (!(LAYER0 && wq == 0)) {
+                const int m = EU == 8 ? lane : lane >> 1;
+                if (EU == 8 || (lane & 1) == 0) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) bp[(lane >> 3) * TH + 16 * q + 8 * grp + (lane & 7)] = db[q];
+                    for (int q = 0; q < 4; ++q) bp[(m / EU) * TH + 16 * q + EU * sub + (m % EU)] = db[q];
+                }
             }
         }
         mbar_wait(done, 0u);
@@ -868,7 +925,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         {
             const int kcat = r;                                               // TMEM lane = row of dWcat^T
             float* wp = wpart + (int64_t)blockIdx.x * TG * 128;
-            for (int c0 = grp * 128; c0 < grp * 128 + 128; c0 += 8) {
+            constexpr int CPW = TG / (BW_EPI_WARPS / 4);                      // accumulator columns per warp
+            for (int c0 = sub * CPW; c0 < sub * CPW + CPW; c0 += 8) {
                 float v[8];
                 tmem_ld8(lane_addr + TMEM_DW + c0, v);
                 tmem_ld_wait();
@@ -913,17 +971,21 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
-                // batches of 4 row groups (64 registers); the first batch is in flight while we wait for the buffer
-                uint64_t m[4];
-                float4 v[4][4];
+                // batches of 2 row groups (32 registers: this warpgroup runs on a small register budget); the first batch
+                // is in flight while we wait for the buffer
+                uint64_t m[2] = {0ull, 0ull};
+                float4 v[2][4];
                 const float* hsrc = h_st + ((int64_t)(t > 0 ? t - 1 : 0) * N + r0) * TH;
                 const int64_t h_live = t > 0 ? rows_live : 0;
+                tile_load<2>(v, hsrc, h_live, lw * 8, lane);
+                if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
+                if (tracer) trace_ev(1, 1, 0, g, ntr);
+#pragma unroll 1
+                for (int b2 = 0; b2 < 4; ++b2) {
+                    if (b2 > 0) tile_load<2>(v, hsrc, h_live, lw * 8 + 2 * b2, lane);
+                    tile_store<NSPLIT, 2>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8 + 2 * b2, lane, false, m, 1.f);
+                }
                 if (LAYER0) {
-                    tile_load<4>(v, hsrc, h_live, lw * 8, lane);
-                    if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
-                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8, lane, false, m, 1.f);
-                    tile_load<4>(v, hsrc, h_live, lw * 8 + 4, lane);
-                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8 + 4, lane, false, m, 1.f);
                     // x part: 16 columns, lane quarter qq covers columns 4qq .. 4qq+3 of its row
 #pragma unroll
                     for (int rgi = 0; rgi < 8; ++rgi) {
@@ -949,18 +1011,12 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 } else {
                     const float* xsrc = xin + ((int64_t)t * N + r0) * TH;
                     const uint64_t* bsrc = drop_bits + (int64_t)t * N + r0;
-                    tile_load<4>(v, xsrc, rows_live, lw * 8, lane);
-                    if (drop) tile_load_bits<4>(m, bsrc, rows_live, lw * 8, lane);
-                    if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
-                    if (tracer) trace_ev(1, 1, 0, g, ntr);
-                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8, lane, drop, m, inv_keep);
-                    tile_load<4>(v, xsrc, rows_live, lw * 8 + 4, lane);
-                    if (drop) tile_load_bits<4>(m, bsrc, rows_live, lw * 8 + 4, lane);
-                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8 + 4, lane, drop, m, inv_keep);
-                    tile_load<4>(v, hsrc, h_live, lw * 8, lane);
-                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8, lane, false, m, 1.f);
-                    tile_load<4>(v, hsrc, h_live, lw * 8 + 4, lane);
-                    tile_store<NSPLIT, 4>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8 + 4, lane, false, m, 1.f);
+#pragma unroll 1
+                    for (int b2 = 0; b2 < 4; ++b2) {
+                        tile_load<2>(v, xsrc, rows_live, lw * 8 + 2 * b2, lane);
+                        if (drop) tile_load_bits<2>(m, bsrc, rows_live, lw * 8 + 2 * b2, lane);
+                        tile_store<NSPLIT, 2>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8 + 2 * b2, lane, drop, m, inv_keep);
+                    }
                 }
                 fence_proxy_async();
                 __syncwarp();

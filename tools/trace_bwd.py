@@ -1,4 +1,4 @@
-"""Event timeline of CTA 0 of the tcgen05 backward kernel (diagnostics).  python tools/trace_bwd.py [--layer 1] [--engine tc_precise]"""
+"""Event timeline of CTA 0 of the tcgen05 backward kernel (diagnostics; needs a library built with B200_TRACE=1 python masters-thesis_b200/build.py --force).  python tools/trace_bwd.py [--layer 1] [--engine tc_precise]"""
 import argparse, sys
 from pathlib import Path
 import numpy as np, torch

@@ -1,4 +1,4 @@
-"""Event timeline of CTA 0 of the tcgen05 forward kernel (diagnostics).  python tools/trace_fwd.py [--layer 1]"""
+"""Event timeline of CTA 0 of the tcgen05 forward kernel (diagnostics; needs a library built with B200_TRACE=1 python masters-thesis_b200/build.py --force).  python tools/trace_fwd.py [--layer 1]"""
 import argparse, sys
 from pathlib import Path
 import numpy as np, torch
