@@ -348,16 +348,25 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     split2(hv[6], hv[7], hi4.w, lo4.w);
                     *reinterpret_cast<uint4*>(h_hi + row_off + uc * LBO_BYTES) = hi4;
                     if (NSPLIT == 2) *reinterpret_cast<uint4*>(h_lo + row_off + uc * LBO_BYTES) = lo4;
-                    if (live) {
-                        st_global_v8(hdst + uc * 8, hv);
-                        st_global_v8(cdst + uc * 8, cv);
+                    if (uc < TH / 8 - 1) {
+                        if (live) {
+                            st_global_v8(hdst + uc * 8, hv);
+                            st_global_v8(cdst + uc * 8, cv);
+                        }
+                    } else {
+                        // last chunk: hand h_t to the tensor core first.  The proxy fence is a full memory barrier that
+                        // waits for outstanding global stores, so the youngest stores are issued after it.
+                        tc_fence_before();            // TMEM reads of this step are complete (wait::ld above)
+                        fence_proxy_async();          // h_t visible to the tensor core
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(h_ready);
+                        if (tracer) trace_ev(0, 6, 0, g, ntr);
+                        if (live) {
+                            st_global_v8(hdst + uc * 8, hv);
+                            st_global_v8(cdst + uc * 8, cv);
+                        }
                     }
                 }
-                tc_fence_before();            // TMEM reads of this step are complete (wait::ld above)
-                fence_proxy_async();          // h_t visible to the tensor core
-                __syncwarp();
-                if (lane == 0) mbar_arrive(h_ready);
-                if (tracer) trace_ev(0, 6, 0, g, ntr);
             }
         }
     } else if (warp < EPI_WARPS + LOADER_WARPS) {
@@ -865,7 +874,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         av[2][i] = dcc * ig * (1.f - gg * gg);
                         av[3][i] = d_o * og * (1.f - og);
                     }
-                    // the next quarter's global operands (this quarter's are consumed)
+                    // the next quarter's global operands (this quarter's are consumed).  Measured: issuing them here, before the
+                    // proxy fence below, is faster than after it (lead time matters more than the fence waiting on them).
                     if (q < 3) issue_loads(t, q + 1); else issue_loads(t - 1, 0);
                     // operand image of this quarter: column kk = gate * 16 + EU * sub + i
                     if (qi >= DB) {
