@@ -90,6 +90,21 @@ B200_API int b200_gen_batch(uint64_t seed, const int64_t* window_idx, int64_t fi
                    int n_stocks, int lookback, int target, int64_t stride, int n_features,
                    float* x, float* y_stock, float* y_market, float* factor, float* inv_psi,
                    void* stream);
+/* The same batch from a RESIDENT series instead of the generator: stocks [n_stocks][n_samples], market [n_samples]
+ * (device, fp32) are what the reference's prepare_data loads from data_dir/stocks.pt and market.pt
+ * (src/data.py:193-196; datamodule=real: 25 portfolios, stride 5).  prediction_task = 0 selects the reconstruction
+ * split of lookback_target_split (src/common.py:107-110): the window is `lookback` days long and the target is its
+ * last `target` days.  ols_alpha / ols_beta [n_windows*n_stocks] (may be NULL) receive the per-window OLS
+ * coefficients that the reference stores in y channels 2, 3 when no true coefficients exist (src/data.py:205-207). */
+B200_API int b200_series_batch(const float* stocks, const float* market, int64_t n_samples, const int64_t* window_idx,
+                      int64_t first_window, int64_t n_windows, int n_stocks, int lookback, int target,
+                      int64_t stride, int n_features, int prediction_task, float* x, float* y_stock,
+                      float* y_market, float* factor, float* inv_psi, float* ols_alpha, float* ols_beta,
+                      void* stream);
+/* days [first_day, first_day + n_days) of the generator's series itself: stocks [n_stocks][n_days], market [n_days]
+ * (what SyntheticLogReturns.generate returns, src/data.py:49-59) */
+B200_API int b200_gen_series(uint64_t seed, int64_t first_day, int64_t n_days, int n_stocks, float* stocks, float* market,
+                    void* stream);
 /* per-stock true alpha_i, beta_i of the run (src/data.py:53-54) */
 B200_API int b200_gen_coefficients(uint64_t seed, int n_stocks, float* alpha, float* beta, void* stream);
 /* raw Philox4x32-10 blocks, for bit-exact checks against the numpy specification:

@@ -24,6 +24,8 @@ PROTOTYPES = {
     "b200_param_count": (_l, [_i, _i, _i]),
     "b200_param_offset": (_l, [_i, _i, _i, _i]),
     "b200_gen_batch": (_i, [_u64, _p, _l, _l, _i, _i, _i, _l, _i, _p, _p, _p, _p, _p, _p]),
+    "b200_series_batch": (_i, [_p, _p, _l, _p, _l, _l, _i, _i, _i, _l, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_gen_series": (_i, [_u64, _l, _l, _i, _p, _p, _p]),
     "b200_gen_coefficients": (_i, [_u64, _i, _p, _p, _p]),
     "b200_philox4x32": (_i, [_u64, _p, _l, _p, _p]),
     "b200_dropout_mask": (_i, [_u64, _i, _l, _i, _i, _f, _p, _p]),

@@ -53,13 +53,20 @@ __device__ __forceinline__ void stock_coeff(uint64_t seed, uint32_t i, float& al
     beta = 0.9444f + 0.3521f * z1;    // src/data.py:39
 }
 
+// Source of the window's returns: the Philox generator (stocks == nullptr) or a resident series
+// (stocks [S][n_samples], market [n_samples], e.g. the reference's data_dir/stocks.pt + market.pt).
+// prediction != 0: window = T + n days, target = the n days after the look-back (src/common.py:104-106);
+// prediction == 0: window = T days, target = the last n days of the look-back itself (src/common.py:107-110).
 __global__ void __launch_bounds__(256)
-gen_batch_kernel(uint64_t seed, const int64_t* __restrict__ window_idx, int64_t first_window, int64_t n_windows,
-                 int S, int T, int n, int64_t stride, int F,
+gen_batch_kernel(uint64_t seed, const float* __restrict__ stocks, const float* __restrict__ market, int64_t n_samples,
+                 const int64_t* __restrict__ window_idx, int64_t first_window, int64_t n_windows,
+                 int S, int T, int n, int64_t stride, int F, int prediction,
                  float* __restrict__ x, float* __restrict__ y_stock, float* __restrict__ y_market,
-                 float* __restrict__ factor, float* __restrict__ inv_psi) {
+                 float* __restrict__ factor, float* __restrict__ inv_psi,
+                 float* __restrict__ ols_alpha, float* __restrict__ ols_beta) {
     extern __shared__ float sm[];
-    const int W = T + n;
+    const int W = prediction ? T + n : T;       // days per window
+    const int Y0 = prediction ? T : T - n;      // first target day inside the window
     float* rs = sm;               // [S][W]
     float* rm = rs + S * W;       // [W]
     float* coef = rm + W;         // [S][2]
@@ -71,21 +78,30 @@ gen_batch_kernel(uint64_t seed, const int64_t* __restrict__ window_idx, int64_t 
         const uint64_t day0 = (uint64_t)w * (uint64_t)stride;
         const int64_t row0 = wl * S;
 
-        for (int d = threadIdx.x; d < W; d += blockDim.x)
-            rm[d] = 0.0678f + 0.5099f * student_t5(day0 + d, ID_MARKET, seed);   // src/data.py:36
-        for (int s = threadIdx.x; s < S; s += blockDim.x) stock_coeff(seed, (uint32_t)s, coef[2 * s], coef[2 * s + 1]);
-        __syncthreads();
-        for (int i = threadIdx.x; i < S * W; i += blockDim.x) {
-            int s = i / W, d = i - s * W;
-            float eps = 0.3140f * student_t5(day0 + d, (uint32_t)s, seed);          // src/data.py:37
-            rs[i] = (coef[2 * s] + coef[2 * s + 1] * rm[d]) + eps;
+        if (stocks) {
+            for (int d = threadIdx.x; d < W; d += blockDim.x) rm[d] = market[day0 + d];
+            for (int i = threadIdx.x; i < S * W; i += blockDim.x) {
+                int s = i / W, d = i - s * W;
+                rs[i] = stocks[(int64_t)s * n_samples + (int64_t)day0 + d];
+            }
+        } else {
+            for (int d = threadIdx.x; d < W; d += blockDim.x)
+                rm[d] = 0.0678f + 0.5099f * student_t5(day0 + d, ID_MARKET, seed);   // src/data.py:36
+            for (int s = threadIdx.x; s < S; s += blockDim.x) stock_coeff(seed, (uint32_t)s, coef[2 * s], coef[2 * s + 1]);
+            __syncthreads();
+            for (int i = threadIdx.x; i < S * W; i += blockDim.x) {
+                int s = i / W, d = i - s * W;
+                float eps = 0.3140f * student_t5(day0 + d, (uint32_t)s, seed);          // src/data.py:37
+                rs[i] = (coef[2 * s] + coef[2 * s + 1] * rm[d]) + eps;
+            }
         }
+        __syncthreads();
         if (threadIdx.x == 0) {
             float mean = 0.f;
-            for (int j = 0; j < n; ++j) mean += rm[T + j];
+            for (int j = 0; j < n; ++j) mean += rm[Y0 + j];
             mean /= (float)n;
             float ss = 0.f;
-            for (int j = 0; j < n; ++j) { float d = rm[T + j] - mean; ss += d * d; }
+            for (int j = 0; j < n; ++j) { float d = rm[Y0 + j] - mean; ss += d * d; }
             stat[0] = mean;
             stat[1] = ss;
             factor[2 * wl] = mean;
@@ -104,26 +120,28 @@ gen_batch_kernel(uint64_t seed, const int64_t* __restrict__ window_idx, int64_t 
         }
         for (int i = threadIdx.x; i < S * n; i += blockDim.x) {
             int s = i / n, j = i - s * n;
-            y_stock[row0 * n + i] = rs[s * W + T + j];
+            y_stock[row0 * n + i] = rs[s * W + Y0 + j];
         }
-        for (int j = threadIdx.x; j < n; j += blockDim.x) y_market[wl * n + j] = rm[T + j];
+        for (int j = threadIdx.x; j < n; j += blockDim.x) y_market[wl * n + j] = rm[Y0 + j];
 
         // per-stock OLS on the target window (closed form of pinv(X^T X) X^T y for [1, m])
         const float mbar = stat[0], smm = stat[1];
         for (int s = threadIdx.x; s < S; s += blockDim.x) {
-            const float* r = rs + s * W + T;
+            const float* r = rs + s * W + Y0;
             float rbar = 0.f;
             for (int j = 0; j < n; ++j) rbar += r[j];
             rbar /= (float)n;
             float smr = 0.f;
-            for (int j = 0; j < n; ++j) smr += (rm[T + j] - mbar) * (r[j] - rbar);
+            for (int j = 0; j < n; ++j) smr += (rm[Y0 + j] - mbar) * (r[j] - rbar);
             float b = smr / smm, a = rbar - b * mbar;
             float ebar = 0.f;
-            for (int j = 0; j < n; ++j) ebar += r[j] - (a + b * rm[T + j]);
+            for (int j = 0; j < n; ++j) ebar += r[j] - (a + b * rm[Y0 + j]);
             ebar /= (float)n;
             float see = 0.f;
-            for (int j = 0; j < n; ++j) { float e = r[j] - (a + b * rm[T + j]) - ebar; see += e * e; }
+            for (int j = 0; j < n; ++j) { float e = r[j] - (a + b * rm[Y0 + j]) - ebar; see += e * e; }
             inv_psi[row0 + s] = (float)(n - 1) / see;      // 1 / unbiased residual variance
+            if (ols_alpha) ols_alpha[row0 + s] = a;         // y channels 2, 3 when no true coefficients exist (src/data.py:205-207)
+            if (ols_beta) ols_beta[row0 + s] = b;
         }
         __syncthreads();
     }
@@ -158,6 +176,41 @@ __global__ void dropout_mask_kernel(uint64_t seed, int layer, int64_t N, int T, 
     }
 }
 
+// the generator's series itself, for consumers that need days rather than windows (reconstruction mode, test.py)
+__global__ void __launch_bounds__(256)
+gen_series_kernel(uint64_t seed, int64_t first_day, int64_t n_days, int S, float* __restrict__ stocks, float* __restrict__ market) {
+    const int64_t total = (int64_t)(S + 1) * n_days;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t s = i / n_days, d = i - s * n_days;
+        const uint64_t day = (uint64_t)(first_day + d);
+        const float m = 0.0678f + 0.5099f * student_t5(day, ID_MARKET, seed);
+        if (s == S) { market[d] = m; continue; }
+        float a, b;
+        stock_coeff(seed, (uint32_t)s, a, b);
+        stocks[s * n_days + d] = (a + b * m) + 0.3140f * student_t5(day, (uint32_t)s, seed);
+    }
+}
+
+static int launch_batch(const char* name, uint64_t seed, const float* stocks, const float* market, int64_t n_samples,
+                        const int64_t* window_idx, int64_t first_window, int64_t n_windows, int n_stocks, int lookback,
+                        int target, int64_t stride, int n_features, int prediction, float* x, float* y_stock, float* y_market,
+                        float* factor, float* inv_psi, float* ols_alpha, float* ols_beta, void* stream) {
+    const int W = prediction ? lookback + target : lookback;
+    size_t smem = ((size_t)n_stocks * W + W + 2 * n_stocks + 2) * sizeof(float);
+    B200_CHECK_ARG(smem <= 200 * 1024, "%s: window of %d stocks x %d days does not fit shared memory", name, n_stocks, W);
+    B200_CUDA(cudaFuncSetAttribute(gen_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t grid = n_windows < (int64_t)num_sms() * 16 ? n_windows : (int64_t)num_sms() * 16;
+    {
+        TimedLaunch _t(stocks ? "series_batch_kernel" : "gen_batch_kernel", (cudaStream_t)stream);
+        gen_batch_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(seed, stocks, market, n_samples, window_idx, first_window,
+                                                                         n_windows, n_stocks, lookback, target, stride, n_features,
+                                                                         prediction, x, y_stock, y_market, factor, inv_psi, ols_alpha,
+                                                                         ols_beta);
+    }
+    B200_LAUNCH_CHECK("gen_batch_kernel");
+    return B200_OK;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -169,17 +222,45 @@ extern "C" int b200_gen_batch(uint64_t seed, const int64_t* window_idx, int64_t 
     B200_CHECK_ARG(n_windows >= 0 && n_stocks > 0 && lookback > 0 && target > 1 && stride > 0,
                    "gen_batch: bad sizes (n_windows=%lld S=%d T=%d n=%d)", (long long)n_windows, n_stocks, lookback, target);
     B200_CHECK_ARG(n_features == 3 || n_features == 5, "gen_batch: n_features must be 3 or 5, got %d", n_features);
+    if (n_windows == 0) return B200_OK;                 // empty batch: nothing to write (outputs may be NULL)
     B200_CHECK_ARG(x && y_stock && y_market && factor && inv_psi, "gen_batch: null output pointer");
-    if (n_windows == 0) return B200_OK;
-    size_t smem = ((size_t)n_stocks * (lookback + target) + (lookback + target) + 2 * n_stocks + 2) * sizeof(float);
-    B200_CHECK_ARG(smem <= 200 * 1024, "gen_batch: window of %d stocks x %d days does not fit shared memory", n_stocks,
-                   lookback + target);
-    B200_CUDA(cudaFuncSetAttribute(gen_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t grid = n_windows < (int64_t)num_sms() * 16 ? n_windows : (int64_t)num_sms() * 16;
-    { TimedLaunch _t("gen_batch_kernel", (cudaStream_t)stream); gen_batch_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(seed, window_idx, first_window, n_windows, n_stocks,
-                                                                         lookback, target, stride, n_features, x, y_stock,
-                                                                         y_market, factor, inv_psi); }
-    B200_LAUNCH_CHECK("gen_batch_kernel");
+    return launch_batch("gen_batch", seed, nullptr, nullptr, 0, window_idx, first_window, n_windows, n_stocks, lookback, target,
+                        stride, n_features, 1, x, y_stock, y_market, factor, inv_psi, nullptr, nullptr, stream);
+}
+
+extern "C" int b200_series_batch(const float* stocks, const float* market, int64_t n_samples, const int64_t* window_idx,
+                                 int64_t first_window, int64_t n_windows, int n_stocks, int lookback, int target,
+                                 int64_t stride, int n_features, int prediction_task, float* x, float* y_stock,
+                                 float* y_market, float* factor, float* inv_psi, float* ols_alpha, float* ols_beta,
+                                 void* stream) {
+    B200_CHECK_ARG(stocks && market && n_samples > 0, "series_batch: null series");
+    B200_CHECK_ARG(n_windows >= 0 && n_stocks > 0 && lookback > 0 && target > 1 && stride > 0,
+                   "series_batch: bad sizes (n_windows=%lld S=%d T=%d n=%d)", (long long)n_windows, n_stocks, lookback, target);
+    B200_CHECK_ARG(prediction_task || target <= lookback, "series_batch: target window must be <= lookback window for the reconstruction task");
+    B200_CHECK_ARG(n_features == 3 || n_features == 5, "series_batch: n_features must be 3 or 5, got %d", n_features);
+    const int64_t W = prediction_task ? lookback + target : lookback;
+    B200_CHECK_ARG(n_samples >= W, "series_batch: series of %lld days is shorter than one window (%lld)", (long long)n_samples, (long long)W);
+    // contiguous ranges are checked here; explicit index lists are the caller's contract (indices < (n_samples - W) / stride + 1)
+    const int64_t n_win_total = (n_samples - W) / stride + 1;
+    B200_CHECK_ARG(window_idx || (first_window >= 0 && first_window + n_windows <= n_win_total),
+                   "series_batch: windows [%lld, %lld) exceed the %lld windows of the series", (long long)first_window,
+                   (long long)(first_window + n_windows), (long long)n_win_total);
+    if (n_windows == 0) return B200_OK;                 // empty batch: nothing to write (outputs may be NULL)
+    B200_CHECK_ARG(x && y_stock && y_market && factor && inv_psi, "series_batch: null output pointer");
+    return launch_batch("series_batch", 0, stocks, market, n_samples, window_idx, first_window, n_windows, n_stocks, lookback, target,
+                        stride, n_features, prediction_task ? 1 : 0, x, y_stock, y_market, factor, inv_psi, ols_alpha, ols_beta, stream);
+}
+
+extern "C" int b200_gen_series(uint64_t seed, int64_t first_day, int64_t n_days, int n_stocks, float* stocks, float* market,
+                               void* stream) {
+    B200_CHECK_ARG(first_day >= 0 && n_days >= 0 && n_stocks > 0, "gen_series: bad sizes");
+    B200_CHECK_ARG(stocks && market, "gen_series: null output pointer");
+    if (n_days == 0) return B200_OK;
+    const int64_t total = (int64_t)(n_stocks + 1) * n_days;
+    int64_t grid = (total + 255) / 256;
+    if (grid > (int64_t)num_sms() * 32) grid = (int64_t)num_sms() * 32;
+    { TimedLaunch _t("gen_series_kernel", (cudaStream_t)stream); gen_series_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(seed, first_day, n_days, n_stocks, stocks, market); }
+    B200_LAUNCH_CHECK("gen_series_kernel");
     return B200_OK;
 }
 

@@ -150,12 +150,17 @@ tc_dropout_bits_kernel(uint64_t seed, int layer, int64_t N, int T, uint32_t thr,
 }
 
 // A loader warp handles NRG consecutive row groups (8 rows each) of a [128 x 64] fp32 tile per batch, starting at
-// row group rg0; lane = (row in group, quarter q): element block (rgi, i) is the float4 at row (rg0 + rgi)*8 + lane/4,
-// columns 4q + 16i .. +3.  tile_load issues all loads of the batch first (one latency per batch), tile_store
+// row group rg0; lane = (row in group rr, quarter q): element block (rgi, i) is the float4 at row (rg0 + rgi)*8 + rr,
+// columns 4q + 16i .. +3.  q = {0,1} live in lanes 0-15 and q = {2,3} in lanes 16-31, so that each half warp of an
+// 8-byte operand store covers one contiguous 128-byte core matrix (the lane / 4, lane % 4 split made every such store
+// a 2-way bank conflict: measured 2x the ideal wavefronts).  tile_load issues all loads of the batch first (one latency per batch), tile_store
 // converts and writes the operand image.
+__device__ __forceinline__ int tile_rr(int lane) { return (lane >> 1) & 7; }
+__device__ __forceinline__ int tile_q(int lane) { return (lane & 1) | ((lane >> 3) & 2); }
+
 template <int NRG>
 __device__ __forceinline__ void tile_load(float4 (&v)[NRG][4], const float* __restrict__ tile_base, int64_t rows_live, int rg0, int lane) {
-    const int rr = lane >> 2, q = lane & 3;
+    const int rr = tile_rr(lane), q = tile_q(lane);
 #pragma unroll
     for (int rgi = 0; rgi < NRG; ++rgi) {
         const int r = (rg0 + rgi) * 8 + rr;
@@ -166,7 +171,7 @@ __device__ __forceinline__ void tile_load(float4 (&v)[NRG][4], const float* __re
 }
 template <int NRG>
 __device__ __forceinline__ void tile_load_bits(uint64_t (&m)[NRG], const uint64_t* __restrict__ bits_base, int64_t rows_live, int rg0, int lane) {
-    const int rr = lane >> 2;
+    const int rr = tile_rr(lane);
 #pragma unroll
     for (int rgi = 0; rgi < NRG; ++rgi) {
         const int r = (rg0 + rgi) * 8 + rr;
@@ -176,7 +181,7 @@ __device__ __forceinline__ void tile_load_bits(uint64_t (&m)[NRG], const uint64_
 template <int NSPLIT, int NRG>
 __device__ __forceinline__ void tile_store(const float4 (&v)[NRG][4], uint8_t* img_hi, uint8_t* img_lo, uint32_t sbo, int kcol0,
                                            int rg0, int lane, bool drop, const uint64_t (&m)[NRG], float inv_keep) {
-    const int rr = lane >> 2, q = lane & 3;
+    const int rr = tile_rr(lane), q = tile_q(lane);
 #pragma unroll
     for (int rgi = 0; rgi < NRG; ++rgi) {
         const int rg = rg0 + rgi;
@@ -968,7 +973,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const int lw = warp - BW_EPI_WARPS;
         const bool drop = drop_bits != nullptr;
         const float inv_keep = 1.0f / (1.0f - p);
-        const int rg_r = lane >> 2, qq = lane & 3;
+        const int rg_r = tile_rr(lane), qq = tile_q(lane);
         int64_t g = 0;
         int ntr = 0;
         const bool tracer = lw == 0 && lane == 0;

@@ -45,24 +45,27 @@ LOG_2PI = math.log(2.0 * math.pi)
 # --------------------------------------------------------------------------- data prep
 
 
-def split_windows(r_stocks, r_market, lookback=60, target=30, stride=None):
+def split_windows(r_stocks, r_market, lookback=60, target=30, stride=None, prediction=True):
     """(S, D) stock and (D,) market series -> X (Nw, S, lookback, 2), y (Nw, S, target, 2).
 
-    Follows lookback_target_split with prediction=True (src/common.py:81-112): channel 0
-    is the stock return, channel 1 the market return broadcast over stocks; windows of
-    lookback+target days start every `stride` days.
+    Follows lookback_target_split (src/common.py:81-112): channel 0 is the stock return, channel 1 the
+    market return broadcast over stocks.  prediction=True: windows of lookback+target days start every
+    `stride` days and y is the part after the look-back; prediction=False (reconstruction,
+    src/common.py:107-110): windows are `lookback` days long and y is their last `target` days.
     """
     if stride is None:
         stride = lookback + target
     S, D = r_stocks.shape
-    total = lookback + target
+    total = lookback + target if prediction else lookback
     n_win = (D - total) // stride + 1
     starts = torch.arange(n_win) * stride
     idx = starts[:, None] + torch.arange(total)[None, :]          # (Nw, total)
     stock = r_stocks[:, idx].permute(1, 0, 2)                       # (Nw, S, total)
     market = r_market[idx][:, None, :].expand(-1, S, -1)            # (Nw, S, total)
     win = torch.stack([stock, market], dim=-1)                      # (Nw, S, total, 2)
-    return win[:, :, :lookback, :], win[:, :, lookback:, :]
+    if prediction:
+        return win[:, :, :lookback, :], win[:, :, lookback:, :]
+    return win, win[:, :, lookback - target:, :]
 
 
 def quadratic_features(X, interaction_only=True):
@@ -95,13 +98,13 @@ def ols_targets(y):
 
 
 def build_dataset(r_stocks, r_market, lookback=60, target=30, stride=90, interaction_only=True,
-                  alphas=None, betas=None):
+                  alphas=None, betas=None, prediction=True):
     """The four tensors of the reference TensorDataset (src/data.py:193-216).
 
     X (Nw,S,60,F), y (Nw,S,30,4) with the true alpha/beta appended as channels 2,3
     (src/data.py:126-130, 213-214), factor (Nw,2), inv_psi (Nw,S).
     """
-    X, y = split_windows(r_stocks, r_market, lookback, target, stride)
+    X, y = split_windows(r_stocks, r_market, lookback, target, stride, prediction)
     X = quadratic_features(X, interaction_only)
     a_hat, b_hat, factor, inv_psi = ols_targets(y)
     if alphas is None or betas is None:

@@ -112,5 +112,33 @@ def main():
               "test", model.test_results["test_loss"])
 
 
+def variants():
+    """golden_variants.npz: the reference's prepare_data body (src/data.py:193-214) on a 25-stock, 400-day slice of the
+    golden series for the switches no shipped config uses: all five quadratic features,
+    the reconstruction split (prediction=False), and no true coefficients (real data: y channels 2, 3 = per-window OLS)."""
+    ref_stubs.install()
+    from src.common import lookback_target_split, add_quadratic_features, ols_features
+    from src.data import _append_feature
+    torch.set_num_threads(1)
+    torch.set_float32_matmul_precision("highest")
+    d = np.load(OUT / "golden_data.npz")
+    rs, rm = torch.from_numpy(d["r_stocks"])[:25, :400].contiguous(), torch.from_numpy(d["r_market"])[:400].contiguous()
+    out = {"r_stocks": rs.numpy(), "r_market": rm.numpy()}
+    for tag, (T, n, stride, pred, inter) in {"f5": (60, 30, 45, True, False), "recon": (60, 30, 45, False, True),
+                                             "real": (60, 30, 5, True, True)}.items():
+        X, y = lookback_target_split(rs, rm, T, n, stride, pred)
+        X = add_quadratic_features(X, interaction_only=inter)
+        a_hat, b_hat, factor, inv_psi = ols_features(y)
+        y = _append_feature(_append_feature(y, a_hat), b_hat)
+        out.update({f"{tag}_X": X.numpy(), f"{tag}_y": y.numpy(), f"{tag}_factor": factor.numpy(),
+                    f"{tag}_inv_psi": inv_psi.numpy(), f"{tag}_cfg": np.array([T, n, stride, int(pred), int(inter)])})
+        print(tag, tuple(X.shape), tuple(y.shape))
+    np.savez_compressed(OUT / "golden_variants.npz", **out)
+
+
 if __name__ == "__main__":
-    main()
+    if "--variants-only" in sys.argv:
+        variants()
+    else:
+        main()
+        variants()

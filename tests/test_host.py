@@ -164,3 +164,37 @@ def test_sweep_plan_assigns_one_gpu_per_job():
     assert len(jobs) == 9
     assert [j["gpu"] for j in jobs] == [0, 1, 2, 3, 4, 5, 6, 7, 0]
     assert jobs[4]["overrides"] == ["datamodule=synthetic", "model=medium", "loss=nll", "trainer=b200"]
+
+
+def test_fama_french_loader(tmp_path):
+    """load_fama_french_25 (mirror of FamaFrench25Portfolios.load, src/data.py:86-123) on CSVs of the published layout:
+    header lines, 3125 skipped old rows, percent returns, -99.99 / -999 missing markers."""
+    rng = np.random.default_rng(0)
+    n_old, n_new = 3125, 40
+    dates = np.arange(19260701, 19260701 + n_old + n_new + 1)
+    mkt, rf = rng.normal(0.03, 1.0, dates.size).round(2), np.full(dates.size, 0.01)
+    p25 = rng.normal(0.04, 1.2, (dates.size, 25)).round(2)
+    p25[n_old + 1 + 7, 3] = -99.99                    # one missing day in the kept part ...
+    rf[n_old + 1 + 7] = 0.0                           # ... on a zero-RF day: the reference tests the marker AFTER subtracting RF (src/data.py:110-113)
+    with open(tmp_path / "F-F_Research_Data_Factors_daily.csv", "w") as f:
+        f.write("line1\nline2\nline3\n\n")             # ff3_skip = 4 lines before the column header
+        for i, dt in enumerate(dates):
+            f.write(f"{dt},{mkt[i]:.2f},0.00,0.00,{rf[i]:.2f}\n")
+    with open(tmp_path / "25_Portfolios_5x5_Daily.csv", "w") as f:
+        f.write("\n" * 18)
+        for i, dt in enumerate(dates):
+            f.write(f"{dt}," + ",".join(f"{v:.2f}" for v in p25[i]) + "\n")
+    stocks, market = B.data.load_fama_french_25(tmp_path)
+    keep = np.ones(n_new, bool); keep[7] = False
+    m = mkt[n_old + 1:][keep].astype(np.float32)
+    p = (p25[n_old + 1:] - rf[n_old + 1:, None]).astype(np.float32)[keep]
+    assert stocks.shape == (25, n_new - 1) and market.shape == (n_new - 1,)
+    np.testing.assert_allclose(market.numpy(), 100 * (np.log(m + 100) - np.log(np.float32(100))), rtol=1e-4, atol=3e-4)   # fp32 cancellation in log(x+100)-log(100)
+    np.testing.assert_allclose(stocks.numpy(), (100 * (np.log(p + 100) - np.log(np.float32(100)))).T, rtol=1e-4, atol=3e-4)
+    ref_root = Path("/root/reference")
+    if ref_root.exists():                             # build container only: the reference's own loader on the same files
+        import ref_stubs
+        src = ref_stubs.install()
+        p_ref, m_ref = src.data.FamaFrench25Portfolios.load(tmp_path)
+        np.testing.assert_allclose(stocks.numpy(), p_ref.numpy(), rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(market.numpy(), m_ref.numpy(), rtol=1e-6, atol=1e-6)

@@ -141,3 +141,17 @@ def test_generator_distribution():
     # determinism / window addressing: window w == days [90w, 90w+90)
     r2, m2, _, _ = O.generate_days(90 * 7, 90, 8, seed=1234)
     assert np.array_equal(r2, r_s[:, 630:720]) and np.array_equal(m2, r_m[630:720])
+
+
+@pytest.mark.parametrize("tag", ["f5", "recon", "real"])
+def test_data_prep_variants_match_reference(tag, golden_dir):
+    """interaction_only=False, the reconstruction split and coefficient-free (real) data: SURVEY.md f3/f4."""
+    g = np.load(golden_dir / "golden_variants.npz")
+    T, n, stride, pred, inter = [int(v) for v in g[f"{tag}_cfg"]]
+    X, y, factor, inv_psi = O.build_dataset(torch.from_numpy(g["r_stocks"]), torch.from_numpy(g["r_market"]), T, n, stride,
+                                            bool(inter), None, None, bool(pred))
+    assert torch.equal(X, torch.from_numpy(g[f"{tag}_X"]))
+    assert torch.equal(y[..., :2], torch.from_numpy(g[f"{tag}_y"])[..., :2])
+    assert torch.allclose(y[..., 2:], torch.from_numpy(g[f"{tag}_y"])[..., 2:], rtol=1e-5, atol=1e-6)
+    assert torch.equal(factor, torch.from_numpy(g[f"{tag}_factor"]))
+    assert torch.allclose(inv_psi, torch.from_numpy(g[f"{tag}_inv_psi"]), rtol=1e-5)

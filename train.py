@@ -49,8 +49,6 @@ def run(cfg):
         raise SystemExit(f"trainer={cfg.trainer.name} is the reference's Lightning path; lightning/hydra are not "
                          "installed here.  Use trainer=b200 (optionally with trainer.max_epochs=..., "
                          "trainer.gradient_clip_val=... to mirror fast/slow/slowest).")
-    if cfg.datamodule.name != "synthetic":
-        raise SystemExit("datamodule=real needs the Fama-French CSVs, which are not shipped (reference train.py:20 TODO)")
 
     tcfg = cfg.trainer
     seed = int(tcfg.get("seed", 1234))
