@@ -4,14 +4,14 @@ Host-side mirror of the reference's operator surface (model / datamodule / train
 CUDA library libb200lstm.so.  The directory name carries a hyphen; import it as
 ``masters_thesis_b200`` (shim module at the repo root) or through importlib.
 """
-from . import _lib
+from . import _lib, data, evaluate
 from ._lib import B200Error, LOSS_KINDS, MODES
 from .config import compose_config
-from .data import DeviceBatch, FinancialLstmDataModule, HostBatchFeeder
+from .data import DeviceBatch, FinancialLstmDataModule, HostBatchFeeder, SeriesBatchSource
 from .engine import LstmEngine
 from .model import FinancialLstm, FinancialLstmCombined, FinancialLstmMse, FinancialLstmNll, get_model_class
 from .trainer import B200Trainer
 
 __all__ = ["B200Error", "B200Trainer", "DeviceBatch", "FinancialLstm", "FinancialLstmCombined",
            "FinancialLstmDataModule", "FinancialLstmMse", "HostBatchFeeder", "FinancialLstmNll", "LOSS_KINDS", "LstmEngine",
-           "MODES", "compose_config", "get_model_class", "_lib"]
+           "MODES", "SeriesBatchSource", "compose_config", "data", "evaluate", "get_model_class", "_lib"]

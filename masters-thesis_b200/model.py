@@ -103,6 +103,19 @@ class FinancialLstm:
         if self.engine is not None:
             self.engine.load_params(flat)
 
+    @classmethod
+    def load_from_checkpoint(cls, checkpoint_path, map_location=None, **overrides):
+        """Lightning's classmethod as test.py:178 uses it: hyper-parameters and weights from a checkpoint written by
+        B200Trainer (or by the reference's ModelCheckpoint: same `state_dict` / `hyper_parameters` keys)."""
+        ck = torch.load(checkpoint_path, map_location="cpu", weights_only=False)
+        hp = dict(ck.get("hyper_parameters", {}))
+        hp.update(overrides)
+        import inspect
+        accepted = inspect.signature(cls.__init__).parameters
+        model = cls(**{k: v for k, v in hp.items() if k in accepted})
+        model.load_state_dict(ck["state_dict"])
+        return model
+
     def forward(self, lstm_input: torch.Tensor):
         """(N, T, F) -> alpha (N,1), beta (N,1); src/model.py:103-109."""
         from .data import DeviceBatch

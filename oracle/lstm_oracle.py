@@ -327,6 +327,43 @@ def test_windows(model, X, y, factor, inv_psi):
     return {"mae": abs_sum / count, "nll": nll_sum / n}
 
 
+def lookback_ols(context):
+    """ols(context[0, :, 1], context[:, :, 0]) of test.py:52 (src/common.py:5-47): per-stock OLS on the market over the
+    look-back days through the same pinv(X^T X) X^T y route."""
+    X = context[0, :, 1]
+    y = context[:, :, 0]
+    D = torch.stack([torch.ones_like(X), X], dim=-1)[None]                  # (1, T, 2)
+    sol = torch.matmul(torch.linalg.pinv(torch.matmul(D.mT, D)), torch.matmul(D.mT, y[None].mT))
+    return sol[0, 0, :], sol[0, 1, :]
+
+
+@torch.no_grad()
+def script_test_windows(model, X, y):
+    """The evaluation script's per-window quantities (test.py:41-89, after transform_test_results): a dictionary of
+    (Nw, S) tensors -- reconstruction residuals (mean over target days), alpha/beta of model, look-back OLS and
+    truth (y channels 2, 3), and their residuals."""
+    model.eval()
+    out = {}
+
+    def put(k, s, v):
+        out.setdefault(k, {}).setdefault(s, []).append(v)
+    for w in range(X.shape[0]):
+        ctx, tgt = X[w], y[w]
+        r_t, m_t, a_t, b_t = tgt[:, :, 0], tgt[:, :, 1], tgt[:, 0, 2], tgt[:, 0, 3]
+        a_m, b_m = model(ctx)
+        a_o, b_o = lookback_ols(ctx)
+        put("recon_residuals", "model", (r_t - (a_m + b_m * m_t)).mean(-1))
+        put("recon_residuals", "ols", (r_t - (a_o[:, None] + b_o[:, None] * m_t)).mean(-1))
+        a_m, b_m = a_m.squeeze(), b_m.squeeze()
+        for k, t_, m_, o_ in (("alpha", a_t, a_m, a_o), ("beta", b_t, b_m, b_o)):
+            put(k + "_residuals", "model", t_ - m_)
+            put(k + "_residuals", "ols", t_ - o_)
+            put(k, "model", m_)
+            put(k, "ols", o_)
+            put(k, "true", t_)
+    return {k: {s: torch.stack(v) for s, v in sub.items()} for k, sub in out.items()}
+
+
 class PlateauSchedule:
     """ReduceLROnPlateau(mode='min', factor=0.5, patience=2) with torch defaults
     (threshold 1e-4 relative, cooldown 0, min_lr 0, eps 1e-8) -- src/model.py:156-161."""

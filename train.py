@@ -59,7 +59,7 @@ def run(cfg):
         target_window=cfg.datamodule.target_window, stride=cfg.datamodule.stride,
         prediction_task=cfg.datamodule.prediction_task, interaction_only=cfg.datamodule.interaction_only,
         batch_size=cfg.datamodule.batch_size, seed=seed, streaming=bool(tcfg.get("streaming", False)),
-        steps_per_epoch=tcfg.get("steps_per_epoch"))
+        steps_per_epoch=tcfg.get("steps_per_epoch"), n_samples=int(tcfg.get("n_samples", 1_000_000)))
 
     ModelClass = b200.get_model_class(cfg.loss.module_class)
     model_params = dict(input_size=cfg.model.input_size, hidden_size=cfg.model.hidden_size,
