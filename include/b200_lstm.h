@@ -151,6 +151,14 @@ B200_API int b200_lstm_bwd(int mode, const float* params, int n_features, int hi
  *   variant 2: D[128][N] = A[K][128]^T * B[K][N]   (weight gradient: A and B images read MN-major)
  * K, N multiples of 16, <= 256. */
 B200_API int b200_tc_selftest(const float* A, const float* B, int variant, int K, int N, float* D, void* stream);
+/* The GEMM of the wide engine (hidden != 64, csrc/lstm_wide.cu) on caller-supplied row-major fp32 device matrices
+ * (no counterpart in the reference; what torch's addmm inside nn.LSTM does there): 128 x 256 output tiles, K chunks
+ * of 64 double-buffered, operands split to bf16 hi(+lo) while staged, fp32 accumulation in TMEM.
+ *   variant 0: C[M][N] = A[M][K] * B[N][K]^T;  variant 1: C = A[M][K] * B[K][N];  variant 2: C = A[K][M]^T * B[K][N]
+ * nsplit 2 = three bf16 products (fp32-grade), 1 = plain bf16.  accumulate != 0 adds to C.  N % 64 == 0; K % 64 == 0
+ * for variants 0, 1; M % 128 == 0 for variant 2, which splits K over CTAs when a workspace (bytes) is given. */
+B200_API int b200_wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C, int64_t M, int N, int64_t K,
+                   int accumulate, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Debug hook (no counterpart in the reference): event trace of CTA 0 of the tcgen05 backward kernel.  The buffer
  * holds 4 roles x 8192 records of {tag, clock64}; NULL switches tracing off.  See tools/trace_bwd.py. */

@@ -68,6 +68,13 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
 int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
                  const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
                  int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+// wide engine (lstm_wide.cu): hidden sizes other than 64 in the tensor-core modes
+size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L);
+int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
+             float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
+                   const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
+                   int training, void* workspace, size_t ws_bytes, cudaStream_t st);
 
 }  // namespace b200
 
@@ -136,6 +143,7 @@ static int check_lstm_args(const char* who, int mode, const float* params, int F
 extern "C" size_t b200_lstm_workspace_bytes(int mode, int64_t n_seq, int T, int n_features, int hidden, int layers) {
     if (n_seq <= 0 || T <= 0 || layers <= 0) return 0;
     // generous default: room for a 64 Ki-sequence da chunk; callers may pass less (smaller chunks)
+    if (hidden != 64) return mode == B200_MODE_FFMA ? 0 : wide_workspace_bytes(n_seq, T, n_features, hidden, layers);
     size_t ffma = ffma_workspace_bytes(n_seq, T, layers);
     if (mode == B200_MODE_FFMA) return ffma;
     size_t tc = tc_workspace_bytes(mode, n_seq, T, n_features, hidden, layers);
@@ -147,6 +155,9 @@ extern "C" int b200_lstm_fwd(int mode, const float* params, int n_features, int 
                              uint64_t dropout_seed, int training, void* workspace, size_t workspace_bytes, void* stream) {
     int rc = check_lstm_args("lstm_fwd", mode, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p);
     if (rc) return rc;
+    if (hidden != 64 && mode != B200_MODE_FFMA)
+        return wide_fwd(mode, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p, dropout_seed, training,
+                        workspace, workspace_bytes, (cudaStream_t)stream);
     if (mode == B200_MODE_FFMA)
         return ffma_fwd(params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dropout_p, dropout_seed, training,
                         (cudaStream_t)stream);
@@ -162,6 +173,9 @@ extern "C" int b200_lstm_bwd_layer(int mode, int layer, const float* params, int
     if (rc) return rc;
     B200_CHECK_ARG(layer >= 0 && layer < layers, "lstm_bwd: layer %d out of range", layer);
     B200_CHECK_ARG(dhT && grads && workspace, "lstm_bwd: null pointer");
+    if (hidden != 64 && mode != B200_MODE_FFMA)
+        return wide_bwd_layer(mode, layer, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dhT, grads, dropout_p,
+                              dropout_seed, training, workspace, workspace_bytes, (cudaStream_t)stream);
     if (mode == B200_MODE_FFMA)
         return ffma_bwd_layer(layer, params, n_features, hidden, layers, x, n_seq, T, stash_h, stash_c, dhT, grads, dropout_p,
                               dropout_seed, training, workspace, workspace_bytes, (cudaStream_t)stream);

@@ -1,0 +1,604 @@
+// Wide-model LSTM engine: hidden sizes other than 64 (BASELINE.json configs[2]: hidden 256, 8 layers).
+//
+// At H = 256 one layer's weights (W_ih, W_hh: 2 x 1024 x 256) no longer fit one SM's shared memory next to the
+// operands, and a 128-row tile's gates (128 x 1024 fp32) no longer fit TMEM, so the persistent fused kernels of
+// lstm_tc.cu do not apply.  This engine is the cuDNN-style decomposition on hand-written tcgen05 GEMMs:
+//
+//   forward  layer l:  G[T*N x 4H]  = dropout(h^{l-1})[T*N x H] . W_ih^T            one GEMM over all steps (l > 0)
+//            step t:   G_t[N x 4H] += h_{t-1}[N x H] . W_hh^T                       GEMM (accumulate), t > 0
+//                      cell kernel: + bias (+ x_t . W_ih^T for layer 0, K = F <= 8 on CUDA cores), activations,
+//                                   c_t, h_t; G_t is overwritten with the ACTIVATED gates (the backward stash)
+//   backward step t:   cell kernel: (dh_t, dc_t, gates, c) -> dG_t (overwrites G_t), dc_{t-1}
+//                      dh_{t-1}[N x H] = dG_t[N x 4H] . W_hh                        GEMM, B operand read MN-major
+//            layer l:  dW_hh = dG[1..T-1]^T . h[0..T-2]     dW_ih = dG^T . dropout(h^{l-1})    split-K GEMMs, both MN-major
+//                      dX = dG . W_ih (then the dropout mask) = d_out of layer l-1;   db = column sums of dG
+//
+// One GEMM kernel serves all of it: C[M x N] (+)= op(A) . op(B) with fp32 operands in global memory that are split
+// into bf16 hi (+ lo) images while being staged (the "interleaved" UMMA layout of tc_common.cuh), fp32 accumulation
+// in TMEM, 128 x 256 output tiles, K chunks of 64 double-buffered in shared memory: all threads stage chunk k+1
+// while the tensor core works on chunk k.  NSPLIT = 2 (B200_MODE_TC_PRECISE) issues hi*hi + lo*hi + hi*lo, NSPLIT = 1
+// (B200_MODE_TC_FAST) is the plain bf16 GEMM with fp32 accumulation that configs[2] names.
+//
+// Replaces, for hidden != 64: nn.LSTM forward/backward (src/model.py:88-109, autograd), as lstm_tc.cu does for 64.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace b200 {
+using namespace tc;
+
+namespace {
+
+constexpr int GM = 128;            // output tile rows = UMMA M
+constexpr int GN = 256;            // output tile columns (max UMMA N)
+constexpr int GK = 64;             // K chunk per pipeline stage
+constexpr int G_THREADS = 256;
+constexpr int MAX_SPLITS = 32;
+
+// operand variants (how A and B are stored in global memory, all row-major fp32)
+//   0: A [M x K], B [N x K]      C = A . B^T          both images K-major
+//   1: A [M x K], B [K x N]      C = A . B            B image read MN-major
+//   2: A [K x M], B [K x N]      C = A^T . B          both images read MN-major (K = rows: split-K over CTAs)
+struct GemmArgs {
+    const float* A; const float* B; float* C;
+    int64_t M; int N; int64_t K;
+    int64_t lda, ldb, ldc;
+    int accumulate;                // C += (ignored when part != nullptr)
+    int64_t k_per_split;           // multiple of GK
+    float* part;                   // split-K partials [splits][M x N] (variant 2), or nullptr
+};
+
+__device__ __forceinline__ int blk_rr(int lane) { return (lane >> 1) & 7; }
+__device__ __forceinline__ int blk_q(int lane) { return (lane & 1) | ((lane >> 3) & 2); }
+
+// A warp moves NRG row groups (8 rows each) x 64 columns of a row-major fp32 matrix (leading dimension ld) into an
+// operand image: lane = (row in group, column quarter); rows >= rows_live read as zero.
+template <int NRG>
+__device__ __forceinline__ void blk_load(float4 (&v)[NRG][4], const float* base, int64_t ld, int64_t rows_live, int rg0, int lane) {
+    const int rr = blk_rr(lane), q = blk_q(lane);
+#pragma unroll
+    for (int rgi = 0; rgi < NRG; ++rgi) {
+        const int r = (rg0 + rgi) * 8 + rr;
+        const float* src = base + (int64_t)r * ld + 4 * q;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            v[rgi][i] = r < rows_live ? *reinterpret_cast<const float4*>(src + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+// image: rows x cols bf16, 8 x 8 core matrices of 128 contiguous bytes, sbo = bytes between 8-row groups
+template <int NSPLIT, int NRG>
+__device__ __forceinline__ void blk_store(const float4 (&v)[NRG][4], uint8_t* img_hi, uint8_t* img_lo, uint32_t sbo, int col0,
+                                          int rg0, int lane) {
+    const int rr = blk_rr(lane), q = blk_q(lane);
+#pragma unroll
+    for (int rgi = 0; rgi < NRG; ++rgi) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int c = col0 + 4 * q + 16 * i;
+            const float4 x = v[rgi][i];
+            uint2 hi2, lo2;
+            split2(x.x, x.y, hi2.x, lo2.x);
+            split2(x.z, x.w, hi2.y, lo2.y);
+            const uint32_t o = (uint32_t)(rg0 + rgi) * sbo + (uint32_t)(c >> 3) * LBO_BYTES + (uint32_t)rr * 16 + (uint32_t)(c & 7) * 2;
+            *reinterpret_cast<uint2*>(img_hi + o) = hi2;
+            if (NSPLIT == 2) *reinterpret_cast<uint2*>(img_lo + o) = lo2;
+        }
+    }
+}
+
+template <int NSPLIT>
+struct GemmSmem {
+    static constexpr uint32_t A_IMG = GM * GK * 2, B_IMG = GN * GK * 2;           // one bf16 image
+    static constexpr uint32_t STAGE = NSPLIT * (A_IMG + B_IMG);
+    static constexpr uint32_t off_bar = 2 * STAGE;                                // 2 stage barriers + done
+    static constexpr uint32_t off_tmem = off_bar + 3 * 8;
+    static constexpr uint32_t total = off_tmem + 16 + 128;
+};
+
+template <int NSPLIT, int VAR>
+__global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
+    using S = GemmSmem<NSPLIT>;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t m0 = (int64_t)blockIdx.x * GM;
+    const int n0 = blockIdx.y * GN;
+    const int NT = a.N - n0 < GN ? a.N - n0 : GN;          // multiple of 64
+    const int64_t k_beg = (int64_t)blockIdx.z * a.k_per_split;
+    const int64_t k_end = k_beg + a.k_per_split < a.K ? k_beg + a.k_per_split : a.K;
+    const int nchunks = (int)((k_end - k_beg + GK - 1) / GK);
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_slot, GN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const uint32_t sbo_k = (uint32_t)(GK / 8) * LBO_BYTES;           // K-major image of [rows x 64]
+    const uint32_t sbo_am = (uint32_t)(GM / 8) * LBO_BYTES;          // MN-major A image [64 x 128]
+    const uint32_t sbo_bm = (uint32_t)(NT / 8) * LBO_BYTES;          // MN-major B image [64 x NT]
+    const uint32_t idesc = make_idesc_bf16(GM, NT, VAR == 2 ? 1 : 0, VAR == 0 ? 0 : 1);
+
+    for (int kc = 0; kc < nchunks; ++kc) {
+        const int s = kc & 1;
+        uint8_t* a_hi = smem + s * S::STAGE;
+        uint8_t* a_lo = a_hi + S::A_IMG;
+        uint8_t* b_hi = a_hi + NSPLIT * S::A_IMG;
+        uint8_t* b_lo = b_hi + S::B_IMG;
+        const int64_t k0 = k_beg + (int64_t)kc * GK;
+        if (kc >= 2) mbar_wait(&bars[s], (uint32_t)(((kc >> 1) - 1) & 1));      // MMAs of chunk kc - 2 have read this stage
+        // ---- stage A ------------------------------------------------------------------------------------------
+        if (VAR != 2) {                       // [128 rows x 64 k]: 16 row groups, 2 per warp
+            float4 v[2][4];
+            blk_load<2>(v, a.A + m0 * a.lda + k0, a.lda, a.M - m0, 2 * warp, lane);
+            blk_store<NSPLIT, 2>(v, a_hi, a_lo, sbo_k, 0, 2 * warp, lane);
+        } else {                              // [64 k-rows x 128 m-cols]: 2 column blocks x 4 row-group pairs
+            const int cb = warp >> 2, pr = warp & 3;
+            float4 v[2][4];
+            blk_load<2>(v, a.A + k0 * a.lda + m0 + cb * 64, a.lda, k_end - k0, 2 * pr, lane);
+            blk_store<NSPLIT, 2>(v, a_hi, a_lo, sbo_am, cb * 64, 2 * pr, lane);
+        }
+        // ---- stage B ------------------------------------------------------------------------------------------
+        if (VAR == 0) {                       // [NT rows x 64 k]: NT / 8 row groups, pairs round-robin over the warps
+            for (int pr = warp; pr < NT / 16; pr += G_THREADS / 32) {
+                float4 v[2][4];
+                blk_load<2>(v, a.B + (int64_t)n0 * a.ldb + k0, a.ldb, NT, 2 * pr, lane);
+                blk_store<NSPLIT, 2>(v, b_hi, b_lo, sbo_k, 0, 2 * pr, lane);
+            }
+        } else {                              // [64 k-rows x NT cols]: (column block, row-group pair) units
+            for (int u = warp; u < (NT / 64) * 4; u += G_THREADS / 32) {
+                const int cb = u >> 2, pr = u & 3;
+                float4 v[2][4];
+                blk_load<2>(v, a.B + k0 * a.ldb + n0 + cb * 64, a.ldb, k_end - k0, 2 * pr, lane);
+                blk_store<NSPLIT, 2>(v, b_hi, b_lo, sbo_bm, cb * 64, 2 * pr, lane);
+            }
+        }
+        fence_proxy_async();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            tc_fence_after();
+            const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
+#pragma unroll
+            for (int ks = 0; ks < GK / 16; ++ks) {
+                uint64_t dah, dal, dbh, dbl;
+                if (VAR != 2) { dah = make_desc(ah + ks * 2 * LBO_BYTES, LBO_BYTES, sbo_k); dal = make_desc(al + ks * 2 * LBO_BYTES, LBO_BYTES, sbo_k); }
+                else { dah = make_desc(ah + ks * 2 * sbo_am, sbo_am, LBO_BYTES); dal = make_desc(al + ks * 2 * sbo_am, sbo_am, LBO_BYTES); }
+                if (VAR == 0) { dbh = make_desc(bh + ks * 2 * LBO_BYTES, LBO_BYTES, sbo_k); dbl = make_desc(bl + ks * 2 * LBO_BYTES, LBO_BYTES, sbo_k); }
+                else { dbh = make_desc(bh + ks * 2 * sbo_bm, sbo_bm, LBO_BYTES); dbl = make_desc(bl + ks * 2 * sbo_bm, sbo_bm, LBO_BYTES); }
+                umma_bf16(tmem_base, dah, dbh, idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                if (NSPLIT == 2) {
+                    umma_bf16(tmem_base, dal, dbh, idesc, 1);
+                    umma_bf16(tmem_base, dah, dbl, idesc, 1);
+                }
+            }
+            umma_commit(&bars[s]);
+            if (kc == nchunks - 1) umma_commit(&bars[2]);
+        }
+    }
+    // ---- epilogue: TMEM -> C (warp = TMEM lane quarter x column half) ------------------------------------------
+    if (nchunks > 0) {
+        mbar_wait(&bars[2], 0u);
+        tc_fence_after();
+    }
+    {
+        const int lq = warp & 3, ch = warp >> 2;
+        const int64_t row = m0 + lq * 32 + lane;
+        float* crow = a.part ? a.part + ((int64_t)blockIdx.z * a.M + row) * a.N + n0 : a.C + row * a.ldc + n0;
+        for (int c0 = ch * (NT / 2); c0 < (ch + 1) * (NT / 2); c0 += 8) {
+            float v[8];
+            if (nchunks > 0) {
+                tmem_ld8(tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)c0, v);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = 0.f;
+            }
+            if (row < a.M) {
+                float4* dst = reinterpret_cast<float4*>(crow + c0);
+                float4 lo = make_float4(v[0], v[1], v[2], v[3]), hi = make_float4(v[4], v[5], v[6], v[7]);
+                if (!a.part && a.accumulate) {
+                    const float4 o0 = dst[0], o1 = dst[1];
+                    lo.x += o0.x; lo.y += o0.y; lo.z += o0.z; lo.w += o0.w;
+                    hi.x += o1.x; hi.y += o1.y; hi.z += o1.z; hi.w += o1.w;
+                }
+                dst[0] = lo;
+                dst[1] = hi;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, GN);
+}
+
+// C[i] = sum over splits of part[z][i] in fixed order (bit-identical run to run)
+__global__ void __launch_bounds__(256) wide_splitk_reduce_kernel(const float* __restrict__ part, int splits, int64_t n, float* __restrict__ C) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += part[(int64_t)z * n + i];
+        C[i] = s;
+    }
+}
+
+template <int NSPLIT, int VAR>
+int launch_gemm_t(GemmArgs a, int splits, cudaStream_t st, const char* name) {
+    using S = GemmSmem<NSPLIT>;
+    auto kern = wide_gemm_kernel<NSPLIT, VAR>;
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
+    dim3 grid((unsigned)((a.M + GM - 1) / GM), (unsigned)((a.N + GN - 1) / GN), (unsigned)splits);
+    {
+        TimedLaunch _t(name, st);
+        kern<<<grid, G_THREADS, S::total, st>>>(a);
+    }
+    B200_LAUNCH_CHECK("wide_gemm_kernel");
+    return B200_OK;
+}
+
+}  // namespace
+
+// C (+)= op(A) . op(B); see the variant table above.  Split-K (variant 2 only) needs `part`.
+int wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C, int64_t M, int N, int64_t K, int64_t lda,
+              int64_t ldb, int64_t ldc, int accumulate, float* part, size_t part_floats, cudaStream_t st, const char* name) {
+    B200_CHECK_ARG(nsplit == 1 || nsplit == 2, "wide_gemm: nsplit must be 1 or 2");
+    B200_CHECK_ARG(variant >= 0 && variant <= 2, "wide_gemm: variant must be 0, 1 or 2");
+    B200_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0, "wide_gemm: bad arguments (M=%lld N=%d K=%lld)", (long long)M, N, (long long)K);
+    B200_CHECK_ARG(N % 64 == 0, "wide_gemm: N must be a multiple of 64, got %d", N);
+    B200_CHECK_ARG(variant == 2 || K % GK == 0, "wide_gemm: K must be a multiple of 64 for variants 0 and 1, got %lld", (long long)K);
+    B200_CHECK_ARG(variant != 2 || M % GM == 0, "wide_gemm: M must be a multiple of 128 for variant 2, got %lld", (long long)M);
+    B200_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0, "wide_gemm: leading dimensions must be multiples of 4 floats");
+    B200_CHECK_ARG((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "wide_gemm: pointers must be 16-byte aligned");
+    GemmArgs a{A, B, C, M, N, K, lda, ldb, ldc, accumulate, 0, nullptr};
+    int splits = 1;
+    const int64_t chunks = (K + GK - 1) / GK;
+    if (variant == 2 && part) {
+        const int64_t tiles = ((M + GM - 1) / GM) * ((N + GN - 1) / GN);
+        int64_t want = (2 * (int64_t)num_sms() + tiles - 1) / tiles;          // about two waves of CTAs
+        if (want > MAX_SPLITS) want = MAX_SPLITS;
+        if (want > chunks) want = chunks;
+        const int64_t fit = (int64_t)(part_floats / ((size_t)M * N));
+        if (want > fit) want = fit;
+        if (want > 1) splits = (int)want;
+    }
+    a.k_per_split = ((chunks + splits - 1) / splits) * GK;
+    splits = (int)((K + a.k_per_split - 1) / a.k_per_split);
+    if (splits > 1) a.part = part;
+    B200_CHECK_ARG(splits == 1 || ldc == N, "wide_gemm: split-K needs a dense C");
+    int rc;
+    if (nsplit == 2) rc = variant == 0 ? launch_gemm_t<2, 0>(a, splits, st, name) : variant == 1 ? launch_gemm_t<2, 1>(a, splits, st, name) : launch_gemm_t<2, 2>(a, splits, st, name);
+    else rc = variant == 0 ? launch_gemm_t<1, 0>(a, splits, st, name) : variant == 1 ? launch_gemm_t<1, 1>(a, splits, st, name) : launch_gemm_t<1, 2>(a, splits, st, name);
+    if (rc) return rc;
+    if (splits > 1) {
+        const int64_t n = M * N;
+        int64_t grid = (n + 255) / 256;
+        if (grid > (int64_t)num_sms() * 8) grid = (int64_t)num_sms() * 8;
+        { TimedLaunch _t("wide_splitk_reduce_kernel", st); wide_splitk_reduce_kernel<<<(unsigned)grid, 256, 0, st>>>(part, splits, n, C); }
+        B200_LAUNCH_CHECK("wide_splitk_reduce_kernel");
+    }
+    return B200_OK;
+}
+
+namespace {
+
+// ------------------------------------------------------------------------------------------- pointwise kernels
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+
+// forward cell of step t of one layer: G_t [N][4H] holds the GEMM part of the gate pre-activations (nothing for
+// layer 0 at t = 0); adds bias (and x_t . W_ih^T for layer 0), writes activated gates, c_t, h_t
+__global__ void __launch_bounds__(256)
+wide_cell_fwd_kernel(float* __restrict__ G, const float* __restrict__ b_ih, const float* __restrict__ b_hh,
+                     const float* __restrict__ x_t, const float* __restrict__ w_ih0, int F, int has_gemm,
+                     const float* __restrict__ c_prev, float* __restrict__ c_out, float* __restrict__ h_out, int64_t N, int H) {
+    const int64_t total = N * H;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t n = i / H;
+        const int u = (int)(i - n * H);
+        float* g = G + n * 4 * H;
+        float pre[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int j = k * H + u;
+            float v = (has_gemm ? g[j] : 0.f) + (b_ih[j] + b_hh[j]);
+            if (w_ih0) for (int f = 0; f < F; ++f) v = fmaf(x_t[n * F + f], w_ih0[j * F + f], v);
+            pre[k] = v;
+        }
+        const float ig = sigmoidf_(pre[0]), fg = sigmoidf_(pre[1]), gg = tanhf(pre[2]), og = sigmoidf_(pre[3]);
+        const float c = fg * (c_prev ? c_prev[i] : 0.f) + ig * gg;
+        g[u] = ig; g[H + u] = fg; g[2 * H + u] = gg; g[3 * H + u] = og;
+        c_out[i] = c;
+        h_out[i] = og * tanhf(c);
+    }
+}
+
+// backward cell of step t: activated gates in G_t are overwritten with the pre-activation gradients
+__global__ void __launch_bounds__(256)
+wide_cell_bwd_kernel(float* __restrict__ G, const float* __restrict__ c_t, const float* __restrict__ c_prev,
+                     const float* __restrict__ d_out_t, const float* __restrict__ dhT, const float* __restrict__ dh_rec,
+                     float* __restrict__ dc, int first, int64_t N, int H) {
+    const int64_t total = N * H;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t n = i / H;
+        const int u = (int)(i - n * H);
+        float* g = G + n * 4 * H;
+        const float ig = g[u], fg = g[H + u], gg = g[2 * H + u], og = g[3 * H + u];
+        float dh = 0.f;
+        if (d_out_t) dh += d_out_t[i];
+        if (dhT) dh += dhT[i];
+        if (dh_rec) dh += dh_rec[i];
+        const float tc = tanhf(c_t[i]);
+        const float dcc = (first ? 0.f : dc[i]) + dh * og * (1.f - tc * tc);
+        const float cp = c_prev ? c_prev[i] : 0.f;
+        dc[i] = dcc * fg;
+        g[u] = dcc * gg * ig * (1.f - ig);
+        g[H + u] = dcc * cp * fg * (1.f - fg);
+        g[2 * H + u] = dcc * ig * (1.f - gg * gg);
+        g[3 * H + u] = dh * tc * og * (1.f - og);
+    }
+}
+
+// dst = src * keep / (1 - p) with the keep mask of the LSTM kernels (common.cuh: one Philox block per 8 units)
+__global__ void __launch_bounds__(256)
+wide_dropout_kernel(uint64_t seed, int layer, int64_t N, int T, int H, float p, const float* src, float* dst) {   // src may alias dst
+    const uint32_t thr = dropout_threshold(p);
+    const float scale = 1.0f / (1.0f - p);
+    const int HB = H / 8;
+    const int64_t total = (int64_t)T * N * HB;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int ub = (int)(i % HB);
+        const int64_t rt = i / HB;
+        const int64_t row = rt % N;
+        const int t = (int)(rt / N);
+        const U4 b = dropout_block(seed, layer, row, t, ub);
+        const float4* s4 = reinterpret_cast<const float4*>(src + rt * H + ub * 8);
+        float4 a0 = s4[0], a1 = s4[1];
+        a0.x = dropout_lane16(b, 0) >= thr ? a0.x * scale : 0.f; a0.y = dropout_lane16(b, 1) >= thr ? a0.y * scale : 0.f;
+        a0.z = dropout_lane16(b, 2) >= thr ? a0.z * scale : 0.f; a0.w = dropout_lane16(b, 3) >= thr ? a0.w * scale : 0.f;
+        a1.x = dropout_lane16(b, 4) >= thr ? a1.x * scale : 0.f; a1.y = dropout_lane16(b, 5) >= thr ? a1.y * scale : 0.f;
+        a1.z = dropout_lane16(b, 6) >= thr ? a1.z * scale : 0.f; a1.w = dropout_lane16(b, 7) >= thr ? a1.w * scale : 0.f;
+        float4* d4 = reinterpret_cast<float4*>(dst + rt * H + ub * 8);
+        d4[0] = a0;
+        d4[1] = a1;
+    }
+}
+
+// column sums of dG [R][C] (bias gradient) and, for layer 0, dG^T . x (x [R][F], F <= 8): per-CTA partials over a slab
+// of rows, then a fixed-order reduce.  part [nslab][C][F + 1]: column F = the plain sum
+constexpr int CS_MAXF = 8;
+__global__ void __launch_bounds__(256)
+wide_colsum_kernel(const float* __restrict__ dG, const float* __restrict__ x, int F, int64_t R, int C, int64_t rows_per_slab,
+                   float* __restrict__ part) {
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
+    const int64_t r1 = r0 + rows_per_slab < R ? r0 + rows_per_slab : R;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < C; j += gridDim.x * blockDim.x) {
+        float acc[CS_MAXF + 1];
+#pragma unroll
+        for (int f = 0; f <= CS_MAXF; ++f) acc[f] = 0.f;
+        for (int64_t r = r0; r < r1; ++r) {
+            const float g = dG[r * C + j];
+            acc[CS_MAXF] += g;
+#pragma unroll
+            for (int f = 0; f < CS_MAXF; ++f) if (f < F) acc[f] = fmaf(g, x[r * F + f], acc[f]);
+        }
+        float* o = part + ((int64_t)blockIdx.y * C + j) * (F + 1);
+        for (int f = 0; f < F; ++f) o[f] = acc[f];
+        o[F] = acc[CS_MAXF];
+    }
+}
+__global__ void __launch_bounds__(256)
+wide_colsum_reduce_kernel(const float* __restrict__ part, int nslab, int C, int F, float* __restrict__ gw_ih0,
+                          float* __restrict__ gb_ih, float* __restrict__ gb_hh) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < C * (F + 1); i += gridDim.x * blockDim.x) {
+        const int j = i / (F + 1), f = i - j * (F + 1);
+        float s = 0.f;
+        for (int z = 0; z < nslab; ++z) s += part[((int64_t)z * C + j) * (F + 1) + f];
+        if (f < F) { if (gw_ih0) gw_ih0[j * F + f] = s; }
+        else { gb_ih[j] = s; gb_hh[j] = s; }
+    }
+}
+
+inline unsigned ew_grid(int64_t n) {
+    int64_t g = (n + 255) / 256;
+    const int64_t cap = (int64_t)num_sms() * 16;
+    return (unsigned)(g < cap ? (g > 0 ? g : 1) : cap);
+}
+
+struct WideWs {
+    float* G;        // [L][T][N][4H] gates (forward: activated; backward: overwritten with dG layer by layer)
+    float* xd;       // [T][N][H]     dropped input of the layer being processed
+    float* dx[2];    // [T][N][H]     d_out ping-pong between layers
+    float* dh_rec;   // [N][H]
+    float* dc;       // [N][H]
+    float* part;     // split-K partials / column-sum partials
+    size_t part_floats;
+};
+constexpr int COLSUM_SLABS = 64;
+
+size_t wide_part_floats(int H, int F) {
+    const size_t gemm = (size_t)MAX_SPLITS * 4 * H * H;
+    const size_t cs = (size_t)COLSUM_SLABS * 4 * H * (CS_MAXF + 1);
+    (void)F;
+    return gemm > cs ? gemm : cs;
+}
+size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+bool wide_ws(void* workspace, size_t ws_bytes, int64_t N, int T, int F, int H, int L, WideWs* w) {
+    uint8_t* p = (uint8_t*)workspace;
+    const size_t lsz = (size_t)T * N * H * 4;
+    size_t off = 0;
+    w->G = (float*)(p + off); off += al256((size_t)L * lsz * 4);
+    w->xd = (float*)(p + off); off += al256(lsz);
+    w->dx[0] = (float*)(p + off); off += al256(lsz);
+    w->dx[1] = (float*)(p + off); off += al256(lsz);
+    w->dh_rec = (float*)(p + off); off += al256((size_t)N * H * 4);
+    w->dc = (float*)(p + off); off += al256((size_t)N * H * 4);
+    w->part = (float*)(p + off);
+    w->part_floats = wide_part_floats(H, F);
+    off += al256(w->part_floats * 4);
+    return workspace != nullptr && off <= ws_bytes;
+}
+
+struct LayerParams { const float *w_ih, *w_hh, *b_ih, *b_hh; int in; };
+LayerParams layer_params(const float* params, int F, int H, int l) {
+    int64_t off = 0;
+    for (int i = 0; i < l; ++i) off += 4LL * H * (i == 0 ? F : H) + 4LL * H * H + 8LL * H;
+    const int in = l == 0 ? F : H;
+    LayerParams lp;
+    lp.in = in;
+    lp.w_ih = params + off;
+    lp.w_hh = lp.w_ih + 4LL * H * in;
+    lp.b_ih = lp.w_hh + 4LL * H * H;
+    lp.b_hh = lp.b_ih + 4LL * H;
+    return lp;
+}
+
+}  // namespace
+
+size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L) {
+    const size_t lsz = (size_t)T * N * H * 4;
+    return al256((size_t)L * lsz * 4) + 3 * al256(lsz) + 2 * al256((size_t)N * H * 4) + al256(wide_part_floats(H, F) * 4) + 256;
+}
+
+static int wide_check(const char* who, int H, int F) {
+    B200_CHECK_ARG(H % 64 == 0 && H >= 128, "%s: the wide engine needs a hidden size that is a multiple of 64 and >= 128, got %d", who, H);
+    B200_CHECK_ARG(F <= CS_MAXF, "%s: at most %d input features", who, CS_MAXF);
+    return B200_OK;
+}
+
+int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
+             float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
+    int rc = wide_check("lstm_fwd", H, F);
+    if (rc) return rc;
+    WideWs w;
+    B200_CHECK_ARG(wide_ws(workspace, ws_bytes, N, T, F, H, L, &w), "lstm_fwd (wide): workspace too small (%zu bytes, need %zu)", ws_bytes,
+                   wide_workspace_bytes(N, T, F, H, L));
+    const int nsplit = mode == B200_MODE_TC_PRECISE ? 2 : 1;
+    const bool drop = training && p > 0.f;
+    const int64_t lsz = (int64_t)T * N * H, NH = N * H, G4 = 4LL * H;
+    for (int l = 0; l < L; ++l) {
+        const LayerParams lp = layer_params(params, F, H, l);
+        float* G = w.G + (int64_t)l * lsz * 4;
+        float* hs = stash_h + (int64_t)l * lsz;
+        float* cs = stash_c + (int64_t)l * lsz;
+        if (l > 0) {
+            const float* xin = stash_h + (int64_t)(l - 1) * lsz;
+            if (drop) {
+                { TimedLaunch _t("wide_dropout_kernel", st); wide_dropout_kernel<<<ew_grid((int64_t)T * N * (H / 8)), 256, 0, st>>>(seed, l, N, T, H, p, xin, w.xd); }
+                B200_LAUNCH_CHECK("wide_dropout_kernel");
+                xin = w.xd;
+            }
+            rc = wide_gemm(nsplit, 0, xin, lp.w_ih, G, (int64_t)T * N, (int)G4, H, H, H, G4, 0, nullptr, 0, st, "wide_gemm_xproj");
+            if (rc) return rc;
+        }
+        for (int t = 0; t < T; ++t) {
+            float* Gt = G + (int64_t)t * N * G4;
+            if (t > 0) {
+                rc = wide_gemm(nsplit, 0, hs + (int64_t)(t - 1) * NH, lp.w_hh, Gt, N, (int)G4, H, H, H, G4, l > 0 ? 1 : 0, nullptr, 0, st,
+                               "wide_gemm_rec_fwd");
+                if (rc) return rc;
+            }
+            {
+                TimedLaunch _t("wide_cell_fwd_kernel", st);
+                wide_cell_fwd_kernel<<<ew_grid(NH), 256, 0, st>>>(Gt, lp.b_ih, lp.b_hh, l == 0 ? x + (int64_t)t * N * F : nullptr,
+                                                                  l == 0 ? lp.w_ih : nullptr, F, (l > 0 || t > 0) ? 1 : 0,
+                                                                  t > 0 ? cs + (int64_t)(t - 1) * NH : nullptr, cs + (int64_t)t * NH,
+                                                                  hs + (int64_t)t * NH, N, H);
+            }
+            B200_LAUNCH_CHECK("wide_cell_fwd_kernel");
+        }
+    }
+    return B200_OK;
+}
+
+// Backward of one layer (layers must be called top-down; the forward's gate stash in the workspace is consumed).
+int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
+                   const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
+                   int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
+    int rc = wide_check("lstm_bwd", H, F);
+    if (rc) return rc;
+    WideWs w;
+    B200_CHECK_ARG(wide_ws(workspace, ws_bytes, N, T, F, H, L, &w), "lstm_bwd (wide): workspace too small (%zu bytes)", ws_bytes);
+    const int nsplit = mode == B200_MODE_TC_PRECISE ? 2 : 1;
+    const bool drop = training && p > 0.f;
+    const int64_t lsz = (int64_t)T * N * H, NH = N * H, G4 = 4LL * H;
+    const int l = layer;
+    const LayerParams lp = layer_params(params, F, H, l);
+    const int64_t poff = lp.w_ih - params;
+    float* gw_ih = grads + poff;
+    float* gw_hh = gw_ih + 4LL * H * lp.in;
+    float* gb_ih = gw_hh + 4LL * H * H;
+    float* gb_hh = gb_ih + 4LL * H;
+    float* G = w.G + (int64_t)l * lsz * 4;
+    const float* hs = stash_h + (int64_t)l * lsz;
+    const float* cs = stash_c + (int64_t)l * lsz;
+    const bool top = l == L - 1;
+    const float* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
+    float* d_in = w.dx[(L - 1 - l) & 1];
+
+    for (int t = T - 1; t >= 0; --t) {
+        float* Gt = G + (int64_t)t * N * G4;
+        {
+            TimedLaunch _t("wide_cell_bwd_kernel", st);
+            wide_cell_bwd_kernel<<<ew_grid(NH), 256, 0, st>>>(Gt, cs + (int64_t)t * NH, t > 0 ? cs + (int64_t)(t - 1) * NH : nullptr,
+                                                              d_out ? d_out + (int64_t)t * NH : nullptr, (top && t == T - 1) ? dhT : nullptr,
+                                                              t < T - 1 ? w.dh_rec : nullptr, w.dc, t == T - 1 ? 1 : 0, N, H);
+        }
+        B200_LAUNCH_CHECK("wide_cell_bwd_kernel");
+        if (t > 0) {
+            rc = wide_gemm(nsplit, 1, Gt, lp.w_hh, w.dh_rec, N, H, G4, G4, H, H, 0, nullptr, 0, st, "wide_gemm_rec_bwd");
+            if (rc) return rc;
+        }
+    }
+    // weight gradients: dW_hh = dG[1..T-1]^T . h[0..T-2]
+    if (T > 1) {
+        rc = wide_gemm(nsplit, 2, G + N * G4, hs, gw_hh, G4, H, (int64_t)(T - 1) * N, G4, H, H, 0, w.part, w.part_floats, st, "wide_gemm_wgrad_hh");
+        if (rc) return rc;
+    } else {
+        B200_CUDA(cudaMemsetAsync(gw_hh, 0, sizeof(float) * 4 * H * H, st));
+    }
+    const int64_t R = (int64_t)T * N;
+    if (l > 0) {
+        const float* xin = stash_h + (int64_t)(l - 1) * lsz;
+        if (drop) {
+            { TimedLaunch _t("wide_dropout_kernel", st); wide_dropout_kernel<<<ew_grid(R * (H / 8)), 256, 0, st>>>(seed, l, N, T, H, p, xin, w.xd); }
+            B200_LAUNCH_CHECK("wide_dropout_kernel");
+            xin = w.xd;
+        }
+        rc = wide_gemm(nsplit, 2, G, xin, gw_ih, G4, H, R, G4, H, H, 0, w.part, w.part_floats, st, "wide_gemm_wgrad_ih");
+        if (rc) return rc;
+        // d_out of the layer below: dX = dG . W_ih, then the mask that was applied to this layer's input
+        rc = wide_gemm(nsplit, 1, G, lp.w_ih, d_in, R, H, G4, G4, H, H, 0, nullptr, 0, st, "wide_gemm_dgrad_x");
+        if (rc) return rc;
+        if (drop) {
+            { TimedLaunch _t("wide_dropout_kernel", st); wide_dropout_kernel<<<ew_grid(R * (H / 8)), 256, 0, st>>>(seed, l, N, T, H, p, d_in, d_in); }
+            B200_LAUNCH_CHECK("wide_dropout_kernel");
+        }
+    }
+    // bias gradients (and layer 0's dW_ih, K = F on CUDA cores)
+    {
+        const int Fx = l == 0 ? F : 0;
+        int64_t rows_per = (R + COLSUM_SLABS - 1) / COLSUM_SLABS;
+        const int nslab = (int)((R + rows_per - 1) / rows_per);
+        dim3 grid((unsigned)((G4 + 255) / 256), (unsigned)nslab);
+        { TimedLaunch _t("wide_colsum_kernel", st); wide_colsum_kernel<<<grid, 256, 0, st>>>(G, l == 0 ? x : nullptr, Fx, R, (int)G4, rows_per, w.part); }
+        B200_LAUNCH_CHECK("wide_colsum_kernel");
+        { TimedLaunch _t("wide_colsum_reduce_kernel", st); wide_colsum_reduce_kernel<<<(unsigned)((G4 * (Fx + 1) + 255) / 256), 256, 0, st>>>(w.part, nslab, (int)G4, Fx, l == 0 ? gw_ih : nullptr, gb_ih, gb_hh); }
+        B200_LAUNCH_CHECK("wide_colsum_reduce_kernel");
+    }
+    return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Diagnostics: the engine's GEMM on caller-supplied matrices (fp32, row-major, device).  variant 0: C = A[MxK] . B[NxK]^T;
+// 1: C = A[MxK] . B[KxN]; 2: C = A[KxM]^T . B[KxN] (split-K when workspace is given).  nsplit 2 = bf16 hi/lo, 1 = plain bf16.
+extern "C" int b200_wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C, int64_t M, int N, int64_t K,
+                              int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
+    const int64_t lda = variant == 2 ? M : K, ldb = variant == 0 ? K : N;
+    return wide_gemm(nsplit, variant, A, B, C, M, N, K, lda, ldb, N, accumulate, (float*)workspace, workspace_bytes / sizeof(float),
+                     (cudaStream_t)stream, "wide_gemm_kernel");
+}
