@@ -235,12 +235,19 @@ def run_b200(args):
     dom = max(kt.items(), key=lambda kv: kv[1][1]) if kt else (None, (0, 0.0))
     seqs = args.batch * S
     F_seq = flops_per_sequence(3, H, L)
-    lstm_ms = sum(v[1] for k, v in kt.items() if k.startswith("lstm_"))
+    lstm_ms = sum(v[1] for k, v in kt.items() if k.startswith(("lstm_", "wide_")))
     lstm_launch_ms = lstm_ms / args.steps if args.steps else 0.0
     achieved = seqs * F_seq / (lstm_launch_ms * 1e-3) / 1e12 if lstm_launch_ms else 0.0
-    roofline = {"bound": "tensor", "kernel": "LSTM forward+backward kernels (" + ", ".join(sorted(k for k in kt if k.startswith("lstm_"))) + ")",
+    traffic = None
+    tj = ROOT / "profiles" / "ncu_r01_traffic.json"
+    if tj.exists():             # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this workload
+        t = json.loads(tj.read_text())
+        wl = t.get("workload", {})
+        if (wl.get("model"), wl.get("engine"), wl.get("batch")) == (args.model, args.engine, args.batch):
+            traffic = t["bytes_per_launch"].get(dom[0])
+    roofline = {"bound": "tensor", "kernel": "LSTM forward+backward kernels (" + ", ".join(sorted(k for k in kt if k.startswith(("lstm_", "wide_")))) + ")",
                 "dominant_kernel": dom[0], "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
-                "traffic": None, "peak_source": f"{src} bf16 sustained (MEASURED_PEAKS.json)",
+                "traffic": traffic, "peak_source": f"{src} bf16 sustained (MEASURED_PEAKS.json)",
                 "algorithmic_flops_per_step": seqs * F_seq, "lstm_ms_per_step": lstm_launch_ms,
                 "kernel_ms_per_step": {k: v[1] / args.steps for k, v in sorted(kt.items())},
                 "kernel_launches_per_step": {k: v[0] / args.steps for k, v in sorted(kt.items())}}
