@@ -62,6 +62,7 @@ constexpr int TH = 64;              // hidden size of this engine
 constexpr int TG = 4 * TH;          // gate columns = UMMA N
 constexpr int TM = 128;             // sequences per tile = UMMA M
 constexpr int LOADER_WARPS = 2;
+constexpr int FW_EH_L0 = 1;          // forward layer 0: epilogue threads per row (see lstm_tc_fwd_kernel); 2 measured SLOWER (5.14 vs 4.83 ms)
 
 __host__ __device__ constexpr int kx_of(bool layer0) { return layer0 ? 16 : TH; }
 // bytes of one operand image with `rows` rows and K columns of bf16
@@ -227,13 +228,19 @@ struct FwdSmem {
     static constexpr uint32_t total = off_tmem + 16 + 128;
 };
 
-template <int NSPLIT, int NTILE, bool LAYER0>
-__global__ void __launch_bounds__(32 * (4 * NTILE + LOADER_WARPS + 1), 1)
+// EH = epilogue warps per TMEM lane quarter of a tile: with EH = 2 a row's 64 hidden units are split between two
+// threads (warps w and w + 4 may both read lanes 32 (w % 4) .. +31), which doubles the warps per SM sub-partition
+// that hide the MUFU / TMEM-load latency of the cell update.  Measured (layer 0, B = 4096): 5.14 ms against 4.83 ms for
+// EH = 1 -- while an epilogue runs, the MUFU pipe is already ~80 % busy (7 MUFU per unit and row at 16 lanes/clk/SM);
+// what is missing is a third tile in flight, which TMEM (2 x 256 columns) does not allow.
+template <int NSPLIT, int NTILE, bool LAYER0, int EH>
+__global__ void __launch_bounds__(32 * (4 * NTILE * EH + LOADER_WARPS + 1), 1)
 lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
                    float* __restrict__ h_out, float* __restrict__ c_out, const uint64_t* __restrict__ drop_bits, float p) {
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     constexpr int KX = S::KX;
-    constexpr int EPI_WARPS = 4 * NTILE;
+    constexpr int EPI_WARPS = 4 * NTILE * EH;
+    constexpr int UCN = TH / 8 / EH;                                      // 8-unit chunks per epilogue thread
     // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
     // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -260,7 +267,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     if (threadIdx.x == 0) {
         for (int s = 0; s < NTILE; ++s) {
             mbar_init(&bars[s * 3 + 0], LOADER_WARPS);
-            mbar_init(&bars[s * 3 + 1], 4);
+            mbar_init(&bars[s * 3 + 1], 4 * EH);
             mbar_init(&bars[s * 3 + 2], 1);
         }
         mbar_init(x_free, 1);
@@ -279,8 +286,8 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     const int64_t total_steps = my_groups * T;             // per slot
 
     if (warp < EPI_WARPS) {
-        // ================================ epilogue: thread = one sequence =================================
-        const int slot = warp >> 2, wq = warp & 3;
+        // ================================ epilogue: thread = one sequence x 64 / EH hidden units =============
+        const int slot = warp / (4 * EH), wq = warp & 3, uh = (warp >> 2) % EH;
         const int r = wq * 32 + lane;                                        // row in tile = TMEM lane
         const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(slot * TG);
         uint8_t* h_hi = smem + S::off_h + (slot * NSPLIT) * S::HB;
@@ -288,7 +295,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         uint64_t* h_ready = &bars[slot * 3 + 1];
         uint64_t* acc_full = &bars[slot * 3 + 2];
         const uint32_t row_off = (uint32_t)(r >> 3) * sbo_of(TH) + (uint32_t)(r & 7) * 16;
-        float cst[TH];
+        float cst[TH / EH];
         int64_t g = 0;
         int ntr = 0;
         const bool tracer = warp == 0 && lane == 0;
@@ -297,7 +304,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             const int64_t row = tile * TM + r;
             const bool live = tile < ntiles && row < N;
 #pragma unroll
-            for (int u = 0; u < TH; ++u) cst[u] = 0.f;
+            for (int u = 0; u < TH / EH; ++u) cst[u] = 0.f;
             for (int t = 0; t < T; ++t, ++g) {
                 if (tracer) trace_ev(0, 0, 0, g, ntr);
                 mbar_wait(acc_full, (uint32_t)(g & 1));
@@ -306,7 +313,8 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 float* hdst = h_out + ((int64_t)t * N + row) * TH;
                 float* cdst = c_out + ((int64_t)t * N + row) * TH;
 #pragma unroll
-                for (int uc = 0; uc < TH / 8; ++uc) {
+                for (int ucl = 0; ucl < UCN; ++ucl) {
+                    const int uc = uh * UCN + ucl;
                     float ai[8], af[8], ag[8], ao[8];
                     tmem_ld8(taddr + 0 * TH + uc * 8, ai);
                     tmem_ld8(taddr + 1 * TH + uc * 8, af);
@@ -333,7 +341,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         const float Di = 1.f + ai[j], Df = 1.f + af[j], Dg = 1.f + ag[j];
                         const float DiDg = Di * Dg;
                         Do[j] = 1.f + ao[j];
-                        num[j] = fmaf(cst[uc * 8 + j], DiDg, (ag[j] - 1.f) * Df);
+                        num[j] = fmaf(cst[ucl * 8 + j], DiDg, (ag[j] - 1.f) * Df);
                         den[j] = Df * DiDg;
                     }
 #pragma unroll
@@ -341,7 +349,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         cv[j] = num[j] * den[j];
-                        cst[uc * 8 + j] = cv[j];
+                        cst[ucl * 8 + j] = cv[j];
                         num[j] = fminf(2.f * LOG2E * cv[j], EXP_CLAMP);
                     }
 #pragma unroll
@@ -359,7 +367,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     split2(hv[6], hv[7], hi4.w, lo4.w);
                     *reinterpret_cast<uint4*>(h_hi + row_off + uc * LBO_BYTES) = hi4;
                     if (NSPLIT == 2) *reinterpret_cast<uint4*>(h_lo + row_off + uc * LBO_BYTES) = lo4;
-                    if (uc < TH / 8 - 1) {
+                    if (ucl < UCN - 1) {
                         if (live) {
                             st_global_v8(hdst + uc * 8, hv);
                             st_global_v8(cdst + uc * 8, cv);
@@ -1317,15 +1325,15 @@ size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L) {
     return ((ffma_workspace_bytes(N, T, L) + 255) & ~(size_t)255) + tc_tail_total(N, T, L) + 512;
 }
 
-template <int NSPLIT, int NTILE, bool LAYER0>
+template <int NSPLIT, int NTILE, bool LAYER0, int EH>
 static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, float* h_out, float* c_out,
                       const uint64_t* drop_bits, float p, cudaStream_t st) {
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
-    auto kern = lstm_tc_fwd_kernel<NSPLIT, NTILE, LAYER0>;
+    auto kern = lstm_tc_fwd_kernel<NSPLIT, NTILE, LAYER0, EH>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     const int64_t ntiles = (N + TM - 1) / TM, ngroups = (ntiles + NTILE - 1) / NTILE;
     const int grid = (int)(ngroups < num_sms() ? ngroups : num_sms());
-    const int threads = 32 * (4 * NTILE + LOADER_WARPS + 1);
+    const int threads = 32 * (4 * NTILE * EH + LOADER_WARPS + 1);
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_fwd_kernel_l0" : "lstm_tc_fwd_kernel_lN", st);
         kern<<<grid, threads, S::total, st>>>(packed, xin, kin, N, T, h_out, c_out, drop_bits, p);
@@ -1366,11 +1374,11 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
         }
         int rc;
         if (l == 0) {
-            rc = precise ? launch_fwd<2, 2, true>(pk, xin, kin, N, T, ho, co, nullptr, p, st)
-                         : launch_fwd<1, 2, true>(pk, xin, kin, N, T, ho, co, nullptr, p, st);
+            rc = precise ? launch_fwd<2, 2, true, FW_EH_L0>(pk, xin, kin, N, T, ho, co, nullptr, p, st)
+                         : launch_fwd<1, 2, true, FW_EH_L0>(pk, xin, kin, N, T, ho, co, nullptr, p, st);
         } else {
-            rc = precise ? launch_fwd<2, 2, false>(pk, xin, kin, N, T, ho, co, bits, p, st)
-                         : launch_fwd<1, 2, false>(pk, xin, kin, N, T, ho, co, bits, p, st);
+            rc = precise ? launch_fwd<2, 2, false, 1>(pk, xin, kin, N, T, ho, co, bits, p, st)
+                         : launch_fwd<1, 2, false, 1>(pk, xin, kin, N, T, ho, co, bits, p, st);
         }
         if (rc) return rc;
         pk += (pack_bytes(l == 0) + 255) & ~(size_t)255;
