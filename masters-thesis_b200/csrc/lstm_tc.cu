@@ -30,8 +30,13 @@ namespace b200 {
 
 using namespace tc;
 
-// tuning switches (host sets them from the environment once; 1 = on)
-__constant__ int c_tc_prefetch = 1;
+// L2 prefetch (cp.async.bulk.prefetch.L2 of the next step's rows, one thread per CTA) -- bit mask, env B200_TC_PREFETCH:
+//   1 forward layers > 0: x     2 backward layer 0: h, c     backward layers > 0: 4 x, 8 h, 16 c, 32 d_out
+// Measured (B = 4096, 1xB200, tools/kbench.sh with B200_TC_PREFETCH=...): bit 2 is worth 0.5 ms in the layer-0 backward
+// kernel; in the layer > 0 backward kernel (whose epilogue warps stage the image themselves, loads issued a wait ahead)
+// each of bits 4, 8, 16 COSTS 0.9-1.0 ms (20.1 -> 21.1 ms) and bit 32 is neutral; bit 1 is worth < 0.1 ms.
+constexpr int PF_DEFAULT = 1 | 2 | 32;
+__constant__ int c_tc_prefetch = PF_DEFAULT;
 #ifdef B200_ABLATE                    // timing experiments only (build with B200_ABLATE=1): env B200_TC_DBG is a bit mask of backward
 __constant__ int c_tc_dbg = 0;        // epilogue pieces to skip (1 bias butterfly, 2 math, 4 operand stores, 8 loads, 16 proxy fence);
 #define TC_DBG() c_tc_dbg             // results are wrong when set.  Compiled out otherwise: the run-time test alone costs 2 ms.
@@ -398,7 +403,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const bool tracer = lw == 0 && lane == 0;
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             for (int t = 0; t < T; ++t, ++g) {
-                if (c_tc_prefetch && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
+                if ((c_tc_prefetch & 1) && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
                     // next step's input rows of both slots -> L2 (the tiles of a group are consecutive)
                     const int64_t r0 = grp * NTILE * TM;
                     if (r0 < N) {
@@ -690,6 +695,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // epilogue warps are idle: they then stage the next image themselves (2 row groups each, loads issued before the
     // buffer is released) and the loader warps only prefetch into L2.
     constexpr bool EPI_LOADS = (XB == 1) && !LAYER0;
+    constexpr bool ROLLQ = !EPI_LOADS;                     // see the quarter loop of the epilogue
     // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
     // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -834,8 +840,12 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             };
             issue_loads(T - 1, 0);
             for (int t = T - 1; t >= 0; --t, ++g) {
-#pragma unroll
+                // ROLLQ: the quarter loop stays a loop (code size / 4: with the loader warps streaming their own code next to
+                // it the unrolled epilogue spent 25-40 % of its issue cycles waiting for instructions, ncu "no instruction").
+                // The per-quarter register state (dc, dh, db) is then addressed as slot 0 and rotated after every quarter.
+#pragma unroll(ROLLQ ? 1 : 4)
                 for (int q = 0; q < 4; ++q) {
+                    const int qs = ROLLQ ? 0 : q;
                     const int u0 = 16 * q + EU * sub;                        // first hidden unit of this thread's slice
                     const int64_t qi = 4 * g + q;                              // running quarter index
                     const int slot = q & 1;
@@ -888,10 +898,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         const float t1 = r1[i] * Dg;
                         const float ig = t1 * Df, fg = t1 * Di, gg = (Dg - 2.f) * (r1[i] * (Di * Df));
                         const float og = r2[i] * Dc[i], tc = (Dc[i] - 2.f) * (r2[i] * Do);
-                        const float dhv = dh[q][i] + ndq[i];
+                        const float dhv = dh[qs][i] + ndq[i];
                         const float d_o = dhv * tc;
-                        const float dcc = dc[q][i] + dhv * og * (1.f - tc * tc);
-                        dc[q][i] = dcc * fg;
+                        const float dcc = dc[qs][i] + dhv * og * (1.f - tc * tc);
+                        dc[qs][i] = dcc * fg;
                         av[0][i] = dcc * gg * ig * (1.f - ig);
                         av[1][i] = dcc * ncp[i] * fg * (1.f - fg);
                         av[2][i] = dcc * ig * (1.f - gg * gg);
@@ -931,8 +941,18 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     if (tracer) trace_ev(0, 6, q, g, ntr);
                     // bias gradient: layer 0 gets it from the tensor core (constant-one column of the x image, see the
                     // loader); other layers reduce da over the warp's 32 rows here
-                    if (!LAYER0 && !(dbg & 1)) db[q] += warp_transpose_sum<EU>(av, lane);
+                    if (!LAYER0 && !(dbg & 1)) db[qs] += warp_transpose_sum<EU>(av, lane);
                     if (tracer) trace_ev(0, 7, q, g, ntr);
+                    if (ROLLQ) {
+#pragma unroll
+                        for (int i = 0; i < EU; ++i) {
+                            const float t0 = dc[0][i], t1 = dh[0][i];
+                            dc[0][i] = dc[1][i]; dc[1][i] = dc[2][i]; dc[2][i] = dc[3][i]; dc[3][i] = t0;
+                            dh[0][i] = dh[1][i]; dh[1][i] = dh[2][i]; dh[2][i] = dh[3][i]; dh[3][i] = t1;
+                        }
+                        const float t2 = db[0];
+                        db[0] = db[1]; db[1] = db[2]; db[2] = db[3]; db[3] = t2;
+                    }
                 }
                 if (EPI_LOADS) {
                     if (t > 0) stage_image(tile, t - 1, g + 1);
@@ -990,16 +1010,17 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             const int64_t rows_live = N - r0;
             for (int t = T - 1; t >= 0; --t, ++g) {
                 if (tracer) trace_ev(1, 0, 0, g, ntr);
-                if (c_tc_prefetch && lw == 0 && lane == 0 && t >= 1) {
+                const int pf = c_tc_prefetch;
+                if ((LAYER0 ? (pf & 2) : (pf & 60)) && lw == 0 && lane == 0 && t >= 1) {
                     // pull the NEXT step's rows (x_{t-1}, h_{t-2}, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
                     const int64_t nrow = rows_live < TM ? rows_live : TM;
                     const uint32_t rb = (uint32_t)nrow * TH * 4;
-                    if (!LAYER0) prefetch_l2(xin + ((int64_t)(t - 1) * N + r0) * TH, rb);
+                    if (!LAYER0 && (pf & 4)) prefetch_l2(xin + ((int64_t)(t - 1) * N + r0) * TH, rb);
                     if (t >= 2) {
-                        prefetch_l2(h_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
-                        prefetch_l2(c_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
+                        if (LAYER0 || (pf & 8)) prefetch_l2(h_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
+                        if (LAYER0 || (pf & 16)) prefetch_l2(c_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
                     }
-                    if (d_out) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
+                    if (d_out && (pf & 32)) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
                 }
                 if (EPI_LOADS) continue;               // the epilogue warps stage the image; this warp only prefetches
                 const int buf = (int)(g % XB);
