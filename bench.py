@@ -208,10 +208,13 @@ def run_b200(args):
         feeder = B.HostBatchFeeder(dev)
 
         def run_e2e(n):
-            last = None
+            # every step's loss is read back to the host (pinned buffer + event), one step behind the enqueue front
+            box, vals = B.LossMailbox(dev), []
             for b in feeder.feed(refs[i % 2] for i in range(n)):
-                last = float(tr.training_step(model, b, LR)[2])     # device -> host read of every step's loss
-            return last
+                vals += box.post(tr.training_step(model, b, LR))
+            vals += box.drain()
+            assert len(vals) == n
+            return vals[-1][2]
 
         run_e2e(2)
         barrier()
@@ -222,8 +225,8 @@ def run_b200(args):
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.batch * world * e2e_steps / float(dt), "unit": "samples/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": 4, "steps": e2e_steps,
-               "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> HostBatchFeeder (cudaMemcpyAsync + layout conversion on a copy stream, one batch ahead) -> B200Trainer.training_step -> loss.item() every step"}
+               "d2h_bytes_per_step": 16, "steps": e2e_steps,
+               "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> HostBatchFeeder (cudaMemcpyAsync + layout conversion on a copy stream, one batch ahead) -> B200Trainer.training_step -> LossMailbox (every step's [mse, nll, total, mae] copied to pinned host memory and read by the host one step behind the enqueue front)"}
 
     if world > 1:
         dist.barrier()

@@ -10,8 +10,8 @@ from .config import compose_config
 from .data import DeviceBatch, FinancialLstmDataModule, HostBatchFeeder, SeriesBatchSource
 from .engine import LstmEngine
 from .model import FinancialLstm, FinancialLstmCombined, FinancialLstmMse, FinancialLstmNll, get_model_class
-from .trainer import B200Trainer
+from .trainer import B200Trainer, LossMailbox
 
 __all__ = ["B200Error", "B200Trainer", "DeviceBatch", "FinancialLstm", "FinancialLstmCombined",
-           "FinancialLstmDataModule", "FinancialLstmMse", "HostBatchFeeder", "FinancialLstmNll", "LOSS_KINDS", "LstmEngine",
+           "FinancialLstmDataModule", "FinancialLstmMse", "HostBatchFeeder", "FinancialLstmNll", "LOSS_KINDS", "LossMailbox", "LstmEngine",
            "MODES", "SeriesBatchSource", "compose_config", "data", "evaluate", "get_model_class", "_lib"]

@@ -20,6 +20,42 @@ import torch
 from .grad_sync import GradBucketer
 
 
+class LossMailbox:
+    """Per-step device -> host read of the step's [mse, nll, total, mae] without draining the GPU queue: step k's
+    values are copied to pinned host memory on the compute stream and read by the host while step k + 1 is already
+    enqueued (a `.item()` after every step would leave the GPU idle for one host launch sequence per step)."""
+
+    def __init__(self, device, depth=2):
+        self.device = torch.device(device)
+        self.slots = [torch.empty(4, dtype=torch.float32).pin_memory() for _ in range(depth)]
+        self.events = [torch.cuda.Event() for _ in range(depth)]
+        self.pending = []            # slot indices in flight, oldest first
+        self.n = 0
+
+    def post(self, losses):
+        """Queue the read of one step's losses; returns the values of steps that fell out of the window."""
+        done = []
+        if len(self.pending) == len(self.slots):
+            done.append(self._take())
+        i = self.n % len(self.slots)
+        self.slots[i].copy_(losses, non_blocking=True)
+        self.events[i].record(torch.cuda.current_stream(self.device))
+        self.pending.append(i)
+        self.n += 1
+        return done
+
+    def _take(self):
+        i = self.pending.pop(0)
+        self.events[i].synchronize()
+        return self.slots[i].tolist()
+
+    def drain(self):
+        out = []
+        while self.pending:
+            out.append(self._take())
+        return out
+
+
 class PlateauSchedule:
     """torch.optim.lr_scheduler.ReduceLROnPlateau(mode='min', factor, patience) with torch's defaults
     (relative threshold 1e-4, cooldown 0, min_lr 0, eps 1e-8) -- src/model.py:156-161."""

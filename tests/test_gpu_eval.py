@@ -73,3 +73,24 @@ def test_reference_style_checkpoint_loads(tmp_path):
         ao, bo = om(x)
     np.testing.assert_allclose(a.cpu().numpy(), ao.numpy(), atol=1e-5)
     np.testing.assert_allclose(b.cpu().numpy(), bo.numpy(), atol=1e-5)
+
+
+def test_loss_mailbox_matches_direct_reads():
+    """The pipelined per-step loss read-back returns every step's values, in order, equal to direct reads."""
+    torch.manual_seed(3)
+    model = B.FinancialLstmMse(3, 64, 2, 0.0, 1e-4)
+    dm = B.FinancialLstmDataModule(lookback_window=60, target_window=30, stride=90, batch_size=2, seed=5, n_samples=90 * 20,
+                                   device=DEV)
+    tr = B.B200Trainer(max_epochs=1, gradient_clip_val=5.0, engine="ffma", verbose=False)
+    dm.prepare_data(); dm.setup("fit")
+    tr._attach(model, dm)
+    box, got, want = B.LossMailbox(DEV, depth=2), [], []
+    for k in range(5):
+        b = dm.source.generate(first_window=2 * k, n_windows=2)
+        losses = tr.training_step(model, b, 1e-4)
+        want.append(losses.clone())
+        got += box.post(losses)
+    got += box.drain()
+    assert len(got) == 5
+    for g, w in zip(got, want):
+        assert g == w.cpu().tolist()
