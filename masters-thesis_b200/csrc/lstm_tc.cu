@@ -562,6 +562,11 @@ constexpr int BW_THREADS = 32 * (BW_EPI_WARPS + LOADER_WARPS + 2);   // + one wa
 // asking for more than the pool blocks the last warpgroup forever.
 constexpr int BW_LAUNCH_REGS = BW_EU == 8 ? 168 : 96;      // 65,536 / threads rounded down to a multiple of 8
 constexpr int BW_EPI_REGS = BW_EU == 8 ? 200 : 104, BW_AUX_REGS = BW_EU == 8 ? 104 : 64;
+// kernels whose epilogue warps stage the operand image themselves (idle loader warps): 208 / 88 measured 0.6 ms faster in the
+// layer > 0 kernel (fewer epilogue spills) and 1.3 ms SLOWER in the layer-0 kernel (its loader warps then spill)
+constexpr int BW_EPI_REGS_EL = BW_EU == 8 ? 208 : 104, BW_AUX_REGS_EL = BW_EU == 8 ? 88 : 64;   // 216/72 and 224/56 measured slower
+static_assert(BW_EPI_WARPS * 32 * BW_EPI_REGS_EL + 4 * 32 * BW_AUX_REGS_EL <= BW_THREADS * BW_LAUNCH_REGS,
+              "setmaxnreg targets exceed the CTA's register pool");
 static_assert(BW_EPI_WARPS * 32 * BW_EPI_REGS + 4 * 32 * BW_AUX_REGS <= BW_THREADS * BW_LAUNCH_REGS,
               "setmaxnreg targets exceed the CTA's register pool");
 constexpr uint32_t TMEM_DW = 0, TMEM_A = 256, TMEM_D = 384;    // dWcat^T | two 64-column gate-quarter slots | [dx | dh]
@@ -741,8 +746,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     const int64_t total_q = 4 * total_steps;
 
     // register rebalancing between warpgroups: the loader/MMA group releases registers, the epilogue groups take them
-    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(BW_EPI_REGS));
-    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(BW_AUX_REGS));
+    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(EPI_LOADS ? BW_EPI_REGS_EL : BW_EPI_REGS));
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(EPI_LOADS ? BW_AUX_REGS_EL : BW_AUX_REGS));
 
     if (warp < BW_EPI_WARPS) {
         // ===================================== epilogue warps =====================================================
