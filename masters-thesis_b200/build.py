@@ -37,6 +37,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     flags = list(NVCC_FLAGS)
     if os.environ.get("B200_TRACE") == "1":          # event tracing of the tcgen05 kernels (tools/trace_*.py); rebuild with --force
         flags.append("-DB200_TRACE")
+    flags += os.environ.get("B200_DEFS", "").split()      # extra -D switches for timing experiments (rebuild with --force)
     if os.environ.get("B200_ABLATE") == "1":        # backward-epilogue ablation switches (env B200_TC_DBG); timing experiments only
         flags.append("-DB200_ABLATE")
     srcs = sorted(CSRC.glob("*.cu"))

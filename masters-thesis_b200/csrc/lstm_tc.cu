@@ -671,7 +671,7 @@ template <>
 __device__ __forceinline__ void tmem_ldn<4>(uint32_t taddr, float (&v)[4]) { tmem_ld4(taddr, v); }
 
 __device__ __forceinline__ void ld_global_v8(const float* p, float (&v)[8]) {
-    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm volatile(B200_LDG_V8 " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
                  : "l"(p));
 }

@@ -131,8 +131,20 @@ __device__ __forceinline__ void split2x2(float a, float b, float c, float d, uin
     split2(c, d, hi.y, lo.y);
 }
 
+// cache-operator experiments (B200_DEFS="-DB200_ST_CS -DB200_LD_CS" python masters-thesis_b200/build.py --force): evict-first
+// 32-byte stash stores / loads
+#ifdef B200_ST_CS
+#define B200_STG_V8 "st.global.cs.v8.f32"
+#else
+#define B200_STG_V8 "st.global.v8.f32"
+#endif
+#ifdef B200_LD_CS
+#define B200_LDG_V8 "ld.global.cs.v8.f32"
+#else
+#define B200_LDG_V8 "ld.global.v8.f32"
+#endif
 __device__ __forceinline__ void st_global_v8(float* p, const float (&v)[8]) {
-    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]),
+    asm volatile(B200_STG_V8 " [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]),
                  "f"(v[5]), "f"(v[6]), "f"(v[7])
                  : "memory");
 }
