@@ -1089,7 +1089,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         // Descriptors are built once; per MMA only a 64-bit add of a compile-time offset remains (the single issuing
         // thread is on the critical path of the recurrence).
         if (lane == 0 && total_q > 0) {
-            constexpr uint32_t idesc_a = make_idesc_bf16(TM, 64, 0, 0);       // recompute of one quarter
             constexpr uint32_t idesc_d = make_idesc_bf16(TM, ND, 0, 1);       // dgrad: A K-major, B MN-major
             const uint32_t s_base = smem_u32(smem);
             const uint32_t mn_off = LAYER0 ? (uint32_t)(KX / 8) * LBO_BYTES : 0u;   // layer 0 dgrad: only the h columns of Wcat
@@ -1100,32 +1099,38 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             for (int b = 0; b < XB; ++b) xk_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, LBO_BYTES, SBO_W);
 #pragma unroll
             for (int b = 0; b < DB; ++b) dak_hi[b] = make_desc(s_base + S::off_da + (b * NSPLIT) * S::DAB, LBO_BYTES, SBO_DA);
-            // gates of running quarter nq -> TMEM slot nq & 1 (waits for the slot to be read out and for the image of its step)
-            auto issue_recompute = [&](int64_t nq) {
+            // Gates of the quarter PAIR (nq, nq + 1), nq even -> TMEM slots 0 and 1 with ONE N = 128 MMA per product and k-step:
+            // a tcgen05.mma of this size costs ~60 clk of fixed overhead plus ~0.43 clk per column of N (measured), so two
+            // N = 64 quarters cost 174 clk and the pair 115.  Waits for both slots to be read out and for the image of its step.
+            constexpr uint32_t idesc_a2 = make_idesc_bf16(TM, 128, 0, 0);
+            auto issue_recompute_pair = [&](int64_t nq) {
                 const int64_t ng = nq >> 2;
-                const int q = (int)(nq & 3), slot = (int)(nq & 1);
-                if (q == 0 || (XB == 1 && q == 1)) mbar_wait(&xh_full[ng % XB], (uint32_t)((ng / XB) & 1));
-                if (nq >= 2) mbar_wait(&a_free[slot], (uint32_t)(((nq >> 1) - 1) & 1));
+                const int q = (int)(nq & 3);                                   // 0 or 2
+                if (q == 0) mbar_wait(&xh_full[ng % XB], (uint32_t)((ng / XB) & 1));
+                if (nq >= 2) {
+                    mbar_wait(&a_free[0], (uint32_t)(((nq >> 1) - 1) & 1));
+                    mbar_wait(&a_free[1], (uint32_t)(((nq >> 1) - 1) & 1));
+                }
                 tc_fence_after();
                 const uint64_t xh = xk_hi[ng % XB], xl = xh + (S::XHB >> 4);
-                const uint32_t d = tmem_base + TMEM_A + 64 * slot;
+                const uint32_t d = tmem_base + TMEM_A;
                 const uint64_t wrow = (uint64_t)(((uint32_t)(q * 64 / 8) * SBO_W) >> 4);
                 const uint64_t wh = wk_hi + wrow, wl = wk_lo + wrow;
 #pragma unroll
                 for (int ks = 0; ks < KC / 16; ++ks) {
                     const uint64_t ko = (uint64_t)((ks * 2 * LBO_BYTES) >> 4);
-                    umma_bf16(d, xh + ko, wh + ko, idesc_a, ks > 0 ? 1u : 0u);
+                    umma_bf16(d, xh + ko, wh + ko, idesc_a2, ks > 0 ? 1u : 0u);
                     if (NSPLIT == 2) {
-                        umma_bf16(d, xl + ko, wh + ko, idesc_a, 1);
-                        umma_bf16(d, xh + ko, wl + ko, idesc_a, 1);
+                        umma_bf16(d, xl + ko, wh + ko, idesc_a2, 1);
+                        umma_bf16(d, xh + ko, wl + ko, idesc_a2, 1);
                     }
                 }
-                umma_commit(&a_full[slot]);
-                if (q == 3) umma_commit(&xh_free[ng % XB]);     // this issuer's last read of the step's image
+                umma_commit(&a_full[0]);
+                umma_commit(&a_full[1]);
+                if (q == 2) umma_commit(&xh_free[ng % XB]);     // this issuer's last read of the step's image
             };
             int ntr = 0;
-            issue_recompute(0);
-            issue_recompute(1);
+            issue_recompute_pair(0);
             for (int64_t qi = 0; qi < total_q; ++qi) {
                 const int64_t g = qi >> 2;
                 const int q = (int)(qi & 3);
@@ -1153,16 +1158,13 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     umma_commit(&da_free[buf]);           // first of two arrivals (the wgrad issuer gives the second)
                 }
                 trace_ev(2, 2, q, g, ntr);
-                // ---- gates two quarters ahead (same step, or the next step when its image is already staged) ----------
-                {
-                    const int64_t nq = qi + 2;
-                    if (nq < total_q && (q < 2 || XB == 2)) issue_recompute(nq);
-                }
+                // ---- next pair of gate quarters: (q2, q3) of this step after quarter 0, (q0, q1) of the next step after
+                //      quarter 2 when its image is already staged (XB == 2)
+                if ((q == 0 || (q == 2 && XB == 2)) && qi + 2 < total_q) issue_recompute_pair(qi + 2);
                 trace_ev(2, 3, q, g, ntr);
-                // single-buffered image: the next step's first two quarters can only be recomputed after the reload
+                // single-buffered image: the next step's first pair can only be recomputed after the reload
                 if (XB == 1 && q == 3 && qi + 1 < total_q) {
-                    issue_recompute(qi + 1);
-                    issue_recompute(qi + 2);
+                    issue_recompute_pair(qi + 1);
                     trace_ev(2, 5, q, g, ntr);
                 }
             }
