@@ -7,12 +7,12 @@ sys.path.insert(0, str(ROOT))
 import masters_thesis_b200 as B
 from masters_thesis_b200._lib import load, check, ptr
 ap = argparse.ArgumentParser(); ap.add_argument("--engine", default="tc_precise"); ap.add_argument("--batch", type=int, default=2048)
-ap.add_argument("--layer", type=int, default=1); ap.add_argument("--steps", default="20,21"); ap.add_argument("--dropout", type=float, default=0.2)
+ap.add_argument("--layer", type=int, default=1); ap.add_argument("--layers", type=int, default=2); ap.add_argument("--steps", default="20,21"); ap.add_argument("--dropout", type=float, default=0.2)
 a = ap.parse_args()
 lib = load(); dev = "cuda:0"
 torch.manual_seed(0)
 # trace the chosen layer by making it the only traced launch: run a 1-layer or 2-layer model accordingly
-m = B.FinancialLstmMse(3, 64, 2, a.dropout, 1e-4); e = m.attach(dev, a.engine)
+m = B.FinancialLstmMse(3, 64, a.layers, a.dropout, 1e-4); e = m.attach(dev, a.engine)
 src = B.data.DeviceBatchSource(dev); b = src.generate(first_window=0, n_windows=a.batch)
 CAP = 8192
 buf = torch.zeros(4 * CAP * 2, dtype=torch.int64, device=dev)
