@@ -79,7 +79,7 @@ class DeviceBatchSource:
             self._bufs[B] = DeviceBatch(e(self.T, N, self.F), e(N, self.n), e(B, self.n), e(B, 2), e(N), B, self.S)
         return self._bufs[B]
 
-    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None) -> DeviceBatch:
+    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None, checked=False) -> DeviceBatch:
         if window_idx is not None:
             window_idx = window_idx.to(self.device, torch.int64).contiguous()
             n_windows = window_idx.numel()
@@ -131,10 +131,10 @@ class SeriesBatchSource:
             self._bufs[B] = DeviceBatch(e(self.T, N, self.F), e(N, self.n), e(B, self.n), e(B, 2), e(N), B, self.S, e(N), e(N))
         return self._bufs[B]
 
-    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None) -> DeviceBatch:
+    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None, checked=False) -> DeviceBatch:
         if window_idx is not None:
             window_idx = window_idx.to(torch.int64)
-            if window_idx.numel() and (int(window_idx.min()) < 0 or int(window_idx.max()) >= self.n_windows):
+            if not checked and window_idx.numel() and (int(window_idx.min()) < 0 or int(window_idx.max()) >= self.n_windows):
                 raise IndexError(f"window index outside [0, {self.n_windows})")
             window_idx = window_idx.to(self.device).contiguous()
             n_windows = window_idx.numel()
@@ -238,7 +238,9 @@ class _Loader:
     def __iter__(self):
         n = self.hi - self.lo
         order = torch.randperm(n, generator=self.gen) if self.shuffle else torch.arange(n)
-        order = order + self.lo
+        # the epoch's order goes to the device ONCE (a per-batch upload of the indices is a blocking copy that makes the host
+        # wait for the previous step: 2.2 of 2.4 ms per step at batch_size 1); batches are slices of it
+        order = (order + self.lo).to(self.source.device)
         for i in range(0, n, self.bs):
             idx = order[i:i + self.bs]
             if self.world > 1:                        # each rank takes its contiguous share of the global batch
@@ -246,7 +248,7 @@ class _Loader:
                 if per == 0:
                     continue
                 idx = idx[self.rank * per:(self.rank + 1) * per]
-            yield self.source.generate(window_idx=idx)
+            yield self.source.generate(window_idx=idx, checked=True)     # lo..hi lie inside the series by construction
 
 
 class _StreamLoader:
