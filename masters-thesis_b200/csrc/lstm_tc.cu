@@ -905,12 +905,13 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         const float og = r2[i] * Dc[i], tc = (Dc[i] - 2.f) * (r2[i] * Do);
                         const float dhv = dh[qs][i] + ndq[i];
                         const float d_o = dhv * tc;
-                        const float dcc = dc[qs][i] + dhv * og * (1.f - tc * tc);
+                        // x (1 - x) and 1 - x^2 as single FMAs (the compiler may not re-associate them itself)
+                        const float dcc = fmaf(dhv * og, fmaf(-tc, tc, 1.f), dc[qs][i]);
                         dc[qs][i] = dcc * fg;
-                        av[0][i] = dcc * gg * ig * (1.f - ig);
-                        av[1][i] = dcc * ncp[i] * fg * (1.f - fg);
-                        av[2][i] = dcc * ig * (1.f - gg * gg);
-                        av[3][i] = d_o * og * (1.f - og);
+                        av[0][i] = dcc * gg * fmaf(-ig, ig, ig);
+                        av[1][i] = dcc * ncp[i] * fmaf(-fg, fg, fg);
+                        av[2][i] = dcc * ig * fmaf(-gg, gg, 1.f);
+                        av[3][i] = d_o * fmaf(-og, og, og);
                     }
                     // the next quarter's global operands (this quarter's are consumed).  Measured: issuing them here, before the
                     // proxy fence below, is faster than after it (lead time matters more than the fence waiting on them).
