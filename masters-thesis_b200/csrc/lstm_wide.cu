@@ -45,6 +45,9 @@ struct GemmArgs {
     int accumulate;                // C += (ignored when part != nullptr)
     int64_t k_per_split;           // multiple of GK
     float* part;                   // split-K partials [splits][M x N] (variant 2), or nullptr
+    // pre-packed B (variants 0, 1): operand images of every (N tile, K chunk) as wide_pack_b_kernel lays them out; then B is
+    // staged by the TMA engine (one bulk copy per image) instead of by the threads
+    const uint8_t* bp_hi; const uint8_t* bp_lo;
 };
 
 __device__ __forceinline__ int blk_rr(int lane) { return (lane >> 1) & 7; }
@@ -89,8 +92,8 @@ template <int NSPLIT>
 struct GemmSmem {
     static constexpr uint32_t A_IMG = GM * GK * 2, B_IMG = GN * GK * 2;           // one bf16 image
     static constexpr uint32_t STAGE = NSPLIT * (A_IMG + B_IMG);
-    static constexpr uint32_t off_bar = 2 * STAGE;                                // 2 stage barriers + done
-    static constexpr uint32_t off_tmem = off_bar + 3 * 8;
+    static constexpr uint32_t off_bar = 2 * STAGE;                                // 2 stage barriers + done + 2 B-full
+    static constexpr uint32_t off_tmem = off_bar + 5 * 8;
     static constexpr uint32_t total = off_tmem + 16 + 128;
 };
 
@@ -109,7 +112,7 @@ __global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
     const int nchunks = (int)((k_end - k_beg + GK - 1) / GK);
 
     if (threadIdx.x == 0) {
-        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1);
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1); mbar_init(&bars[3], 1); mbar_init(&bars[4], 1);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(tmem_slot, GN);
@@ -131,19 +134,18 @@ __global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
         uint8_t* b_lo = b_hi + S::B_IMG;
         const int64_t k0 = k_beg + (int64_t)kc * GK;
         if (kc >= 2) mbar_wait(&bars[s], (uint32_t)(((kc >> 1) - 1) & 1));      // MMAs of chunk kc - 2 have read this stage
-        // ---- stage A ------------------------------------------------------------------------------------------
-        if (VAR != 2) {                       // [128 rows x 64 k]: 16 row groups, 2 per warp
-            float4 v[2][4];
-            blk_load<2>(v, a.A + m0 * a.lda + k0, a.lda, a.M - m0, 2 * warp, lane);
-            blk_store<NSPLIT, 2>(v, a_hi, a_lo, sbo_k, 0, 2 * warp, lane);
-        } else {                              // [64 k-rows x 128 m-cols]: 2 column blocks x 4 row-group pairs
-            const int cb = warp >> 2, pr = warp & 3;
-            float4 v[2][4];
-            blk_load<2>(v, a.A + k0 * a.lda + m0 + cb * 64, a.lda, k_end - k0, 2 * pr, lane);
-            blk_store<NSPLIT, 2>(v, a_hi, a_lo, sbo_am, cb * 64, 2 * pr, lane);
-        }
         // ---- stage B ------------------------------------------------------------------------------------------
-        if (VAR == 0) {                       // [NT rows x 64 k]: NT / 8 row groups, pairs round-robin over the warps
+        if (VAR != 2 && a.bp_hi) {            // pre-packed images: one bulk copy each, issued before the threads stage A
+            if (threadIdx.x == 0) {
+                const uint32_t img = (uint32_t)NT * GK * 2;
+                const int64_t chunk = k0 / GK, nchunk_all = a.K / GK;
+                // image index: variant 0 [N tile][K chunk], variant 1 [K chunk][N tile]; every image padded to GN x GK
+                const int64_t idx = VAR == 0 ? (int64_t)blockIdx.y * nchunk_all + chunk : chunk * gridDim.y + blockIdx.y;
+                mbar_arrive_expect_tx(&bars[3 + s], NSPLIT * img);
+                bulk_copy_g2s(b_hi, a.bp_hi + idx * S::B_IMG, img, &bars[3 + s]);
+                if (NSPLIT == 2) bulk_copy_g2s(b_lo, a.bp_lo + idx * S::B_IMG, img, &bars[3 + s]);
+            }
+        } else if (VAR == 0) {                       // [NT rows x 64 k]: NT / 8 row groups, pairs round-robin over the warps
             for (int pr = warp; pr < NT / 16; pr += G_THREADS / 32) {
                 float4 v[2][4];
                 blk_load<2>(v, a.B + (int64_t)n0 * a.ldb + k0, a.ldb, NT, 2 * pr, lane);
@@ -157,9 +159,21 @@ __global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
                 blk_store<NSPLIT, 2>(v, b_hi, b_lo, sbo_bm, cb * 64, 2 * pr, lane);
             }
         }
+        // ---- stage A ------------------------------------------------------------------------------------------
+        if (VAR != 2) {                       // [128 rows x 64 k]: 16 row groups, 2 per warp
+            float4 v[2][4];
+            blk_load<2>(v, a.A + m0 * a.lda + k0, a.lda, a.M - m0, 2 * warp, lane);
+            blk_store<NSPLIT, 2>(v, a_hi, a_lo, sbo_k, 0, 2 * warp, lane);
+        } else {                              // [64 k-rows x 128 m-cols]: 2 column blocks x 4 row-group pairs
+            const int cb = warp >> 2, pr = warp & 3;
+            float4 v[2][4];
+            blk_load<2>(v, a.A + k0 * a.lda + m0 + cb * 64, a.lda, k_end - k0, 2 * pr, lane);
+            blk_store<NSPLIT, 2>(v, a_hi, a_lo, sbo_am, cb * 64, 2 * pr, lane);
+        }
         fence_proxy_async();
         __syncthreads();
         if (threadIdx.x == 0) {
+            if (VAR != 2 && a.bp_hi) mbar_wait(&bars[3 + s], (uint32_t)((kc >> 1) & 1));      // B images have landed
             tc_fence_after();
             const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
 #pragma unroll
@@ -215,6 +229,31 @@ __global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
     if (warp == 0) tmem_dealloc(tmem_base, GN);
 }
 
+// Operand images of a weight matrix W for use as the B operand, one GN x GK image per (N tile, K chunk), hi and lo:
+//   variant 0 (W is [N x K], C = A . W^T): image rows = n within the tile, cols = k within the chunk (K-major)
+//   variant 1 (W is [K x N], C = A . W):   image rows = k within the chunk, cols = n within the tile (read MN-major)
+__global__ void __launch_bounds__(256)
+wide_pack_b_kernel(const float* __restrict__ W, int variant, int N, int64_t K, uint8_t* __restrict__ out_hi, uint8_t* __restrict__ out_lo) {
+    const int ntile = (N + GN - 1) / GN;
+    const int64_t nchunk = K / GK;
+    const int64_t total = (int64_t)N * K;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t n, k;
+        if (variant == 0) { n = i / K; k = i - n * K; } else { k = i / N; n = i - k * N; }
+        const int nt = (int)(n / GN), nl = (int)(n - (int64_t)nt * GN);
+        const int64_t kc = k / GK;
+        const int kl = (int)(k - kc * GK);
+        const int NT = N - nt * GN < GN ? N - nt * GN : GN;
+        const int64_t img = variant == 0 ? (int64_t)nt * nchunk + kc : kc * ntile + nt;
+        const int r = variant == 0 ? nl : kl, c = variant == 0 ? kl : nl, cols = variant == 0 ? GK : NT;
+        const uint32_t o = (uint32_t)(r >> 3) * (uint32_t)(cols / 8) * LBO_BYTES + (uint32_t)(c >> 3) * LBO_BYTES + (uint32_t)(r & 7) * 16 + (uint32_t)(c & 7) * 2;
+        const float v = W[i];
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        *reinterpret_cast<__nv_bfloat16*>(out_hi + img * (GN * GK * 2) + o) = h;
+        *reinterpret_cast<__nv_bfloat16*>(out_lo + img * (GN * GK * 2) + o) = __float2bfloat16_rn(v - __bfloat162float(h));
+    }
+}
+
 // C[i] = sum over splits of part[z][i] in fixed order (bit-identical run to run)
 __global__ void __launch_bounds__(256) wide_splitk_reduce_kernel(const float* __restrict__ part, int splits, int64_t n, float* __restrict__ C) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -241,8 +280,21 @@ int launch_gemm_t(GemmArgs a, int splits, cudaStream_t st, const char* name) {
 }  // namespace
 
 // C (+)= op(A) . op(B); see the variant table above.  Split-K (variant 2 only) needs `part`.
+size_t wide_pack_bytes(int N, int64_t K) { return (size_t)((N + GN - 1) / GN) * (size_t)(K / GK) * GN * GK * 2; }   // one of hi / lo
+
+int wide_pack_b(const float* W, int variant, int N, int64_t K, uint8_t* out_hi, uint8_t* out_lo, cudaStream_t st) {
+    B200_CHECK_ARG(variant == 0 || variant == 1, "wide_pack_b: variant must be 0 or 1");
+    B200_CHECK_ARG(W && out_hi && out_lo && N % 64 == 0 && K % GK == 0, "wide_pack_b: bad arguments");
+    int64_t grid = ((int64_t)N * K + 255) / 256;
+    if (grid > (int64_t)num_sms() * 8) grid = (int64_t)num_sms() * 8;
+    { TimedLaunch _t("wide_pack_b_kernel", st); wide_pack_b_kernel<<<(unsigned)grid, 256, 0, st>>>(W, variant, N, K, out_hi, out_lo); }
+    B200_LAUNCH_CHECK("wide_pack_b_kernel");
+    return B200_OK;
+}
+
 int wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C, int64_t M, int N, int64_t K, int64_t lda,
-              int64_t ldb, int64_t ldc, int accumulate, float* part, size_t part_floats, cudaStream_t st, const char* name) {
+              int64_t ldb, int64_t ldc, int accumulate, float* part, size_t part_floats, cudaStream_t st, const char* name,
+              const uint8_t* bp_hi = nullptr, const uint8_t* bp_lo = nullptr) {
     B200_CHECK_ARG(nsplit == 1 || nsplit == 2, "wide_gemm: nsplit must be 1 or 2");
     B200_CHECK_ARG(variant >= 0 && variant <= 2, "wide_gemm: variant must be 0, 1 or 2");
     B200_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0, "wide_gemm: bad arguments (M=%lld N=%d K=%lld)", (long long)M, N, (long long)K);
@@ -251,7 +303,7 @@ int wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C,
     B200_CHECK_ARG(variant != 2 || M % GM == 0, "wide_gemm: M must be a multiple of 128 for variant 2, got %lld", (long long)M);
     B200_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0, "wide_gemm: leading dimensions must be multiples of 4 floats");
     B200_CHECK_ARG((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "wide_gemm: pointers must be 16-byte aligned");
-    GemmArgs a{A, B, C, M, N, K, lda, ldb, ldc, accumulate, 0, nullptr};
+    GemmArgs a{A, B, C, M, N, K, lda, ldb, ldc, accumulate, 0, nullptr, variant == 2 ? nullptr : bp_hi, variant == 2 ? nullptr : bp_lo};
     int splits = 1;
     const int64_t chunks = (K + GK - 1) / GK;
     if (variant == 2 && part) {
@@ -413,6 +465,7 @@ struct WideWs {
     float* dc;       // [N][H]
     float* part;     // split-K partials / column-sum partials
     size_t part_floats;
+    uint8_t* pack[4];   // B-operand images of the current layer's weights: [W_ih, W_hh] x [hi, lo] (K-major in forward, MN-major in backward)
 };
 constexpr int COLSUM_SLABS = 64;
 
@@ -423,6 +476,12 @@ size_t wide_part_floats(int H, int F) {
     return gemm > cs ? gemm : cs;
 }
 size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
+// one of hi / lo of a [4H x H] weight as B operand: [N = 4H][K = H] (variant 0) or [K = 4H][N = H] (variant 1); images are padded
+// to GN columns, so the two counts differ when H < GN
+size_t wide_pack_region(int H) {
+    const size_t a = wide_pack_bytes(4 * H, H), b = wide_pack_bytes(H, 4 * H);
+    return al256(a > b ? a : b);
+}
 
 bool wide_ws(void* workspace, size_t ws_bytes, int64_t N, int T, int F, int H, int L, WideWs* w) {
     uint8_t* p = (uint8_t*)workspace;
@@ -437,6 +496,8 @@ bool wide_ws(void* workspace, size_t ws_bytes, int64_t N, int T, int F, int H, i
     w->part = (float*)(p + off);
     w->part_floats = wide_part_floats(H, F);
     off += al256(w->part_floats * 4);
+    const size_t pk = wide_pack_region(H);
+    for (int i = 0; i < 4; ++i) { w->pack[i] = p + off; off += pk; }
     return workspace != nullptr && off <= ws_bytes;
 }
 
@@ -458,7 +519,8 @@ LayerParams layer_params(const float* params, int F, int H, int l) {
 
 size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L) {
     const size_t lsz = (size_t)T * N * H * 4;
-    return al256((size_t)L * lsz * 4) + 3 * al256(lsz) + 2 * al256((size_t)N * H * 4) + al256(wide_part_floats(H, F) * 4) + 256;
+    return al256((size_t)L * lsz * 4) + 3 * al256(lsz) + 2 * al256((size_t)N * H * 4) + al256(wide_part_floats(H, F) * 4) +
+           4 * wide_pack_region(H) + 256;
 }
 
 static int wide_check(const char* who, int H, int F) {
@@ -482,6 +544,10 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
         float* G = w.G + (int64_t)l * lsz * 4;
         float* hs = stash_h + (int64_t)l * lsz;
         float* cs = stash_c + (int64_t)l * lsz;
+        // this layer's weights as K-major operand images (once per step; every GEMM below then stages B with bulk copies)
+        if (l > 0) { rc = wide_pack_b(lp.w_ih, 0, (int)G4, H, w.pack[0], w.pack[1], st); if (rc) return rc; }
+        rc = wide_pack_b(lp.w_hh, 0, (int)G4, H, w.pack[2], w.pack[3], st);
+        if (rc) return rc;
         if (l > 0) {
             const float* xin = stash_h + (int64_t)(l - 1) * lsz;
             if (drop) {
@@ -489,14 +555,14 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
                 B200_LAUNCH_CHECK("wide_dropout_kernel");
                 xin = w.xd;
             }
-            rc = wide_gemm(nsplit, 0, xin, lp.w_ih, G, (int64_t)T * N, (int)G4, H, H, H, G4, 0, nullptr, 0, st, "wide_gemm_xproj");
+            rc = wide_gemm(nsplit, 0, xin, lp.w_ih, G, (int64_t)T * N, (int)G4, H, H, H, G4, 0, nullptr, 0, st, "wide_gemm_xproj", w.pack[0], w.pack[1]);
             if (rc) return rc;
         }
         for (int t = 0; t < T; ++t) {
             float* Gt = G + (int64_t)t * N * G4;
             if (t > 0) {
                 rc = wide_gemm(nsplit, 0, hs + (int64_t)(t - 1) * NH, lp.w_hh, Gt, N, (int)G4, H, H, H, G4, l > 0 ? 1 : 0, nullptr, 0, st,
-                               "wide_gemm_rec_fwd");
+                               "wide_gemm_rec_fwd", w.pack[2], w.pack[3]);
                 if (rc) return rc;
             }
             {
@@ -537,6 +603,10 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
     const float* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
     float* d_in = w.dx[(L - 1 - l) & 1];
 
+    // W_hh [4H x H] and W_ih [4H x H] (layers > 0) as MN-major operand images for dG . W
+    rc = wide_pack_b(lp.w_hh, 1, H, G4, w.pack[2], w.pack[3], st);
+    if (rc) return rc;
+    if (l > 0) { rc = wide_pack_b(lp.w_ih, 1, H, G4, w.pack[0], w.pack[1], st); if (rc) return rc; }
     for (int t = T - 1; t >= 0; --t) {
         float* Gt = G + (int64_t)t * N * G4;
         {
@@ -547,7 +617,7 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
         }
         B200_LAUNCH_CHECK("wide_cell_bwd_kernel");
         if (t > 0) {
-            rc = wide_gemm(nsplit, 1, Gt, lp.w_hh, w.dh_rec, N, H, G4, G4, H, H, 0, nullptr, 0, st, "wide_gemm_rec_bwd");
+            rc = wide_gemm(nsplit, 1, Gt, lp.w_hh, w.dh_rec, N, H, G4, G4, H, H, 0, nullptr, 0, st, "wide_gemm_rec_bwd", w.pack[2], w.pack[3]);
             if (rc) return rc;
         }
     }
@@ -569,7 +639,7 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
         rc = wide_gemm(nsplit, 2, G, xin, gw_ih, G4, H, R, G4, H, H, 0, w.part, w.part_floats, st, "wide_gemm_wgrad_ih");
         if (rc) return rc;
         // d_out of the layer below: dX = dG . W_ih, then the mask that was applied to this layer's input
-        rc = wide_gemm(nsplit, 1, G, lp.w_ih, d_in, R, H, G4, G4, H, H, 0, nullptr, 0, st, "wide_gemm_dgrad_x");
+        rc = wide_gemm(nsplit, 1, G, lp.w_ih, d_in, R, H, G4, G4, H, H, 0, nullptr, 0, st, "wide_gemm_dgrad_x", w.pack[0], w.pack[1]);
         if (rc) return rc;
         if (drop) {
             { TimedLaunch _t("wide_dropout_kernel", st); wide_dropout_kernel<<<ew_grid(R * (H / 8)), 256, 0, st>>>(seed, l, N, T, H, p, d_in, d_in); }
@@ -599,6 +669,16 @@ using namespace b200;
 extern "C" int b200_wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C, int64_t M, int N, int64_t K,
                               int accumulate, void* workspace, size_t workspace_bytes, void* stream) {
     const int64_t lda = variant == 2 ? M : K, ldb = variant == 0 ? K : N;
+    if (variant != 2 && workspace && N > 0 && K > 0 && N % 64 == 0 && K % 64 == 0) {      // B through pre-packed images + TMA bulk copies
+        const size_t pk = (wide_pack_bytes(N, K) + 255) & ~(size_t)255;
+        if (workspace_bytes >= 2 * pk) {
+            uint8_t* hi = (uint8_t*)workspace;
+            uint8_t* lo = hi + pk;
+            int rc = wide_pack_b(B, variant, N, K, hi, lo, (cudaStream_t)stream);
+            if (rc) return rc;
+            return wide_gemm(nsplit, variant, A, B, C, M, N, K, lda, ldb, N, accumulate, nullptr, 0, (cudaStream_t)stream, "wide_gemm_kernel", hi, lo);
+        }
+    }
     return wide_gemm(nsplit, variant, A, B, C, M, N, K, lda, ldb, N, accumulate, (float*)workspace, workspace_bytes / sizeof(float),
                      (cudaStream_t)stream, "wide_gemm_kernel");
 }
