@@ -9,10 +9,11 @@ import masters_thesis_b200 as B
 ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=4096); ap.add_argument("--steps", type=int, default=1)
 ap.add_argument("--engine", default="tc_precise"); ap.add_argument("--dropout", type=float, default=0.2)
+ap.add_argument("--hidden", type=int, default=64); ap.add_argument("--layers", type=int, default=2)
 a = ap.parse_args()
 dev = "cuda:0"
 torch.manual_seed(0)
-m = B.FinancialLstmMse(3, 64, 2, a.dropout, 1e-4)
+m = B.FinancialLstmMse(3, a.hidden, a.layers, a.dropout, 1e-4)
 e = m.attach(dev, a.engine)
 src = B.data.DeviceBatchSource(dev)
 for k in range(a.steps):
