@@ -78,7 +78,8 @@ heads_stats_kernel(const float* __restrict__ hp, const float* __restrict__ hT, c
     if (do_nll) mu = factor[2 * ((w / wpg) * wpg)];
 
     float sse = 0.f, sae = 0.f, spq = 0.f, uacc = 0.f, s_acc = 0.f, lp_acc = 0.f;
-    for (int r = warp; r < S; r += HEADS_WARPS) {
+#pragma unroll 5
+    for (int r = warp; r < S; r += HEADS_WARPS) {          // unrolled: several rows' loads in flight per warp
         const int64_t row = w * S + r;
         const float* h = hT + row * H;
         float pa = 0.f, pb = 0.f;
@@ -192,7 +193,8 @@ heads_grad_kernel(const float* __restrict__ hp, const float* __restrict__ hT, co
     if (do_nll) { mu = gs[0]; rDn = gs[1]; suD = gs[2]; su2D = gs[3]; c4 = gs[4]; uD = lane < n ? gs[PW_FIXED + lane] : 0.f; }
     (void)rDn;
 
-    for (int r = warp; r < S; r += HEADS_WARPS) {
+#pragma unroll 5
+    for (int r = warp; r < S; r += HEADS_WARPS) {          // unrolled: several rows' loads in flight per warp
         const int64_t row = w * S + r;
         const float al = alpha_i[row], be = beta_i[row];
         const float rt = lane < n ? y_stock[row * n + lane] : 0.f;
