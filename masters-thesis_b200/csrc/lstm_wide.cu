@@ -48,6 +48,11 @@ struct GemmArgs {
     // pre-packed B (variants 0, 1): operand images of every (N tile, K chunk) as wide_pack_b_kernel lays them out; then B is
     // staged by the TMA engine (one bulk copy per image) instead of by the threads
     const uint8_t* bp_hi; const uint8_t* bp_lo;
+    // fused LSTM cell (forward recurrent step, FUSE kernels only): C is the gate buffer G_t [M][4H] in torch gate order holding
+    // the input projection (has_x) and receiving the ACTIVATED gates; one N tile = the four gates of 64 hidden units
+    int H; int has_x; int F;
+    const float* b_ih; const float* b_hh; const float* c_prev; float* c_out; float* h_out;
+    const float* x_t; const float* w_ih0;
 };
 
 __device__ __forceinline__ int blk_rr(int lane) { return (lane >> 1) & 7; }
@@ -97,7 +102,9 @@ struct GemmSmem {
     static constexpr uint32_t total = off_tmem + 16 + 128;
 };
 
-template <int NSPLIT, int VAR>
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+
+template <int NSPLIT, int VAR, bool FUSE = false>
 __global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
     using S = GemmSmem<NSPLIT>;
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -202,7 +209,65 @@ __global__ void __launch_bounds__(G_THREADS, 1) wide_gemm_kernel(GemmArgs a) {
         mbar_wait(&bars[2], 0u);
         tc_fence_after();
     }
-    {
+    if (FUSE) {
+        // accumulator columns of this tile: [i | f | g | o] x 64 units (gate-interleaved weight images, pack variant 3);
+        // warp = TMEM lane quarter x unit half; the cell update of wide_cell_fwd_kernel on the accumulators
+        const int lq = warp & 3, uh = warp >> 2, H = a.H;
+        const int64_t row = m0 + lq * 32 + lane;
+        const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16);
+#pragma unroll 1
+        for (int uc = 0; uc < 4; ++uc) {
+            const int ul = uh * 32 + uc * 8;                      // first unit of the chunk inside the tile
+            float acc[4][8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) tmem_ld8(tl + (uint32_t)(k * 64 + ul), acc[k]);
+            tmem_ld_wait();
+            if (row < a.M) {
+                const int u0 = nt_idx * 64 + ul;                  // global hidden unit
+                float* g = a.C + row * a.ldc;
+                float cp[8], cv[8], hv[8];
+                if (a.c_prev) {
+                    const float4* c4 = reinterpret_cast<const float4*>(a.c_prev + row * H + u0);
+                    const float4 c0 = c4[0], c1 = c4[1];
+                    cp[0] = c0.x; cp[1] = c0.y; cp[2] = c0.z; cp[3] = c0.w; cp[4] = c1.x; cp[5] = c1.y; cp[6] = c1.z; cp[7] = c1.w;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cp[j] = 0.f;
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int col = k * H + u0;
+                    if (a.has_x) {
+                        const float4* x4 = reinterpret_cast<const float4*>(g + col);
+                        const float4 x0 = x4[0], x1 = x4[1];
+                        acc[k][0] += x0.x; acc[k][1] += x0.y; acc[k][2] += x0.z; acc[k][3] += x0.w;
+                        acc[k][4] += x1.x; acc[k][5] += x1.y; acc[k][6] += x1.z; acc[k][7] += x1.w;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float v = acc[k][j] + (a.b_ih[col + j] + a.b_hh[col + j]);
+                        if (a.w_ih0) for (int f = 0; f < a.F; ++f) v = fmaf(a.x_t[row * a.F + f], a.w_ih0[(int64_t)(col + j) * a.F + f], v);
+                        acc[k][j] = k == 2 ? tanhf(v) : sigmoidf_(v);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    cv[j] = acc[1][j] * cp[j] + acc[0][j] * acc[2][j];
+                    hv[j] = acc[3][j] * tanhf(cv[j]);
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float4* o4 = reinterpret_cast<float4*>(g + k * H + u0);
+                    o4[0] = make_float4(acc[k][0], acc[k][1], acc[k][2], acc[k][3]);
+                    o4[1] = make_float4(acc[k][4], acc[k][5], acc[k][6], acc[k][7]);
+                }
+                float4* co = reinterpret_cast<float4*>(a.c_out + row * H + u0);
+                co[0] = make_float4(cv[0], cv[1], cv[2], cv[3]); co[1] = make_float4(cv[4], cv[5], cv[6], cv[7]);
+                float4* ho = reinterpret_cast<float4*>(a.h_out + row * H + u0);
+                ho[0] = make_float4(hv[0], hv[1], hv[2], hv[3]); ho[1] = make_float4(hv[4], hv[5], hv[6], hv[7]);
+            }
+        }
+    } else {
         const int lq = warp & 3, ch = warp >> 2;
         const int64_t row = m0 + lq * 32 + lane;
         float* crow = a.part ? a.part + ((int64_t)blockIdx.z * a.M + row) * a.N + n0 : a.C + row * a.ldc + n0;
@@ -243,13 +308,18 @@ wide_pack_b_kernel(const float* __restrict__ W, int variant, int N, int64_t K, u
     const int64_t total = (int64_t)N * K;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int64_t n, k;
-        if (variant == 0) { n = i / K; k = i - n * K; } else { k = i / N; n = i - k * N; }
-        const int nt = (int)(n / GN), nl = (int)(n - (int64_t)nt * GN);
+        if (variant != 1) { n = i / K; k = i - n * K; } else { k = i / N; n = i - k * N; }
+        int nt = (int)(n / GN), nl = (int)(n - (int64_t)nt * GN);
+        if (variant == 3) {                   // W row n = gate * H + u  ->  tile u / 64, row gate * 64 + u % 64   (N = 4H)
+            const int Hh = N / 4, gate = (int)(n / Hh), u = (int)(n - (int64_t)gate * Hh);
+            nt = u / 64;
+            nl = gate * 64 + (u & 63);
+        }
         const int64_t kc = k / GK;
         const int kl = (int)(k - kc * GK);
         const int NT = N - nt * GN < GN ? N - nt * GN : GN;
-        const int64_t img = variant == 0 ? (int64_t)nt * nchunk + kc : kc * ntile + nt;
-        const int r = variant == 0 ? nl : kl, c = variant == 0 ? kl : nl, cols = variant == 0 ? GK : NT;
+        const int64_t img = variant != 1 ? (int64_t)nt * nchunk + kc : kc * ntile + nt;
+        const int r = variant != 1 ? nl : kl, c = variant != 1 ? kl : nl, cols = variant != 1 ? GK : NT;
         const uint32_t o = (uint32_t)(r >> 3) * (uint32_t)(cols / 8) * LBO_BYTES + (uint32_t)(c >> 3) * LBO_BYTES + (uint32_t)(r & 7) * 16 + (uint32_t)(c & 7) * 2;
         const float v = W[i];
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
@@ -267,10 +337,10 @@ __global__ void __launch_bounds__(256) wide_splitk_reduce_kernel(const float* __
     }
 }
 
-template <int NSPLIT, int VAR>
+template <int NSPLIT, int VAR, bool FUSE = false>
 int launch_gemm_t(GemmArgs a, int splits, cudaStream_t st, const char* name) {
     using S = GemmSmem<NSPLIT>;
-    auto kern = wide_gemm_kernel<NSPLIT, VAR>;
+    auto kern = wide_gemm_kernel<NSPLIT, VAR, FUSE>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     dim3 grid((unsigned)(((a.M + GM - 1) / GM) * ((a.N + GN - 1) / GN)), 1, (unsigned)splits);
     {
@@ -287,7 +357,8 @@ int launch_gemm_t(GemmArgs a, int splits, cudaStream_t st, const char* name) {
 size_t wide_pack_bytes(int N, int64_t K) { return (size_t)((N + GN - 1) / GN) * (size_t)(K / GK) * GN * GK * 2; }   // one of hi / lo
 
 int wide_pack_b(const float* W, int variant, int N, int64_t K, uint8_t* out_hi, uint8_t* out_lo, cudaStream_t st) {
-    B200_CHECK_ARG(variant == 0 || variant == 1, "wide_pack_b: variant must be 0 or 1");
+    B200_CHECK_ARG(variant == 0 || variant == 1 || variant == 3, "wide_pack_b: variant must be 0, 1 or 3 (gate-interleaved 0)");
+    B200_CHECK_ARG(variant != 3 || N % 256 == 0, "wide_pack_b: gate-interleaved packing needs N = 4H with H a multiple of 64");
     B200_CHECK_ARG(W && out_hi && out_lo && N % 64 == 0 && K % GK == 0, "wide_pack_b: bad arguments");
     int64_t grid = ((int64_t)N * K + 255) / 256;
     if (grid > (int64_t)num_sms() * 8) grid = (int64_t)num_sms() * 8;
@@ -307,7 +378,8 @@ int wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C,
     B200_CHECK_ARG(variant != 2 || M % GM == 0, "wide_gemm: M must be a multiple of 128 for variant 2, got %lld", (long long)M);
     B200_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0, "wide_gemm: leading dimensions must be multiples of 4 floats");
     B200_CHECK_ARG((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0, "wide_gemm: pointers must be 16-byte aligned");
-    GemmArgs a{A, B, C, M, N, K, lda, ldb, ldc, accumulate, 0, nullptr, variant == 2 ? nullptr : bp_hi, variant == 2 ? nullptr : bp_lo};
+    GemmArgs a{A, B, C, M, N, K, lda, ldb, ldc, accumulate, 0, nullptr, variant == 2 ? nullptr : bp_hi, variant == 2 ? nullptr : bp_lo,
+               0, 0, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int splits = 1;
     const int64_t chunks = (K + GK - 1) / GK;
     if (variant == 2 && part) {
@@ -337,11 +409,20 @@ int wide_gemm(int nsplit, int variant, const float* A, const float* B, float* C,
     return B200_OK;
 }
 
+// Forward recurrent step with the LSTM cell fused into the GEMM epilogue: G_t (input projection, torch gate order) += h_{t-1} . W_hh^T,
+// bias, activations, c_t, h_t; G_t receives the activated gates.  W_hh comes as gate-interleaved operand images (pack variant 3).
+int wide_rec_fwd_fused(int nsplit, const float* h_prev, float* Gt, int64_t N, int H, int has_x, const float* b_ih, const float* b_hh,
+                       const float* c_prev, float* c_out, float* h_out, const float* x_t, const float* w_ih0, int F,
+                       const uint8_t* bp_hi, const uint8_t* bp_lo, cudaStream_t st) {
+    B200_CHECK_ARG(H % 64 == 0 && bp_hi && bp_lo, "wide_rec_fwd_fused: needs H % 64 == 0 and packed weights");
+    GemmArgs a{h_prev, nullptr, Gt, N, 4 * H, H, H, H, 4LL * H, 0, (int64_t)H, nullptr, bp_hi, bp_lo,
+               H, has_x, F, b_ih, b_hh, c_prev, c_out, h_out, x_t, w_ih0};
+    return nsplit == 2 ? launch_gemm_t<2, 0, true>(a, 1, st, "wide_gemm_rec_fwd_cell") : launch_gemm_t<1, 0, true>(a, 1, st, "wide_gemm_rec_fwd_cell");
+}
+
 namespace {
 
 // ------------------------------------------------------------------------------------------- pointwise kernels
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
-
 // forward cell of step t of one layer: G_t [N][4H] holds the GEMM part of the gate pre-activations (nothing for
 // layer 0 at t = 0); adds bias (and x_t . W_ih^T for layer 0), writes activated gates, c_t, h_t
 __global__ void __launch_bounds__(256)
@@ -543,6 +624,11 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
     const int nsplit = mode == B200_MODE_TC_PRECISE ? 2 : 1;
     const bool drop = training && p > 0.f;
     const int64_t lsz = (int64_t)T * N * H, NH = N * H, G4 = 4LL * H;
+    // B200_WIDE_FUSE=1: LSTM cell in the epilogue of the recurrent GEMM.  Measured (hidden 256 x 8 layers, 256 windows): no gain in
+    // bf16 mode (85 ms against 47 + 38 ms for GEMM + cell kernel) and slower with three products (125 against 102 ms): the
+    // thread-per-row epilogue runs after the MMAs of its CTA instead of beside another kernel's, so it stays off by default.
+    const char* fe = getenv("B200_WIDE_FUSE");
+    const bool fuse = fe && atoi(fe) == 1;
     for (int l = 0; l < L; ++l) {
         const LayerParams lp = layer_params(params, F, H, l);
         float* G = w.G + (int64_t)l * lsz * 4;
@@ -550,7 +636,7 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
         float* cs = stash_c + (int64_t)l * lsz;
         // this layer's weights as K-major operand images (once per step; every GEMM below then stages B with bulk copies)
         if (l > 0) { rc = wide_pack_b(lp.w_ih, 0, (int)G4, H, w.pack[0], w.pack[1], st); if (rc) return rc; }
-        rc = wide_pack_b(lp.w_hh, 0, (int)G4, H, w.pack[2], w.pack[3], st);
+        rc = wide_pack_b(lp.w_hh, fuse ? 3 : 0, (int)G4, H, w.pack[2], w.pack[3], st);
         if (rc) return rc;
         if (l > 0) {
             const float* xin = stash_h + (int64_t)(l - 1) * lsz;
@@ -564,6 +650,13 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
         }
         for (int t = 0; t < T; ++t) {
             float* Gt = G + (int64_t)t * N * G4;
+            if (t > 0 && fuse) {
+                rc = wide_rec_fwd_fused(nsplit, hs + (int64_t)(t - 1) * NH, Gt, N, H, l > 0 ? 1 : 0, lp.b_ih, lp.b_hh, cs + (int64_t)(t - 1) * NH,
+                                        cs + (int64_t)t * NH, hs + (int64_t)t * NH, l == 0 ? x + (int64_t)t * N * F : nullptr,
+                                        l == 0 ? lp.w_ih : nullptr, F, w.pack[2], w.pack[3], st);
+                if (rc) return rc;
+                continue;
+            }
             if (t > 0) {
                 rc = wide_gemm(nsplit, 0, hs + (int64_t)(t - 1) * NH, lp.w_hh, Gt, N, (int)G4, H, H, H, G4, l > 0 ? 1 : 0, nullptr, 0, st,
                                "wide_gemm_rec_fwd", w.pack[2], w.pack[3]);
