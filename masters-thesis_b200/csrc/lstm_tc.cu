@@ -34,7 +34,8 @@ using namespace tc;
 //   1 forward layers > 0: x     2 backward layer 0: h, c     backward layers > 0: 4 x, 8 h, 16 c, 32 d_out
 // Measured (B = 4096, 1xB200, tools/kbench.sh with B200_TC_PREFETCH=...): bit 2 is worth 0.5 ms in the layer-0 backward
 // kernel; in the layer > 0 backward kernel (whose epilogue warps stage the image themselves, loads issued a wait ahead)
-// each of bits 4, 8, 16 COSTS 0.9-1.0 ms (20.1 -> 21.1 ms) and bit 32 is neutral; bit 1 is worth < 0.1 ms.
+// each of bits 4, 8, 16 COST 0.9-1.0 ms (20.1 -> 21.1 ms) when issued at the step boundary and are neutral when issued after
+// the second quarter of the step (as they are now); bit 32 is neutral; bit 1 is worth < 0.1 ms.
 constexpr int PF_DEFAULT = 1 | 2 | 32;
 __constant__ int c_tc_prefetch = PF_DEFAULT;
 #ifdef B200_ABLATE                    // timing experiments only (build with B200_ABLATE=1): env B200_TC_DBG is a bit mask of backward
@@ -1017,6 +1018,12 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             for (int t = T - 1; t >= 0; --t, ++g) {
                 if (tracer) trace_ev(1, 0, 0, g, ntr);
                 const int pf = c_tc_prefetch;
+                if (EPI_LOADS && (pf & 28) && lw == 0 && lane == 0) {
+                    // time the prefetch into the middle of the step (after its second quarter): at the step boundary the epilogue
+                    // warps' image loads are on the critical path and a 128 KB L2 fill in front of them costs more than it saves
+                    mbar_wait(&da_full[0], 0u);
+                    mbar_wait(&da_full[0], 1u);
+                }
                 if ((LAYER0 ? (pf & 2) : (pf & 60)) && lw == 0 && lane == 0 && t >= 1) {
                     // pull the NEXT step's rows (x_{t-1}, h_{t-2}, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
                     const int64_t nrow = rows_live < TM ? rows_live : TM;
