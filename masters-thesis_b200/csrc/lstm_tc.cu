@@ -694,7 +694,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                    float* __restrict__ bpart, const uint64_t* __restrict__ drop_bits, float p) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     constexpr int KX = S::KX, KC = S::KC;
-    constexpr uint32_t SBO_W = sbo_of(KC), SBO_DA = sbo_of(64);
+    // da quarter images: with two buffers (DB == 2) both quarters of a pair live in ONE [128 x 128] image (buffer b = column block
+    // b), so that the weight gradient of the pair is a single N = 128 MMA per product and k-step; hi and lo images follow each other
+    constexpr uint32_t SBO_W = sbo_of(KC), SBO_DA = sbo_of(64 * DB);
+    constexpr uint32_t DA_BUF = DB == 2 ? 8 * LBO_BYTES : 0;            // byte offset of buffer 1 inside a row group
+    constexpr uint32_t DA_LO = DB * S::DAB;                              // lo image after the hi image(s)
     constexpr int DH_COL0 = LAYER0 ? 0 : TH;                 // column of dh inside the d region
     constexpr int ND = LAYER0 ? TH : 2 * TH;                  // dgrad N
     // With a single image buffer the reload sits on the critical path between two steps, exactly when the eight
@@ -860,8 +864,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     tc_fence_after();
                     if (tracer) trace_ev(0, 1, q, g, ntr);
                     const int buf = (int)(qi % DB);
-                    uint8_t* da_hi = smem + S::off_da + (buf * NSPLIT) * S::DAB;
-                    uint8_t* da_lo = da_hi + S::DAB;
+                    uint8_t* da_hi = smem + S::off_da + (DB == 2 ? buf * DA_BUF : 0u);
+                    uint8_t* da_lo = da_hi + DA_LO;
                     float av[4][EU];
                     const uint32_t acol = TMEM_A + 64 * slot + EU * sub;
 #pragma unroll
@@ -1106,7 +1110,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 #pragma unroll
             for (int b = 0; b < XB; ++b) xk_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, LBO_BYTES, SBO_W);
 #pragma unroll
-            for (int b = 0; b < DB; ++b) dak_hi[b] = make_desc(s_base + S::off_da + (b * NSPLIT) * S::DAB, LBO_BYTES, SBO_DA);
+            for (int b = 0; b < DB; ++b) dak_hi[b] = make_desc(s_base + S::off_da + b * DA_BUF, LBO_BYTES, SBO_DA);
             // Gates of the quarter PAIR (nq, nq + 1), nq even -> TMEM slots 0 and 1 with ONE N = 128 MMA per product and k-step:
             // a tcgen05.mma of this size costs ~60 clk of fixed overhead plus ~0.43 clk per column of N (measured), so two
             // N = 64 quarters cost 174 clk and the pair 115.  Waits for both slots to be read out and for the image of its step.
@@ -1151,7 +1155,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 // ---- dgrad partial (on the dh critical path).  K = the four 16-row runs of this quarter of Wcat
                 {
                     const uint32_t d = tmem_base + TMEM_D;
-                    const uint64_t dah = dak_hi[buf], dal = dah + (S::DAB >> 4);
+                    const uint64_t dah = dak_hi[buf], dal = dah + (DA_LO >> 4);
 #pragma unroll
                     for (int gate = 0; gate < 4; ++gate) {
                         const uint64_t wk = (uint64_t)(((uint32_t)((q * 64 + gate * 16) / 8) * SBO_W) >> 4);
@@ -1184,37 +1188,37 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     } else {
         // ===================================== MMA issuer B: wgrad ==================================================
         if (lane == 0 && total_q > 0) {
-            constexpr uint32_t idesc_w = make_idesc_bf16(TM, 64, 1, 1);       // wgrad: both MN-major
+            constexpr int WN = 64 * DB;                                       // quarters per MMA: one (DB == 1) or a pair (DB == 2)
+            constexpr uint32_t idesc_w = make_idesc_bf16(TM, WN, 1, 1);       // wgrad: both MN-major
             const uint32_t s_base = smem_u32(smem);
-            uint64_t xm_hi[XB], dam_hi[DB];
+            uint64_t xm_hi[XB];
 #pragma unroll
             for (int b = 0; b < XB; ++b) xm_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, SBO_W, LBO_BYTES);
-#pragma unroll
-            for (int b = 0; b < DB; ++b) dam_hi[b] = make_desc(s_base + S::off_da + (b * NSPLIT) * S::DAB, SBO_DA, LBO_BYTES);
+            const uint64_t dam_hi = make_desc(s_base + S::off_da, SBO_DA, LBO_BYTES), dam_lo = dam_hi + (DA_LO >> 4);
             int ntr = 0;
-            for (int64_t qi = 0; qi < total_q; ++qi) {
+            for (int64_t qi = 0; qi < total_q; qi += DB) {
                 const int64_t g = qi >> 2;
                 const int q = (int)(qi & 3);
-                const int buf = (int)(qi % DB);
-                mbar_wait(&da_full[buf], (uint32_t)((qi / DB) & 1));
+#pragma unroll
+                for (int b = 0; b < DB; ++b) mbar_wait(&da_full[b], (uint32_t)((qi / DB) & 1));
                 tc_fence_after();
-                // dWcat^T[:, quarter columns] += xh^T * da_quarter, K = the 128 rows of the tile
+                // dWcat^T[:, quarter (pair) columns] += xh^T * da, K = the 128 rows of the tile
                 const uint32_t d = tmem_base + TMEM_DW + q * 64;
                 const uint64_t xh = xm_hi[g % XB], xl = xh + (S::XHB >> 4);
-                const uint64_t dah = dam_hi[buf], dal = dah + (S::DAB >> 4);
 #pragma unroll
                 for (int ks = 0; ks < TM / 16; ++ks) {
                     const uint64_t xo = (uint64_t)((ks * 2 * SBO_W) >> 4), dao = (uint64_t)((ks * 2 * SBO_DA) >> 4);
-                    umma_bf16(d, xh + xo, dah + dao, idesc_w, (g > 0 || ks > 0) ? 1u : 0u);
+                    umma_bf16(d, xh + xo, dam_hi + dao, idesc_w, (g > 0 || ks > 0) ? 1u : 0u);
                     if (NSPLIT == 2) {
                         // all three split products: dropping xl * dah (x rounded to bf16 in the weight gradient only) saves 4 % of
                         // the kernel but fails the 1e-3 gradient gate on the reference's golden vectors (measured)
-                        umma_bf16(d, xl + xo, dah + dao, idesc_w, 1);
-                        umma_bf16(d, xh + xo, dal + dao, idesc_w, 1);
+                        umma_bf16(d, xl + xo, dam_hi + dao, idesc_w, 1);
+                        umma_bf16(d, xh + xo, dam_lo + dao, idesc_w, 1);
                     }
                 }
-                umma_commit(&da_free[buf]);               // second arrival
-                if (q == 3) umma_commit(&xh_free[g % XB]);
+#pragma unroll
+                for (int b = 0; b < DB; ++b) umma_commit(&da_free[b]);      // second arrival
+                if (q + DB == 4) umma_commit(&xh_free[g % XB]);
                 trace_ev(3, 4, q, g, ntr);
             }
             umma_commit(done);
