@@ -226,3 +226,38 @@ def test_model_forward_api():
     np.testing.assert_allclose(b.cpu().numpy(), bo.numpy(), atol=1e-5)
     sd = model.state_dict()
     assert list(sd.keys()) == list(om.state_dict().keys())
+
+
+@pytest.mark.parametrize("engine,H", [("ffma", 64), ("tc_precise", 64), ("tc_fast", 64), ("tc_precise", 128)])
+def test_no_out_of_bounds_writes(engine, H, data):
+    """Every device buffer the library writes (stash, dhT, alpha/beta, workspaces, gradients) sits between guard bands
+    for a training step on a ragged batch (3 windows x 7 stocks = 21 sequences: a partial tile, a partial tile pair):
+    the guards must come back untouched.  (compute-sanitizer is not available on this pool.)"""
+    if engine != "ffma" and not B._lib.load().b200_mode_available(B.MODES[engine]):
+        pytest.skip("tcgen05 engine unavailable")
+    G = 4096
+    torch.manual_seed(5)
+    m = O.OracleLstm(3, H, 2, 0.0)
+    e = B.LstmEngine(3, H, 2, 0.3, DEV, engine, n_stocks=7)
+    e.load_params(O.flat_params(m))
+    X, y, f, ip = ref_batch(data, 0, 3)
+    batch = B.DeviceBatch.from_reference([X[:, :7].contiguous(), y[:, :7].contiguous(), f, ip[:, :7].contiguous()], DEV)
+    e.ensure_capacity(batch.n_windows)
+    guards = {}
+    for name in ("stash_h", "stash_c", "dhT", "alpha", "beta", "lstm_ws", "heads_ws", "grads"):
+        t = getattr(e, name)
+        fill = 0xA5 if t.dtype == torch.uint8 else -123456.0
+        big = torch.full((t.numel() + 2 * G,), fill, dtype=t.dtype, device=DEV)
+        view = big[G:G + t.numel()]
+        view.copy_(t)
+        setattr(e, name, view)
+        guards[name] = (big, t.numel(), fill)
+    e.forward(batch, training=True, dropout_seed=3)
+    e.heads(batch, "combined", 100.0, None, 1.0, True)
+    e.backward(batch, True, dropout_seed=3)
+    e.optimizer_step(1e-4, 5.0)
+    torch.cuda.synchronize()
+    for name, (big, n, fill) in guards.items():
+        lo, hi = big[:G], big[G + n:]
+        assert bool((lo == fill).all()) and bool((hi == fill).all()), f"{engine}: write outside {name}"
+    assert np.isfinite(e.grads[: e.P].cpu().numpy()).all()
