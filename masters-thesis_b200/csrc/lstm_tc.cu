@@ -549,9 +549,12 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
 // The epilogue of a quarter has a part that does not depend on the dh recurrence (gates and tanh(c_t) from the
 // recomputed pre-activations) and a part that does (da); the read-back of dh_{t} from the previous step's dgrad is
 // placed between the two, so that the dgrad latency of the last quarter hides behind the gate math of the next step.
-// The MMA warp issues, per quarter: dgrad (critical path) -> gate recompute two quarters ahead -> wgrad.
+// MMA issue: thread A issues, per quarter, dgrad (critical path) and -- after quarters 0 and 2 -- the gate recompute of
+// the NEXT pair of quarters as N = 128 MMAs into both slots; thread B issues wgrad (per quarter, or per pair as N = 128
+// MMAs when two da buffers exist).  A tcgen05.mma of these sizes costs ~60 clk plus ~0.43 clk per column of N.
 // Warp roles: 8 epilogue warps (thread = one sequence x 8 units per quarter), 2 loader warps ([x_t | h_{t-1}] image
-// from the fp32 stash, dropout keep-bits applied), 1 MMA warp.
+// from the fp32 stash, dropout keep-bits applied; with a single image buffer the epilogue warps stage it themselves),
+// 2 MMA issuer warps.
 // Barriers: xh_full/xh_free, a_full/a_free (per slot), da_full/da_free, d_full/d_free, done.
 // Epilogue geometry.  BW_EU = hidden units per epilogue thread per 16-unit quarter: 8 -> 8 epilogue warps (2 per SM
 // sub-partition), 4 -> 16 warps.  Measured on B200 (B = 4096, precise): EU = 8 is 15-20 % faster; with 16 warps the
