@@ -1213,8 +1213,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     const uint64_t xo = (uint64_t)((ks * 2 * SBO_W) >> 4), dao = (uint64_t)((ks * 2 * SBO_DA) >> 4);
                     umma_bf16(d, xh + xo, dam_hi + dao, idesc_w, (g > 0 || ks > 0) ? 1u : 0u);
                     if (NSPLIT == 2) {
-                        // all three split products: dropping xl * dah (x rounded to bf16 in the weight gradient only) saves 4 % of
-                        // the kernel but fails the 1e-3 gradient gate on the reference's golden vectors (measured)
+                        // All three split products.  Measured (tools/grad_margin.py, per-tensor max error / max gradient): dropping
+                        // xl * dah fails the 1e-3 gate in layer 0; in layers > 0 dropping either xl * dah or xh * dal saves 0.95 ms
+                        // (5 % of that kernel) and passes every test, but lands at 7e-4 .. 8e-4 on some weight tensors (3e-5 with
+                        // all three) -- too close to the 1e-3 parity gate to ship.
                         umma_bf16(d, xl + xo, dam_hi + dao, idesc_w, 1);
                         umma_bf16(d, xh + xo, dam_lo + dao, idesc_w, 1);
                     }
