@@ -17,6 +17,7 @@ Differences from the reference entry point, all forced by the environment (SURVE
 from __future__ import annotations
 
 import sys
+import os
 from pathlib import Path
 
 import torch
@@ -34,6 +35,9 @@ def banner(title, width=50):
 
 
 def run(cfg):
+    if int(os.environ.get("RANK", "0")) != 0:           # like Lightning's rank_zero_only printing
+        global print
+        print = lambda *a, **k: None
     banner("EXPERIMENT CONFIGURATION", 70)
     print(f"Datamodule: {cfg.datamodule.name}")
     print(f"Model: {cfg.model.name} (hidden={cfg.model.hidden_size}, layers={cfg.model.num_layers})")
