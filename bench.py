@@ -226,7 +226,7 @@ def run_b200(args):
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.batch * world * e2e_steps / float(dt), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 16, "steps": e2e_steps,
-               "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> HostBatchFeeder (cudaMemcpyAsync + layout conversion on a copy stream, one batch ahead) -> B200Trainer.training_step -> LossMailbox (every step's [mse, nll, total, mae] copied to pinned host memory and read by the host one step behind the enqueue front)"}
+               "path": "pinned host [X,y,factor,inv_psi] (reference DataLoader layout) -> HostBatchFeeder (cudaMemcpyAsync + b200_collate_reference on a copy stream, one batch ahead) -> B200Trainer.training_step -> LossMailbox (every step's [mse, nll, total, mae] copied to pinned host memory and read by the host one step behind the enqueue front)"}
 
     if world > 1:
         dist.barrier()

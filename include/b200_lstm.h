@@ -101,6 +101,11 @@ B200_API int b200_series_batch(const float* stocks, const float* market, int64_t
                       int64_t stride, int n_features, int prediction_task, float* x, float* y_stock,
                       float* y_market, float* factor, float* inv_psi, float* ols_alpha, float* ols_beta,
                       void* stream);
+/* A batch in the reference's layout, already on the device (X [B][S][T][F], y [B][S][n][4]: what its DataLoader yields,
+ * src/data.py:216, 236-238) -> the kernels' layout (x [T][N][F], y_stock [N][n] = channel 0, y_market [B][n] = channel 1):
+ * replaces the flatten(0, 1) / channel slicing of _shared_step (src/model.py:192-196) for host-fed batches. */
+B200_API int b200_collate_reference(const float* X, const float* y, int64_t n_windows, int n_stocks, int lookback, int target,
+                           int n_features, float* x, float* y_stock, float* y_market, void* stream);
 /* days [first_day, first_day + n_days) of the generator's series itself: stocks [n_stocks][n_days], market [n_days]
  * (what SyntheticLogReturns.generate returns, src/data.py:49-59) */
 B200_API int b200_gen_series(uint64_t seed, int64_t first_day, int64_t n_days, int n_stocks, float* stocks, float* market,

@@ -26,6 +26,7 @@ PROTOTYPES = {
     "b200_gen_batch": (_i, [_u64, _p, _l, _l, _i, _i, _i, _l, _i, _p, _p, _p, _p, _p, _p]),
     "b200_series_batch": (_i, [_p, _p, _l, _p, _l, _l, _i, _i, _i, _l, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     "b200_gen_series": (_i, [_u64, _l, _l, _i, _p, _p, _p]),
+    "b200_collate_reference": (_i, [_p, _p, _l, _i, _i, _i, _i, _p, _p, _p, _p]),
     "b200_gen_coefficients": (_i, [_u64, _i, _p, _p, _p]),
     "b200_philox4x32": (_i, [_u64, _p, _l, _p, _p]),
     "b200_dropout_mask": (_i, [_u64, _i, _l, _i, _i, _f, _p, _p]),

@@ -176,6 +176,44 @@ __global__ void dropout_mask_kernel(uint64_t seed, int layer, int64_t N, int T, 
     }
 }
 
+// Reference-layout batch (device copies of what the reference's DataLoader yields, src/data.py:216, 236-238:
+// X [B][S][T][F], y [B][S][n][4], factor [B][2], inv_psi [B][S]) -> the kernels' layout: x time-major [T][N][F], y_stock [N][n]
+// (channel 0), y_market [B][n] (channel 1 of stock 0).  One pass; reads and writes are both coalesced over the F-wide rows
+// through a shared-memory transpose of a (32 sequences x 32 steps) tile.
+__global__ void __launch_bounds__(256)
+collate_reference_kernel(const float* __restrict__ X, const float* __restrict__ y, int64_t B, int S, int T, int n, int F,
+                         float* __restrict__ x, float* __restrict__ y_stock, float* __restrict__ y_market) {
+    extern __shared__ float tile[];                       // [32 seq][32 steps * F + 1]
+    const int64_t N = B * S;
+    const int TF = 32 * F + 1;
+    const int64_t tiles_n = (N + 31) / 32;
+    const int tiles_t = (T + 31) / 32;
+    for (int64_t tl = blockIdx.x; tl < tiles_n * tiles_t; tl += gridDim.x) {
+        const int64_t n0 = (tl / tiles_t) * 32;
+        const int t0 = (int)(tl % tiles_t) * 32;
+        const int tw = T - t0 < 32 ? T - t0 : 32;
+        // read: for each sequence, tw * F contiguous floats of X[(n, t0.., :)]
+        for (int i = threadIdx.x; i < 32 * tw * F; i += blockDim.x) {
+            const int r = i / (tw * F), c = i - r * (tw * F);
+            if (n0 + r < N) tile[r * TF + c] = X[((n0 + r) * T + t0) * F + c];
+        }
+        __syncthreads();
+        // write: for each step, 32 * F contiguous floats of x[(t, n0.., :)]
+        for (int i = threadIdx.x; i < tw * 32 * F; i += blockDim.x) {
+            const int tt = i / (32 * F), c = i - tt * (32 * F);
+            const int r = c / F, f = c - r * F;
+            if (n0 + r < N) x[((int64_t)(t0 + tt) * N + n0 + r) * F + f] = tile[r * TF + tt * F + f];
+        }
+        __syncthreads();
+    }
+    const int64_t total = N * n;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        y_stock[i] = y[i * 4];
+        const int64_t row = i / n;
+        if (row % S == 0) y_market[(row / S) * n + (i - row * n)] = y[i * 4 + 1];
+    }
+}
+
 // the generator's series itself, for consumers that need days rather than windows (reconstruction mode, test.py)
 __global__ void __launch_bounds__(256)
 gen_series_kernel(uint64_t seed, int64_t first_day, int64_t n_days, int S, float* __restrict__ stocks, float* __restrict__ market) {
@@ -249,6 +287,21 @@ extern "C" int b200_series_batch(const float* stocks, const float* market, int64
     B200_CHECK_ARG(x && y_stock && y_market && factor && inv_psi, "series_batch: null output pointer");
     return launch_batch("series_batch", 0, stocks, market, n_samples, window_idx, first_window, n_windows, n_stocks, lookback, target,
                         stride, n_features, prediction_task ? 1 : 0, x, y_stock, y_market, factor, inv_psi, ols_alpha, ols_beta, stream);
+}
+
+extern "C" int b200_collate_reference(const float* X, const float* y, int64_t n_windows, int n_stocks, int lookback, int target,
+                                      int n_features, float* x, float* y_stock, float* y_market, void* stream) {
+    B200_CHECK_ARG(n_windows >= 0 && n_stocks > 0 && lookback > 0 && target > 0 && n_features > 0 && n_features <= 8,
+                   "collate_reference: bad sizes");
+    if (n_windows == 0) return B200_OK;
+    B200_CHECK_ARG(X && y && x && y_stock && y_market, "collate_reference: null pointer");
+    const int64_t N = n_windows * n_stocks;
+    const int64_t tiles = ((N + 31) / 32) * ((lookback + 31) / 32);
+    int64_t grid = tiles < (int64_t)num_sms() * 8 ? tiles : (int64_t)num_sms() * 8;
+    const size_t smem = (size_t)32 * (32 * n_features + 1) * sizeof(float);
+    { TimedLaunch _t("collate_reference_kernel", (cudaStream_t)stream); collate_reference_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(X, y, n_windows, n_stocks, lookback, target, n_features, x, y_stock, y_market); }
+    B200_LAUNCH_CHECK("collate_reference_kernel");
+    return B200_OK;
 }
 
 extern "C" int b200_gen_series(uint64_t seed, int64_t first_day, int64_t n_days, int n_stocks, float* stocks, float* market,

@@ -53,10 +53,19 @@ class DeviceBatch:
 
     @staticmethod
     def from_reference(batch, device):
-        """Inverse of to_reference(): accepts the list of four tensors the reference's loaders yield."""
+        """Inverse of to_reference(): accepts the list of four tensors the reference's loaders yield.  On a CUDA device
+        the layout change is one launch of the library's own kernel (b200_collate_reference)."""
         X, y, factor, inv_psi = [t.to(device=device, dtype=torch.float32) for t in batch]
         B, S, T, F = X.shape
         n = y.shape[2]
+        if X.is_cuda and y.shape[3] == 4:
+            X, y = X.contiguous(), y.contiguous()
+            e = lambda *s: torch.empty(*s, dtype=torch.float32, device=X.device)
+            out = DeviceBatch(e(T, B * S, F), e(B * S, n), e(B, n), factor.contiguous(), inv_psi.reshape(B * S).contiguous(), B, S)
+            stream = torch.cuda.current_stream(X.device).cuda_stream
+            check(_lib.load().b200_collate_reference(ptr(X), ptr(y), B, S, T, n, F, ptr(out.x), ptr(out.y_stock), ptr(out.y_market),
+                                                     stream), "b200_collate_reference")
+            return out
         x = X.reshape(B * S, T, F).permute(1, 0, 2).contiguous()
         return DeviceBatch(x, y[..., 0].reshape(B * S, n).contiguous(), y[:, 0, :, 1].contiguous(),
                            factor.contiguous(), inv_psi.reshape(B * S).contiguous(), B, S)

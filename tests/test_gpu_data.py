@@ -115,3 +115,19 @@ def test_datamodule_from_files_and_reconstruction(tmp_path, variants):
     b = next(iter(rec.val_dataloader()))
     X, y, _, _ = [t.cpu() for t in b.to_reference()]
     assert torch.equal(y[0, :, :, 0], X[0, :, 30:, 0])      # the target IS the tail of the look-back
+
+
+@pytest.mark.parametrize("B_,S,T,n,F", [(3, 7, 60, 30, 3), (2, 100, 60, 30, 5), (1, 33, 45, 10, 3)])
+def test_collate_reference_kernel(B_, S, T, n, F):
+    """b200_collate_reference (device layout change of a reference-format batch) against the torch permute it replaces."""
+    g = torch.Generator().manual_seed(B_ * 1000 + S)
+    X, y = torch.randn(B_, S, T, F, generator=g), torch.randn(B_, S, n, 4, generator=g)
+    y[:, :, :, 1] = y[:, :1, :, 1]                      # the market channel is the same for every stock of a window
+    factor, inv_psi = torch.randn(B_, 2, generator=g), torch.rand(B_, S, generator=g)
+    b = B.DeviceBatch.from_reference([X, y, factor, inv_psi], DEV)
+    assert torch.equal(b.x.cpu(), X.reshape(B_ * S, T, F).permute(1, 0, 2).contiguous())
+    assert torch.equal(b.y_stock.cpu(), y[..., 0].reshape(B_ * S, n))
+    assert torch.equal(b.y_market.cpu(), y[:, 0, :, 1])
+    assert torch.equal(b.inv_psi.cpu(), inv_psi.reshape(-1)) and torch.equal(b.factor.cpu(), factor)
+    back = b.to_reference()
+    assert torch.equal(back[0].cpu(), X) and torch.equal(back[1].cpu()[..., :2], y[..., :2])
