@@ -64,6 +64,8 @@ extern "C" {
 
 B200_API int b200_version(void);
 B200_API const char* b200_last_error(void);
+/* hash of the sources and flags this binary was built from (masters-thesis_b200/build.py source_hash) */
+B200_API const char* b200_build_hash(void);
 /* 1 when the LSTM engine `mode` is compiled into this library, else 0 */
 B200_API int b200_mode_available(int mode);
 
@@ -73,6 +75,12 @@ B200_API int b200_mode_available(int mode);
  * "<kernel name> <launches> <total milliseconds>\n". */
 B200_API int b200_timing_enable(int on);
 B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
+
+/* Tuning knobs for experiments (no counterpart in the reference); process-wide, read at launch time, defaults are
+ * the measured best.  The library reads no environment variables.
+ *   "tc_prefetch"  bit mask of L2 prefetches in the tcgen05 kernels (csrc/lstm_tc.cu, default 35)
+ *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM (default 0) */
+B200_API int b200_set_option(const char* name, int value);
 
 /* number of fp32 parameters of the model (src/model.py:88-97): 51,074 for F=3,H=64,L=2 */
 B200_API int64_t b200_param_count(int n_features, int hidden, int layers);
@@ -221,14 +229,21 @@ B200_API int b200_grad_sqnorm(const float* grads, int64_t count, float* sqnorm_o
  * the library (one fp64 slot per 4,096 gradients) instead of caller memory.
  *   - limit: count <= B200_SQNORM_STATIC_MAX (4,194,304 gradients, a 16 MB vector: every model of
  *     configs/model/ including `wide`); larger counts are rejected with B200_ERR_INVALID
- *   - the first call on each device looks up the array's device address; make that first call with
- *     the device current and before starting any stream capture.  Later calls only launch kernels.
+ *   - every call looks up the array's device address for the CURRENT device (so it stays right after a
+ *     cudaDeviceReset); the first call on a device does the one-time set-up behind that lookup: make it
+ *     with the device current and before starting any stream capture.  Later calls only launch kernels.
  *   - nothing needs zeroing between calls (each call overwrites the slots it then reads), but all
  *     calls on a device share the one array: two calls whose kernels can overlap on the GPU
  *     (different streams, no ordering between them) race and return garbage.  Serialise them.
  *   - allocates nothing: no cudaMalloc/cudaFree, no library or torch allocation. */
 #define B200_SQNORM_STATIC_MAX 4194304
 B200_API int b200_grad_sqnorm_static(const float* grads, int64_t count, float* sqnorm_out, void* stream);
+
+/* dst[i] += scale * src[i]: accumulates the gradient of one micro-batch into the step's gradient when a batch is
+ * processed in several forward/backward passes (one optimiser step per datamodule.batch_size windows,
+ * src/data.py:236-238, src/model.py:204-209 -- the reference never splits a batch; this is what lets batches whose
+ * activations exceed device memory keep that one-step-per-batch semantics). */
+B200_API int b200_grad_accumulate(float* dst, const float* src, int64_t count, float scale, void* stream);
 
 /* Replaces the clip scaling + torch.optim.Adam.step (src/model.py:150-154): L2-coupled weight
  * decay, bias correction, eps outside the sqrt(v_hat).  clip_val <= 0 or sqnorm == NULL disables
@@ -237,6 +252,24 @@ B200_API int b200_grad_sqnorm_static(const float* grads, int64_t count, float* s
 B200_API int b200_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t count,
                    float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                    float clip_val, const float* sqnorm, int zero_grad, void* stream);
+
+/* ---------------------------------------------------------------- data-parallel gradient exchange
+ * Replaces the gradient all-reduce of Lightning's implicit DDP (train.py:169: Trainer(strategy='auto') on a multi-GPU box
+ * -> torch DistributedDataParallel -> one ncclAllReduce per gradient bucket).  One process per GPU; NCCL is called from
+ * inside this library (bound at run time, the host framework's libnccl.so.2 when it is already loaded).
+ *   rank 0: b200_dp_unique_id(id_host[128]) -> the caller distributes the 128 bytes to every rank (torchrun's store,
+ *           a file, MPI ...) -> every rank, with ITS device current: b200_dp_init(id, world, rank, &comm)
+ *   per bucket: b200_dp_allreduce(comm, grads + offset, count, comm_stream): in-place fp32 SUM over the ranks, enqueued
+ *           on the given stream (the heads and backward kernels pre-scale gradients by grad_scale = 1/world, so the sum
+ *           is the DDP mean).  Buckets are slices of the flat gradient vector; a slice may be reduced as soon as the
+ *           b200_lstm_bwd_layer call that writes it has been enqueued and the communication stream waits on an event
+ *           recorded after it, so the exchange of the upper layers overlaps the backward kernels of the lower ones.
+ *   b200_dp_destroy(comm) at the end.  Errors: -2000 - ncclResult_t. */
+B200_API int b200_dp_nccl_version(void);                 /* e.g. 22809; 0 when libnccl cannot be loaded */
+B200_API int b200_dp_unique_id(void* id_out_host);       /* 128 bytes */
+B200_API int b200_dp_init(const void* id_host, int world_size, int rank, void** comm_out);
+B200_API int b200_dp_allreduce(void* comm, float* buf, int64_t count, void* stream);
+B200_API int b200_dp_destroy(void* comm);
 
 #ifdef __cplusplus
 }

@@ -7,7 +7,7 @@ CUDA library libb200lstm.so.  The directory name carries a hyphen; import it as
 from . import _lib, data, evaluate
 from ._lib import B200Error, LOSS_KINDS, MODES
 from .config import compose_config
-from .data import DeviceBatch, FinancialLstmDataModule, HostBatchFeeder, SeriesBatchSource
+from .data import ChunkedBatch, DeviceBatch, FinancialLstmDataModule, HostBatchFeeder, SeriesBatchSource
 from .engine import LstmEngine
 from .model import FinancialLstm, FinancialLstmCombined, FinancialLstmMse, FinancialLstmNll, get_model_class
 from .trainer import B200Trainer, LossMailbox

@@ -18,9 +18,11 @@ _p, _i, _l, _f, _u64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint6
 PROTOTYPES = {
     "b200_version": (_i, []),
     "b200_last_error": (C.c_char_p, []),
+    "b200_build_hash": (C.c_char_p, []),
     "b200_mode_available": (_i, [_i]),
     "b200_timing_enable": (_i, [_i]),
     "b200_timing_report": (_i, [C.c_char_p, _sz]),
+    "b200_set_option": (_i, [C.c_char_p, _i]),
     "b200_param_count": (_l, [_i, _i, _i]),
     "b200_param_offset": (_l, [_i, _i, _i, _i]),
     "b200_gen_batch": (_i, [_u64, _p, _l, _l, _i, _i, _i, _l, _i, _p, _p, _p, _p, _p, _p]),
@@ -44,7 +46,13 @@ PROTOTYPES = {
     "b200_sqnorm_workspace_bytes": (_sz, [_l]),
     "b200_grad_sqnorm": (_i, [_p, _l, _p, _p, _sz, _p]),
     "b200_grad_sqnorm_static": (_i, [_p, _l, _p, _p]),
+    "b200_grad_accumulate": (_i, [_p, _p, _l, _f, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _l, _f, _p, _i, _p]),
+    "b200_dp_nccl_version": (_i, []),
+    "b200_dp_unique_id": (_i, [_p]),
+    "b200_dp_init": (_i, [_p, _i, _i, C.POINTER(_p)]),
+    "b200_dp_allreduce": (_i, [_p, _p, _l, _p]),
+    "b200_dp_destroy": (_i, [_p]),
 }
 
 
@@ -68,6 +76,13 @@ def load(path: Path | None = None):
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)       # AttributeError if the symbol is not exported
         fn.restype, fn.argtypes = res, args
+    # a prebuilt binary that does not match the sources next to it must not pass silently
+    from . import build as _build
+    if _build.CSRC.exists():
+        want, got = _build.source_hash(_build._extra_flags()), lib.b200_build_hash().decode()
+        if got != want:
+            raise B200Error(f"{path} was built from other sources (library {got}, tree {want}): "
+                            "run `python masters-thesis_b200/build.py`")
     _lib = lib
     return lib
 

@@ -33,13 +33,37 @@ def _stale(target: Path, deps) -> bool:
     return any(Path(d).stat().st_mtime > t for d in deps)
 
 
+def source_hash(extra_flags=()) -> str:
+    """sha256 over csrc/*, include/b200_lstm.h and the compile flags: compiled into the library (b200_build_hash) so that
+    a stale prebuilt .so is detected by _lib.load() instead of passing silently."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "b200_lstm.h"]:
+        h.update(f.name.encode()); h.update(f.read_bytes())
+    h.update(" ".join(list(NVCC_FLAGS) + list(extra_flags)).encode())
+    return h.hexdigest()[:16]
+
+
+def _extra_flags():
+    flags = []
+    if os.environ.get("B200_TRACE") == "1":
+        flags.append("-DB200_TRACE")
+    flags += os.environ.get("B200_DEFS", "").split()
+    if os.environ.get("B200_ABLATE") == "1":
+        flags.append("-DB200_ABLATE")
+    return flags
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
     flags = list(NVCC_FLAGS)
-    if os.environ.get("B200_TRACE") == "1":          # event tracing of the tcgen05 kernels (tools/trace_*.py); rebuild with --force
-        flags.append("-DB200_TRACE")
-    flags += os.environ.get("B200_DEFS", "").split()      # extra -D switches for timing experiments (rebuild with --force)
-    if os.environ.get("B200_ABLATE") == "1":        # backward-epilogue ablation switches (env B200_TC_DBG); timing experiments only
-        flags.append("-DB200_ABLATE")
+    digest = source_hash(_extra_flags())
+    stamp = OBJ / "source_hash.txt"
+    old = stamp.read_text().split() if stamp.exists() else []
+    flag_sig = "|".join(_extra_flags()) or "-"
+    if not force and (len(old) != 2 or old[1] != flag_sig):
+        force = True                     # B200_TRACE / B200_DEFS / B200_ABLATE switches changed: rebuild every object
+    hash_changed = len(old) != 2 or old[0] != digest
+    flags += _extra_flags()
     srcs = sorted(CSRC.glob("*.cu"))
     hdrs = sorted(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "b200_lstm.h"]
     OBJ.mkdir(exist_ok=True)
@@ -47,8 +71,10 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     jobs = []
     for s in srcs:
         o = OBJ / (s.stem + ".o")
-        if force or _stale(o, [s] + hdrs):
+        if force or _stale(o, [s] + hdrs) or (s.stem == "api" and hash_changed):
             cmd = [nvcc, *flags, "-c", str(s), "-o", str(o)]
+            if s.stem == "api":           # the hash lives in api.cu only, so that one edited file recompiles two, not all
+                cmd.insert(1, f'-DB200_SRC_HASH="{digest}"')
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)
@@ -66,8 +92,9 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     objs = [OBJ / (s.stem + ".o") for s in srcs]
     if force or jobs or _stale(LIB, objs):
         cmd = [nvcc, "-shared", "-o", str(LIB), *map(str, objs), "-gencode", "arch=compute_100a,code=sm_100a",
-               "-Xcompiler", "-fPIC", "-lcudart", "-lcuda"]
+               "-Xcompiler", "-fPIC", "-lcudart", "-lcuda", "-ldl"]
         run(cmd)
+    stamp.write_text(f"{digest} {flag_sig}")
     return LIB
 
 

@@ -37,6 +37,9 @@ def _wrap(obj):
 
 
 def to_container(cfg):
+    if type(cfg).__module__.startswith("omegaconf"):          # a DictConfig composed by Hydra itself
+        from omegaconf import OmegaConf
+        return OmegaConf.to_container(cfg, resolve=True)
     if isinstance(cfg, dict):
         return {k: to_container(v) for k, v in cfg.items()}
     if isinstance(cfg, list):

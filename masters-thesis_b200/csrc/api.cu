@@ -1,6 +1,9 @@
 // C-ABI glue: error reporting, parameter-vector geometry and the LSTM engine dispatch.
 #include <stdarg.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -20,6 +23,9 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 // ---- per-kernel timing registry ---------------------------------------------------------------
+// Process-wide and OFF unless b200_timing_enable(1) was called (bench.py's roofline leg): the only mutable state of the
+// library besides b200_set_option's two tuning values.  A mutex serialises the registry, so concurrent host threads are
+// safe; while it is off, timing_begin/timing_end are one relaxed flag test.
 struct TimingSlot {
     const char* name;
     cudaEvent_t ev[2 * 4096];
@@ -28,11 +34,13 @@ struct TimingSlot {
 };
 static TimingSlot g_slots[32];
 static int g_nslots = 0;
-static bool g_timing = false;
-static TimingSlot* g_open = nullptr;
+static std::atomic<bool> g_timing{false};
+static std::mutex g_timing_mu;
+static thread_local TimingSlot* g_open = nullptr;      // a launch is bracketed by the thread that issues it
 
 void timing_begin(const char* name, cudaStream_t st) {
-    if (!g_timing) return;
+    if (!g_timing.load(std::memory_order_relaxed)) return;
+    std::lock_guard<std::mutex> lock(g_timing_mu);
     TimingSlot* s = nullptr;
     for (int i = 0; i < g_nslots; ++i)
         if (g_slots[i].name == name || strcmp(g_slots[i].name, name) == 0) { s = &g_slots[i]; break; }
@@ -48,7 +56,8 @@ void timing_begin(const char* name, cudaStream_t st) {
 }
 
 void timing_end(cudaStream_t st) {
-    if (!g_timing || !g_open) return;
+    if (!g_open) return;
+    std::lock_guard<std::mutex> lock(g_timing_mu);
     cudaEventRecord(g_open->ev[g_open->used + 1], st);
     g_open->used += 2;
     g_open = nullptr;
@@ -62,6 +71,8 @@ int ffma_bwd_layer(int layer, const float* params, int F, int H, int L, const fl
                    const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
                    int training, void* workspace, size_t ws_bytes, cudaStream_t st);
 bool tc_available();
+void tc_set_prefetch(int mask);
+void wide_set_fuse(int on);
 size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L);
 int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
            float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st);
@@ -80,7 +91,11 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
 
 using namespace b200;
 
-extern "C" int b200_version(void) { return 100; }
+extern "C" int b200_version(void) { return 200; }
+#ifndef B200_SRC_HASH
+#define B200_SRC_HASH "unknown"
+#endif
+extern "C" const char* b200_build_hash(void) { return B200_SRC_HASH; }
 extern "C" const char* b200_last_error(void) { return g_err; }
 extern "C" int b200_mode_available(int mode) {
     if (mode == B200_MODE_FFMA) return 1;
@@ -89,13 +104,23 @@ extern "C" int b200_mode_available(int mode) {
 }
 
 extern "C" int b200_timing_enable(int on) {
-    g_timing = on != 0;
+    std::lock_guard<std::mutex> lock(g_timing_mu);
+    g_timing.store(on != 0);
     if (on) for (int i = 0; i < g_nslots; ++i) g_slots[i].used = 0;
     return B200_OK;
 }
 
+extern "C" int b200_set_option(const char* name, int value) {
+    B200_CHECK_ARG(name != nullptr, "set_option: null name");
+    if (strcmp(name, "tc_prefetch") == 0) { tc_set_prefetch(value); return B200_OK; }
+    if (strcmp(name, "wide_fuse") == 0) { wide_set_fuse(value); return B200_OK; }
+    set_error("set_option: unknown option '%s' (known: tc_prefetch, wide_fuse)", name);
+    return B200_ERR_INVALID;
+}
+
 extern "C" int b200_timing_report(char* buf, size_t buf_bytes) {
     B200_CHECK_ARG(buf && buf_bytes > 0, "timing_report: null buffer");
+    std::lock_guard<std::mutex> lock(g_timing_mu);
     size_t off = 0;
     buf[0] = 0;
     for (int i = 0; i < g_nslots; ++i) {

@@ -36,8 +36,10 @@ using namespace tc;
 // kernel; in the layer > 0 backward kernel (whose epilogue warps stage the image themselves, loads issued a wait ahead)
 // each of bits 4, 8, 16 COST 0.9-1.0 ms (20.1 -> 21.1 ms) when issued at the step boundary and are neutral when issued after
 // the second quarter of the step (as they are now); bit 32 is neutral; bit 1 is worth < 0.1 ms.
+// The mask is a kernel argument; b200_set_option("tc_prefetch", mask) changes it for later launches of this process.
 constexpr int PF_DEFAULT = 1 | 2 | 32;
-__constant__ int c_tc_prefetch = PF_DEFAULT;
+static int g_tc_prefetch = PF_DEFAULT;
+void tc_set_prefetch(int mask) { g_tc_prefetch = mask; }
 #ifdef B200_ABLATE                    // timing experiments only (build with B200_ABLATE=1): env B200_TC_DBG is a bit mask of backward
 __constant__ int c_tc_dbg = 0;        // epilogue pieces to skip (1 bias butterfly, 2 math, 4 operand stores, 8 loads, 16 proxy fence);
 #define TC_DBG() c_tc_dbg             // results are wrong when set.  Compiled out otherwise: the run-time test alone costs 2 ms.
@@ -139,9 +141,18 @@ tc_pack_weights_kernel(const float* __restrict__ w_ih, const float* __restrict__
 // Inter-layer dropout keep bits: bit u of bits[t * N + row] = keep(unit u) for the input of one layer; built once
 // per step by tc_dropout_bits_kernel (same Philox blocks as b200_dropout_mask) so that the loaders and the dx
 // epilogue read 8 bytes per (row, step) instead of re-running Philox.
+// The keep bits of a layer are followed by a 32-byte tag {seed, layer, N, T << 32 | threshold}: the backward kernel reads the
+// bits the forward pass left in the workspace instead of regenerating them, and checks the tag against its own
+// arguments so that a foreign, reused or differently sized workspace aborts the launch instead of silently
+// producing gradients for other masks.
+__host__ __device__ inline uint64_t drop_tag3(int T, uint32_t thr) { return ((uint64_t)(uint32_t)T << 32) | thr; }
 __global__ void __launch_bounds__(256)
 tc_dropout_bits_kernel(uint64_t seed, int layer, int64_t N, int T, uint32_t thr, uint64_t* __restrict__ bits) {
     const int64_t total = (int64_t)T * N;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        uint64_t* tag = bits + total;
+        tag[0] = seed; tag[1] = (uint64_t)layer; tag[2] = (uint64_t)N; tag[3] = drop_tag3(T, thr);
+    }
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t row = i % N;
         const int t = (int)(i / N);
@@ -242,7 +253,7 @@ struct FwdSmem {
 template <int NSPLIT, int NTILE, bool LAYER0, int EH>
 __global__ void __launch_bounds__(32 * (4 * NTILE * EH + LOADER_WARPS + 1), 1)
 lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
-                   float* __restrict__ h_out, float* __restrict__ c_out, const uint64_t* __restrict__ drop_bits, float p) {
+                   float* __restrict__ h_out, float* __restrict__ c_out, const uint64_t* __restrict__ drop_bits, float p, int pf_mask) {
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     constexpr int KX = S::KX;
     constexpr int EPI_WARPS = 4 * NTILE * EH;
@@ -404,7 +415,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const bool tracer = lw == 0 && lane == 0;
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             for (int t = 0; t < T; ++t, ++g) {
-                if ((c_tc_prefetch & 1) && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
+                if ((pf_mask & 1) && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
                     // next step's input rows of both slots -> L2 (the tiles of a group are consecutive)
                     const int64_t r0 = grp * NTILE * TM;
                     if (r0 < N) {
@@ -694,8 +705,17 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
 lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
                    const float* __restrict__ h_st, const float* __restrict__ c_st, const float* __restrict__ d_out,
                    const float* __restrict__ dhT, float* __restrict__ d_in, float* __restrict__ wpart,
-                   float* __restrict__ bpart, const uint64_t* __restrict__ drop_bits, float p) {
+                   float* __restrict__ bpart, const uint64_t* __restrict__ drop_bits, float p, uint64_t drop_seed, int drop_layer,
+                   uint32_t drop_thr, int pf_mask) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
+    if (drop_bits != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+        const uint64_t* tag = drop_bits + (int64_t)T * N;
+        if (tag[0] != drop_seed || tag[1] != (uint64_t)drop_layer || tag[2] != (uint64_t)N || tag[3] != drop_tag3(T, drop_thr)) {
+            printf("lstm_tc_bwd_kernel: the dropout keep bits in the workspace were not written by the forward pass of this step "
+                   "(seed/layer/size mismatch); pass the SAME workspace, untouched, to b200_lstm_fwd and b200_lstm_bwd_layer\n");
+            __trap();
+        }
+    }
     constexpr int KX = S::KX, KC = S::KC;
     // da quarter images: with two buffers (DB == 2) both quarters of a pair live in ONE [128 x 128] image (buffer b = column block
     // b), so that the weight gradient of the pair is a single N = 128 MMA per product and k-step; hi and lo images follow each other
@@ -1024,7 +1044,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             const int64_t rows_live = N - r0;
             for (int t = T - 1; t >= 0; --t, ++g) {
                 if (tracer) trace_ev(1, 0, 0, g, ntr);
-                const int pf = c_tc_prefetch;
+                const int pf = pf_mask;
                 if (EPI_LOADS && (pf & 28) && lw == 0 && lane == 0) {
                     // time the prefetch into the middle of the step (after its second quarter): at the step boundary the epilogue
                     // warps' image loads are on the critical path and a 128 KB L2 fill in front of them costs more than it saves
@@ -1322,13 +1342,8 @@ size_t ffma_workspace_bytes(int64_t N, int T, int L);
 bool tc_available() { return true; }
 
 static void tc_apply_env() {
-    static bool done = false;
-    if (done) return;
-    done = true;
-    const char* e = getenv("B200_TC_PREFETCH");
-    if (e) { int v = atoi(e); cudaMemcpyToSymbol(c_tc_prefetch, &v, sizeof(int)); }
-#ifdef B200_ABLATE
-    e = getenv("B200_TC_DBG");
+#ifdef B200_ABLATE          // ablation builds only (timing experiments, results are wrong by design): env B200_TC_DBG, every call, current device
+    const char* e = getenv("B200_TC_DBG");
     if (e) { int v = atoi(e); cudaMemcpyToSymbol(c_tc_dbg, &v, sizeof(int)); }
 #endif
 }
@@ -1344,7 +1359,7 @@ static size_t tc_fwd_pack_total(int L) {
     for (int l = 0; l < L; ++l) tot += (pack_bytes(l == 0) + 255) & ~(size_t)255;
     return tot;
 }
-static size_t tc_bits_bytes(int64_t N, int T) { return ((size_t)T * N * 8 + 255) & ~(size_t)255; }
+static size_t tc_bits_bytes(int64_t N, int T) { return (((size_t)T * N * 8 + 255) & ~(size_t)255) + 256; }   // + tag
 // tail of the workspace: dropout keep bits of layers 1..L-1, forward packs, one backward pack
 static size_t tc_tail_total(int64_t N, int T, int L) {
     return (size_t)(L - 1) * tc_bits_bytes(N, T) + tc_fwd_pack_total(L) + ((bwd_pack_bytes(false) + 255) & ~(size_t)255);
@@ -1384,7 +1399,7 @@ static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t 
     const int threads = 32 * (4 * NTILE * EH + LOADER_WARPS + 1);
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_fwd_kernel_l0" : "lstm_tc_fwd_kernel_lN", st);
-        kern<<<grid, threads, S::total, st>>>(packed, xin, kin, N, T, h_out, c_out, drop_bits, p);
+        kern<<<grid, threads, S::total, st>>>(packed, xin, kin, N, T, h_out, c_out, drop_bits, p, g_tc_prefetch);
     }
     B200_LAUNCH_CHECK("lstm_tc_fwd_kernel");
     return B200_OK;
@@ -1437,13 +1452,14 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
 template <int NSPLIT, bool LAYER0, int XB, int DB>
 static int launch_bwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, const float* h_st, const float* c_st,
                       const float* d_out, const float* dhT, float* d_in, float* wpart, float* bpart, const uint64_t* drop_bits,
-                      float p, int grid, cudaStream_t st) {
+                      float p, uint64_t seed, int layer, int grid, cudaStream_t st) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     auto kern = lstm_tc_bwd_kernel<NSPLIT, LAYER0, XB, DB>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_bwd_kernel_l0" : "lstm_tc_bwd_kernel_lN", st);
-        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, drop_bits, p);
+        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, drop_bits, p, seed, layer,
+                                                 dropout_threshold(p), g_tc_prefetch);
     }
     B200_LAUNCH_CHECK("lstm_tc_bwd_kernel");
     return B200_OK;
@@ -1480,15 +1496,15 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     const int64_t ntiles = (N + TM - 1) / TM;
     const int grid = (int)(ntiles < nsplit ? ntiles : nsplit);
     const bool precise = mode == B200_MODE_TC_PRECISE;
-    // keep bits of this layer's input were built by the forward pass of the same step (same workspace)
+    // keep bits of this layer's input were built by the forward pass of the same step (same workspace); the kernel checks
+    // the tag behind them against (seed, layer, N, T, p) and aborts on a mismatch
     const uint64_t* bits = (!layer0 && drop) ? tail.bits + (size_t)(layer - 1) * (tc_bits_bytes(N, T) / 8) : nullptr;
-    (void)seed;
     if (layer0)
-        rc = precise ? launch_bwd<2, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, grid, st)
-                     : launch_bwd<1, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, grid, st);
+        rc = precise ? launch_bwd<2, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, st)
+                     : launch_bwd<1, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, st);
     else
-        rc = precise ? launch_bwd<2, false, 1, 1>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, grid, st)
-                     : launch_bwd<1, false, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, grid, st);
+        rc = precise ? launch_bwd<2, false, 1, 1>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, st)
+                     : launch_bwd<1, false, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, st);
     if (rc) return rc;
     float* gbase = grads + b200_param_offset(F, TH, L, layer);
     float* gw_ih = gbase;

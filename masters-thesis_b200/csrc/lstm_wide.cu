@@ -608,6 +608,9 @@ size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L) {
            4 * wide_pack_region(H) + 256;
 }
 
+static int g_wide_fuse = 0;
+void wide_set_fuse(int on) { g_wide_fuse = on; }
+
 static int wide_check(const char* who, int H, int F) {
     B200_CHECK_ARG(H % 64 == 0 && H >= 128, "%s: the wide engine needs a hidden size that is a multiple of 64 and >= 128, got %d", who, H);
     B200_CHECK_ARG(F <= CS_MAXF, "%s: at most %d input features", who, CS_MAXF);
@@ -624,11 +627,10 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
     const int nsplit = mode == B200_MODE_TC_PRECISE ? 2 : 1;
     const bool drop = training && p > 0.f;
     const int64_t lsz = (int64_t)T * N * H, NH = N * H, G4 = 4LL * H;
-    // B200_WIDE_FUSE=1: LSTM cell in the epilogue of the recurrent GEMM.  Measured (hidden 256 x 8 layers, 256 windows): no gain in
+    // option wide_fuse = 1: LSTM cell in the epilogue of the recurrent GEMM.  Measured (hidden 256 x 8 layers, 256 windows): no gain in
     // bf16 mode (85 ms against 47 + 38 ms for GEMM + cell kernel) and slower with three products (125 against 102 ms): the
     // thread-per-row epilogue runs after the MMAs of its CTA instead of beside another kernel's, so it stays off by default.
-    const char* fe = getenv("B200_WIDE_FUSE");
-    const bool fuse = fe && atoi(fe) == 1;
+    const bool fuse = g_wide_fuse != 0;      // b200_set_option("wide_fuse", 1)
     for (int l = 0; l < L; ++l) {
         const LayerParams lp = layer_params(params, F, H, l);
         float* G = w.G + (int64_t)l * lsz * 4;

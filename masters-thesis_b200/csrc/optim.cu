@@ -100,7 +100,16 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
 // B200_SQNORM_STATIC_MAX gradients.  Lives in every CUDA context that loads the library until exit (8 KB).
 // In host code this name is only a handle; the device address comes from cudaGetSymbolAddress.
 static __device__ __align__(256) double g_sqnorm_static_scratch[SQ_MAX_BLOCKS];
-static double* g_sqnorm_static_ptr[64] = {nullptr};    // per-device address of the array above
+
+static_assert((int64_t)B200_SQNORM_STATIC_MAX == (int64_t)SQ_MAX_BLOCKS * SQ_THREADS * 16,
+              "B200_SQNORM_STATIC_MAX (header) must equal the gradients covered by SQ_MAX_BLOCKS scratch slots");
+
+// dst += scale * src (micro-batch gradient accumulation; 8 B read + 4 B written per element)
+__global__ void __launch_bounds__(256)
+grad_accumulate_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t count, float scale) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = fmaf(scale, src[i], dst[i]);
+}
 
 static int sq_blocks(int64_t count) {
     int64_t b = (count / 4 + SQ_THREADS * 4 - 1) / (SQ_THREADS * 4);
@@ -151,6 +160,16 @@ extern "C" int b200_adam_step(float* params, float* grads, float* exp_avg, float
     return B200_OK;
 }
 
+extern "C" int b200_grad_accumulate(float* dst, const float* src, int64_t count, float scale, void* stream) {
+    B200_CHECK_ARG(count > 0 && dst && src, "grad_accumulate: bad arguments");
+    int64_t nb = (count + 255) / 256;
+    const int64_t cap = (int64_t)num_sms() * 8;
+    if (nb > cap) nb = cap;
+    { TimedLaunch _t("grad_accumulate_kernel", (cudaStream_t)stream); grad_accumulate_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(dst, src, count, scale); }
+    B200_LAUNCH_CHECK("grad_accumulate_kernel");
+    return B200_OK;
+}
+
 // Allocation-free variant of b200_grad_sqnorm (see include/b200_lstm.h).
 extern "C" int b200_grad_sqnorm_static(const float* grads, int64_t count, float* sqnorm_out, void* stream) {
     B200_CHECK_ARG(count > 0 && grads && sqnorm_out, "grad_sqnorm_static: bad arguments");
@@ -158,16 +177,11 @@ extern "C" int b200_grad_sqnorm_static(const float* grads, int64_t count, float*
                    "grad_sqnorm_static: %lld gradients exceed the built-in scratch (max %lld); use b200_grad_sqnorm with a caller workspace",
                    (long long)count, (long long)B200_SQNORM_STATIC_MAX);
     B200_CHECK_ARG(((uintptr_t)grads & 15) == 0, "grad_sqnorm_static: grads must be 16-byte aligned");
-    int dev = 0;
-    B200_CUDA(cudaGetDevice(&dev));
-    B200_CHECK_ARG(dev >= 0 && dev < 64, "grad_sqnorm_static: device ordinal %d out of range", dev);
-    if (g_sqnorm_static_ptr[dev] == nullptr) {
-        // one-time set-up for this device (it is the current device): resolve the array's device address
-        double* p = nullptr;
-        B200_CUDA(cudaGetSymbolAddress((void**)&p, g_sqnorm_static_scratch));
-        g_sqnorm_static_ptr[dev] = p;
-    }
-    double* scratch = g_sqnorm_static_ptr[dev];
+    // The array's device address is looked up on every call (the device is current): after the first call on a device
+    // this is a table lookup inside the runtime, and it stays correct across cudaDeviceReset / context re-creation,
+    // which a cached pointer would not.  The first call per device loads the module: make it before any stream capture.
+    double* scratch = nullptr;
+    B200_CUDA(cudaGetSymbolAddress((void**)&scratch, g_sqnorm_static_scratch));
     const int nb = sq_blocks(count);       // <= SQ_MAX_BLOCKS; every slot read below is written first, nothing to clear
     { TimedLaunch _t("sqnorm_partial_kernel", (cudaStream_t)stream); sqnorm_partial_kernel<<<nb, SQ_THREADS, 0, (cudaStream_t)stream>>>(grads, count, scratch); }
     B200_LAUNCH_CHECK("sqnorm_partial_kernel");

@@ -71,6 +71,32 @@ class DeviceBatch:
                            factor.contiguous(), inv_psi.reshape(B * S).contiguous(), B, S)
 
 
+class ChunkedBatch:
+    """One optimiser step's local batch as micro-batches: the activation stash of a whole batch can exceed device memory
+    (25 GB per 4096 windows for the small model), so the LSTM runs micro-batch by micro-batch while the step keeps the
+    reference's semantics -- one loss, one clip, one Adam update per `datamodule.batch_size` windows
+    (src/data.py:236-238, src/model.py:204-209).  The targets of the WHOLE batch live in one set of tensors (the joint
+    NLL of src/model.py:237-247 couples every row of the batch); each chunk's y_stock / y_market / factor / inv_psi
+    are views into them, x is per chunk (time-major, so a row range of it is not contiguous)."""
+
+    def __init__(self, chunks, y_stock, y_market, factor, inv_psi, n_stocks):
+        self.chunks = chunks
+        self.y_stock, self.y_market, self.factor, self.inv_psi = y_stock, y_market, factor, inv_psi
+        self.n_windows = sum(c.n_windows for c in chunks)
+        self.n_stocks = n_stocks
+
+    @staticmethod
+    def split(batch: "DeviceBatch", micro: int):
+        """Micro-batches of an existing DeviceBatch (copies the x rows of each chunk; targets are views)."""
+        B, S = batch.n_windows, batch.n_stocks
+        chunks = []
+        for lo in range(0, B, micro):
+            hi = min(B, lo + micro)
+            chunks.append(DeviceBatch(batch.x[:, lo * S:hi * S].contiguous(), batch.y_stock[lo * S:hi * S], batch.y_market[lo:hi],
+                                      batch.factor[lo:hi], batch.inv_psi[lo * S:hi * S], hi - lo, S))
+        return ChunkedBatch(chunks, batch.y_stock, batch.y_market, batch.factor, batch.inv_psi, S)
+
+
 class DeviceBatchSource:
     """Allocates (and reuses) the output tensors of b200_gen_batch."""
 
@@ -88,17 +114,44 @@ class DeviceBatchSource:
             self._bufs[B] = DeviceBatch(e(self.T, N, self.F), e(N, self.n), e(B, self.n), e(B, 2), e(N), B, self.S)
         return self._bufs[B]
 
-    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None, checked=False) -> DeviceBatch:
+    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None, checked=False, micro=None):
+        """One batch; with `micro` (windows) smaller than the batch, a ChunkedBatch of micro-batches."""
         if window_idx is not None:
             window_idx = window_idx.to(self.device, torch.int64).contiguous()
             n_windows = window_idx.numel()
-        b = out if out is not None else self._alloc(int(n_windows))
-        stream = torch.cuda.current_stream(self.device).cuda_stream
-        check(self.lib.b200_gen_batch(self.seed, ptr(window_idx), int(first_window), int(n_windows), self.S, self.T, self.n,
-                                      self.stride, self.F, ptr(b.x), ptr(b.y_stock), ptr(b.y_market), ptr(b.factor),
-                                      ptr(b.inv_psi), stream), "b200_gen_batch")
-        self.launches += 1
+        n_windows = int(n_windows)
+        if micro and n_windows > int(micro):
+            return self._generate_chunked(window_idx, int(first_window), n_windows, int(micro))
+        b = out if out is not None else self._alloc(n_windows)
+        self._launch(window_idx, int(first_window), n_windows, b.x, b.y_stock, b.y_market, b.factor, b.inv_psi)
         return b
+
+    def _launch(self, window_idx, first_window, n_windows, x, y_stock, y_market, factor, inv_psi):
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self.lib.b200_gen_batch(self.seed, ptr(window_idx), first_window, n_windows, self.S, self.T, self.n,
+                                      self.stride, self.F, ptr(x), ptr(y_stock), ptr(y_market), ptr(factor),
+                                      ptr(inv_psi), stream), "b200_gen_batch")
+        self.launches += 1
+
+    def _generate_chunked(self, window_idx, first_window, n_windows, micro):
+        key = ("chunked", n_windows, micro)
+        if key not in self._bufs:
+            N, d = n_windows * self.S, self.device
+            e = lambda *s: torch.empty(*s, dtype=torch.float32, device=d)
+            ys, ym, fa, ip = e(N, self.n), e(n_windows, self.n), e(n_windows, 2), e(N)
+            chunks = []
+            for lo in range(0, n_windows, micro):
+                hi = min(n_windows, lo + micro)
+                chunks.append(DeviceBatch(e(self.T, (hi - lo) * self.S, self.F), ys[lo * self.S:hi * self.S], ym[lo:hi], fa[lo:hi],
+                                          ip[lo * self.S:hi * self.S], hi - lo, self.S))
+            self._bufs[key] = ChunkedBatch(chunks, ys, ym, fa, ip, self.S)
+        cb = self._bufs[key]
+        lo = 0
+        for c in cb.chunks:
+            idx = None if window_idx is None else window_idx[lo:lo + c.n_windows]
+            self._launch(idx, first_window + lo, c.n_windows, c.x, c.y_stock, c.y_market, c.factor, c.inv_psi)
+            lo += c.n_windows
+        return cb
 
     def coefficients(self):
         a = torch.empty(self.S, dtype=torch.float32, device=self.device)
@@ -140,7 +193,7 @@ class SeriesBatchSource:
             self._bufs[B] = DeviceBatch(e(self.T, N, self.F), e(N, self.n), e(B, self.n), e(B, 2), e(N), B, self.S, e(N), e(N))
         return self._bufs[B]
 
-    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None, checked=False) -> DeviceBatch:
+    def generate(self, window_idx=None, first_window=0, n_windows=None, out=None, checked=False, micro=None):
         if window_idx is not None:
             window_idx = window_idx.to(torch.int64)
             if not checked and window_idx.numel() and (int(window_idx.min()) < 0 or int(window_idx.max()) >= self.n_windows):
@@ -154,6 +207,8 @@ class SeriesBatchSource:
                                          ptr(b.x), ptr(b.y_stock), ptr(b.y_market), ptr(b.factor), ptr(b.inv_psi),
                                          ptr(b.ols_alpha), ptr(b.ols_beta), stream), "b200_series_batch")
         self.launches += 1
+        if micro and int(n_windows) > int(micro):
+            return ChunkedBatch.split(b, int(micro))
         return b
 
     def coefficients(self):
@@ -234,45 +289,62 @@ class HostBatchFeeder:
         yield self._finish(nxt)
 
 
-class _Loader:
-    """Iterable of DeviceBatch over a window range; mirrors DataLoader(batch_size, shuffle)."""
+def rank_share(order, rank, world):
+    """The windows of one epoch that rank `rank` of `world` sees: what torch's DistributedSampler (which Lightning
+    installs under DDP, train.py:169) does to the epoch's order -- pad by wrapping around to a multiple of the world
+    size, then every world-th index starting at the rank.  world == 1 returns the order unchanged."""
+    if world <= 1:
+        return order
+    n = order.numel()
+    total = (n + world - 1) // world * world
+    if total > n:
+        order = torch.cat([order, order[: total - n]])
+    return order[rank:total:world]
 
-    def __init__(self, source, lo, hi, batch_size, shuffle, generator=None, rank=0, world=1, drop_uneven=False):
+
+class _Loader:
+    """Iterable of DeviceBatch over a window range; mirrors DataLoader(batch_size, shuffle).  Under data parallelism
+    `batch_size` is PER RANK, as with Lightning DDP on the reference (global batch = world x batch_size): every rank
+    shuffles with the same generator and takes its DistributedSampler share (rank_share) of the epoch."""
+
+    def __init__(self, source, lo, hi, batch_size, shuffle, generator=None, rank=0, world=1, micro=None):
         self.source, self.lo, self.hi, self.bs = source, lo, hi, int(batch_size)
-        self.shuffle, self.gen, self.rank, self.world = shuffle, generator, rank, world
+        self.shuffle, self.gen, self.rank, self.world, self.micro = shuffle, generator, rank, max(1, world), micro
+        if self.bs < 1:
+            raise ValueError(f"batch_size must be >= 1, got {batch_size}")
+
+    def _per_rank(self):
+        return (self.hi - self.lo + self.world - 1) // self.world
 
     def __len__(self):
-        return (self.hi - self.lo + self.bs - 1) // self.bs
+        return (self._per_rank() + self.bs - 1) // self.bs
 
     def __iter__(self):
         n = self.hi - self.lo
         order = torch.randperm(n, generator=self.gen) if self.shuffle else torch.arange(n)
+        order = rank_share(order + self.lo, self.rank, self.world)
         # the epoch's order goes to the device ONCE (a per-batch upload of the indices is a blocking copy that makes the host
         # wait for the previous step: 2.2 of 2.4 ms per step at batch_size 1); batches are slices of it
-        order = (order + self.lo).to(self.source.device)
-        for i in range(0, n, self.bs):
-            idx = order[i:i + self.bs]
-            if self.world > 1:                        # each rank takes its contiguous share of the global batch
-                per = idx.numel() // self.world
-                if per == 0:
-                    continue
-                idx = idx[self.rank * per:(self.rank + 1) * per]
-            yield self.source.generate(window_idx=idx, checked=True)     # lo..hi lie inside the series by construction
+        order = order.to(self.source.device)
+        for i in range(0, order.numel(), self.bs):
+            # lo..hi lie inside the series by construction
+            yield self.source.generate(window_idx=order[i:i + self.bs], checked=True, micro=self.micro)
 
 
 class _StreamLoader:
-    """Endless fresh windows: batch k of rank r = windows first + k*B + [r*B/W, (r+1)*B/W)."""
+    """Endless fresh windows, `batch_size` per rank: step k of rank r = windows first + (k*W + r)*B .. +B."""
 
-    def __init__(self, source, first, batch_size, steps, rank=0, world=1):
-        self.source, self.first, self.bs, self.steps, self.rank, self.world = source, first, int(batch_size), steps, rank, world
+    def __init__(self, source, first, batch_size, steps, rank=0, world=1, micro=None):
+        self.source, self.first, self.bs, self.steps = source, first, int(batch_size), steps
+        self.rank, self.world, self.micro = rank, max(1, world), micro
 
     def __len__(self):
         return self.steps
 
     def __iter__(self):
-        per = self.bs // self.world
         for k in range(self.steps):
-            yield self.source.generate(first_window=self.first + k * self.bs + self.rank * per, n_windows=per)
+            yield self.source.generate(first_window=self.first + (k * self.world + self.rank) * self.bs, n_windows=self.bs,
+                                       micro=self.micro)
 
 
 class FinancialLstmDataModule:
@@ -286,7 +358,7 @@ class FinancialLstmDataModule:
                  stride: int = 80, prediction_task: bool = True, interaction_only: bool = True, batch_size: int = 1,
                  *, seed: int = 1234, n_stocks: int = 100, n_samples: int = 1_000_000, device="cuda:0",
                  streaming: bool = False, steps_per_epoch: int | None = None, rank: int = 0, world_size: int = 1,
-                 use_files: bool | None = None):
+                 use_files: bool | None = None, micro_batch_windows: int | None = None):
         if not prediction_task and target_window > lookback_window:
             raise ValueError('target window must be <= lookback window for reconstruction task')
         self.data_dir = Path(data_dir)
@@ -296,6 +368,7 @@ class FinancialLstmDataModule:
         self.device, self.streaming, self.steps_per_epoch = device, streaming, steps_per_epoch
         self.rank, self.world_size = rank, world_size
         self.use_files = use_files
+        self.micro_batch_windows = micro_batch_windows      # set by the trainer from the device's free memory when None
         self.n_features = 3 if interaction_only else 5
         self.source = None
         self.source_kind = None
@@ -357,10 +430,11 @@ class FinancialLstmDataModule:
         if self.streaming:
             if self.source_kind != "generator":
                 raise ValueError("streaming=True needs the generator source (a finite series has no fresh windows)")
-            steps = self.steps_per_epoch or max(1, self.train_end // max(1, bs))
+            steps = self.steps_per_epoch or max(1, self.train_end // max(1, bs * max(1, self.world_size)))
             # stream from beyond the test split so that evaluation windows are never trained on
-            return _StreamLoader(self.source, self.n_windows, bs, steps, self.rank, self.world_size)
-        return _Loader(self.source, 0, self.train_end, bs, True, self._shuffle_gen, self.rank, self.world_size)
+            return _StreamLoader(self.source, self.n_windows, bs, steps, self.rank, self.world_size, self.micro_batch_windows)
+        return _Loader(self.source, 0, self.train_end, bs, True, self._shuffle_gen, self.rank, self.world_size,
+                       self.micro_batch_windows)
 
     def val_dataloader(self, batch_size=1):
         return _Loader(self.source, self.train_end, self.val_end, batch_size, False)

@@ -22,6 +22,11 @@ class LstmEngine:
         self.F, self.H, self.L, self.p = int(n_features), int(hidden), int(layers), float(dropout)
         self.T, self.n, self.S = int(lookback), int(target), int(n_stocks)
         self.mode = MODES[mode] if isinstance(mode, str) else int(mode)
+        # hidden sizes every kernel on the path supports: 64 (persistent engines, all modes) and 128 / 256 (wide tcgen05
+        # engine x heads kernels); checked here so that an unsupported width fails before any launch, not mid-step
+        if not (self.H == 64 or (self.H in (128, 256) and self.mode != MODES["ffma"])):
+            raise _lib.B200Error(f"hidden_size={self.H} is not supported with engine mode {mode}: the fp32 CUDA-core engine "
+                                 "runs hidden 64 only, the tcgen05 engines hidden 64, 128 and 256")
         self.device = torch.device(device)
         self.P = int(self.lib.b200_param_count(self.F, self.H, self.L))
         self.head_off = int(self.lib.b200_param_offset(self.F, self.H, self.L, self.L))
@@ -82,33 +87,43 @@ class LstmEngine:
         off = ((self.L - 1) * self.T + (self.T - 1)) * N * self.H
         return self.stash_h[off: off + N * self.H]
 
-    def heads(self, batch, kind="mse", mse_weight=100.0, windows_per_group=None, grad_scale=1.0, want_grad=True):
-        """Heads + objective (+ gradients into dhT and the head slice of grads).  losses -> self.losses."""
+    def heads(self, batch, kind="mse", mse_weight=100.0, windows_per_group=None, grad_scale=1.0, want_grad=True,
+              hT=None, dhT=None, head_grads=None, alpha=None, beta=None, heads_ws=None):
+        """Heads + objective (+ gradients into dhT and the head slice of grads).  losses -> self.losses.
+        `batch` supplies the targets (a DeviceBatch or a ChunkedBatch: its whole-batch tensors); the keyword buffers
+        default to the engine's per-micro-batch ones."""
         B = batch.n_windows
         wpg = B if windows_per_group is None else int(windows_per_group)
         k = LOSS_KINDS[kind] if isinstance(kind, str) else int(kind)
-        hT = self.final_hidden(B)
+        hT = self.final_hidden(B) if hT is None else hT
         head_params = self.params[self.head_off:]
-        head_grads = self.grads[self.head_off:]
+        head_grads = self.grads[self.head_off:] if head_grads is None else head_grads
+        dhT = self.dhT if dhT is None else dhT
+        alpha, beta = (self.alpha if alpha is None else alpha), (self.beta if beta is None else beta)
+        ws = self.heads_ws if heads_ws is None else heads_ws
         check(self.lib.b200_heads_loss_fwd_bwd(
             k, float(mse_weight), ptr(head_params), self.H, ptr(hT), ptr(batch.y_stock), ptr(batch.y_market),
             ptr(batch.factor), ptr(batch.inv_psi), B, self.S, self.n, wpg, float(grad_scale),
-            ptr(self.alpha), ptr(self.beta), ptr(self.losses), ptr(self.dhT) if want_grad else None,
-            ptr(head_grads) if want_grad else None, ptr(self.heads_ws), self.heads_ws.numel(), self.stream),
+            ptr(alpha), ptr(beta), ptr(self.losses), ptr(dhT) if want_grad else None,
+            ptr(head_grads) if want_grad else None, ptr(ws), ws.numel(), self.stream),
             "b200_heads_loss_fwd_bwd")
         self.launches += 5 if want_grad else 3
         return self.losses
 
-    def backward(self, batch, training=True, dropout_seed=0, on_layer_done=None):
-        """BPTT, top layer first; on_layer_done(layer) is called after each layer's launches are queued
-        (the data-parallel trainer hooks its bucket all-reduce here)."""
+    def backward_layer(self, batch, layer, training=True, dropout_seed=0, dhT=None, grads=None):
         N = batch.n_windows * self.S
+        dhT = self.dhT if dhT is None else dhT
+        grads = self.grads if grads is None else grads
+        check(self.lib.b200_lstm_bwd_layer(self.mode, layer, ptr(self.params), self.F, self.H, self.L, ptr(batch.x), N,
+                                           self.T, ptr(self.stash_h), ptr(self.stash_c), ptr(dhT), ptr(grads),
+                                           self.p, int(dropout_seed), int(bool(training)), ptr(self.lstm_ws),
+                                           self.lstm_ws.numel(), self.stream), "b200_lstm_bwd_layer")
+        self.launches += 3
+
+    def backward(self, batch, training=True, dropout_seed=0, on_layer_done=None):
+        """BPTT, top layer first; on_layer_done(layer) is called after each layer's launches are queued."""
         for layer in range(self.L - 1, -1, -1):
-            check(self.lib.b200_lstm_bwd_layer(self.mode, layer, ptr(self.params), self.F, self.H, self.L, ptr(batch.x), N,
-                                               self.T, ptr(self.stash_h), ptr(self.stash_c), ptr(self.dhT), ptr(self.grads),
-                                               self.p, int(dropout_seed), int(bool(training)), ptr(self.lstm_ws),
-                                               self.lstm_ws.numel(), self.stream), "b200_lstm_bwd_layer")
-            self.launches += 3
+            self.backward_layer(batch, layer, training, dropout_seed)
             if on_layer_done is not None:
                 on_layer_done(layer)
 
@@ -117,6 +132,110 @@ class LstmEngine:
         lo = int(self.lib.b200_param_offset(self.F, self.H, self.L, layer))
         hi = self.P if layer == self.L else int(self.lib.b200_param_offset(self.F, self.H, self.L, layer + 1))
         return lo, hi - lo
+
+    def _accumulate(self, dst, src, count, scale=1.0):
+        check(self.lib.b200_grad_accumulate(ptr(dst), ptr(src), int(count), float(scale), self.stream), "b200_grad_accumulate")
+        self.launches += 1
+
+    @staticmethod
+    def chunk_seed(dropout_seed, chunk):
+        """Dropout seed of micro-batch `chunk` of a step (the keep mask is a function of seed and row-in-launch, so every
+        micro-batch needs its own stream of masks); chunk 0 keeps the step's seed."""
+        return (int(dropout_seed) + 0x9E3779B97F4A7C15 * int(chunk)) & 0xFFFFFFFFFFFFFFFF
+
+    def forward_backward(self, batch, kind, mse_weight=100.0, dropout_seed=0, grad_scale=1.0, on_slice_ready=None):
+        """Loss and gradient of ONE optimiser step's local batch: self.grads <- grad_scale * d loss / d params, returns the
+        device tensor [mse, nll, total, mae].  on_slice_ready(offset, length, last) is called as soon as every kernel
+        writing a slice of self.grads is queued (heads first, then layers top-down): the data-parallel trainer hooks
+        its bucket all-reduce there.
+
+        A ChunkedBatch runs micro-batch by micro-batch (see data.ChunkedBatch):
+          * mse is a mean over rows, so each micro-batch contributes its own loss and gradient with weight
+            windows_in_chunk / windows_in_batch -- exact up to fp32 summation order;
+          * nll / combined couple all rows of the batch through the joint Gaussian (src/model.py:237-247): pass 1 runs the
+            forward of every micro-batch and collects the final hidden states, the heads kernels then see the WHOLE
+            batch at once (one loss, dL/dh_T for every row), pass 2 re-runs each micro-batch's forward (same dropout
+            masks) and back-propagates its rows."""
+        ready = on_slice_ready or (lambda off, n, last: None)
+        chunks = getattr(batch, "chunks", None)
+        if chunks is None or len(chunks) == 1:
+            b = batch if chunks is None else chunks[0]
+            self.forward(b, training=True, dropout_seed=dropout_seed)
+            losses = self.heads(b, kind, mse_weight, None, grad_scale, want_grad=True)
+            ready(*self.layer_slice(self.L), False)
+            for layer in range(self.L - 1, -1, -1):
+                self.backward_layer(b, layer, True, dropout_seed)
+                ready(*self.layer_slice(layer), layer == 0)
+            return losses
+        Btot, nchunk = batch.n_windows, len(chunks)
+        self.ensure_capacity(max(c.n_windows for c in chunks))
+        if not hasattr(self, "grads_chunk"):
+            self.grads_chunk = torch.zeros_like(self.grads)
+            self.losses_acc = torch.zeros_like(self.losses)
+        joint = (kind if isinstance(kind, str) else {0: "mse", 1: "nll", 2: "combined"}[int(kind)]) != "mse"
+        hl, hn = self.layer_slice(self.L)
+        if joint:
+            self._ensure_joint(Btot)
+            row = 0
+            for ci, c in enumerate(chunks):                         # pass 1: final hidden state of every row
+                self.forward(c, training=True, dropout_seed=self.chunk_seed(dropout_seed, ci))
+                n = c.n_windows * self.S * self.H
+                self.hT_full[row:row + n].copy_(self.final_hidden(c.n_windows))
+                row += n
+            losses = self.heads(batch, kind, mse_weight, None, grad_scale, True, hT=self.hT_full, dhT=self.dhT_full,
+                                alpha=self.alpha_full, beta=self.beta_full, heads_ws=self.heads_ws_full)
+            ready(hl, hn, False)
+        else:
+            self.losses_acc.zero_()
+        row = 0
+        for ci, c in enumerate(chunks):
+            first, last = ci == 0, ci == nchunk - 1
+            seed = self.chunk_seed(dropout_seed, ci)
+            gbuf = self.grads if first else self.grads_chunk       # the first micro-batch writes the step's gradient directly
+            self.forward(c, training=True, dropout_seed=seed)
+            n = c.n_windows * self.S * self.H
+            if joint:
+                dhT = self.dhT_full[row:row + n]
+            else:
+                w = c.n_windows / Btot
+                self.heads(c, kind, mse_weight, None, grad_scale * w, True, head_grads=gbuf[self.head_off:])
+                self._accumulate(self.losses_acc, self.losses, 4, w)
+                if not first:
+                    self._accumulate(self.grads[hl:], self.grads_chunk[hl:], hn)
+                if last:
+                    ready(hl, hn, False)
+                dhT = self.dhT
+            row += n
+            for layer in range(self.L - 1, -1, -1):
+                self.backward_layer(c, layer, True, seed, dhT=dhT, grads=gbuf)
+                lo, ln = self.layer_slice(layer)
+                if not first:
+                    self._accumulate(self.grads[lo:], self.grads_chunk[lo:], ln)
+                if last:
+                    ready(lo, ln, layer == 0)
+        if not joint:
+            self.losses.copy_(self.losses_acc)
+        return self.losses
+
+    def _ensure_joint(self, n_windows):
+        """Whole-batch buffers of the two-pass joint-NLL path: final hidden states, their gradient, alpha/beta, heads workspace."""
+        if getattr(self, "_joint_cap", 0) >= n_windows:
+            return
+        N, dev = n_windows * self.S, self.device
+        self.hT_full = torch.empty(N * self.H, dtype=torch.float32, device=dev)
+        self.dhT_full = torch.empty_like(self.hT_full)
+        self.alpha_full = torch.empty(N, dtype=torch.float32, device=dev)
+        self.beta_full = torch.empty_like(self.alpha_full)
+        hws = int(self.lib.b200_heads_workspace_bytes(n_windows, self.S, self.n, self.H))
+        self.heads_ws_full = torch.empty(max(hws, 256), dtype=torch.uint8, device=dev)
+        self._joint_cap = n_windows
+
+    def bytes_per_window(self):
+        """Device bytes the engine's per-micro-batch buffers need per window (stash, LSTM workspace, dhT ...): used by the
+        trainer to size micro-batches for the free device memory."""
+        probe = 1024
+        ws = int(self.lib.b200_lstm_workspace_bytes(self.mode, probe * self.S, self.T, self.F, self.H, self.L))
+        return self.stash_bytes(1) + ws // probe + self.S * (self.H + 2) * 4 + self.S * (self.T * self.F + self.n + 1) * 4
 
     def optimizer_step(self, lr, clip_val=0.0, weight_decay=1e-5, betas=(0.9, 0.999), eps=1e-8):
         """Global-norm clip + Adam on the flat vector (train.py:171, src/model.py:150-154)."""
@@ -133,11 +252,9 @@ class LstmEngine:
         self.launches += 1
 
     def train_step(self, batch, kind, lr, clip_val, mse_weight=100.0, dropout_seed=0, grad_scale=1.0,
-                   on_layer_done=None, before_optimizer=None):
+                   on_slice_ready=None, before_optimizer=None):
         """One optimisation step; returns the device tensor [mse, nll, total, mae] (no host sync)."""
-        self.forward(batch, training=True, dropout_seed=dropout_seed)
-        losses = self.heads(batch, kind, mse_weight, None, grad_scale, want_grad=True)
-        self.backward(batch, True, dropout_seed, on_layer_done)
+        losses = self.forward_backward(batch, kind, mse_weight, dropout_seed, grad_scale, on_slice_ready)
         if before_optimizer is not None:
             before_optimizer()
         self.optimizer_step(lr, clip_val)

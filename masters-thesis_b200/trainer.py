@@ -5,8 +5,11 @@ shuffled training batches -> one fused device step each (forward, objective, BPT
 Adam), validation with batch size 1 semantics every `check_val_every_n_epoch` epochs, ReduceLROnPlateau
 on loss/total/val (src/model.py:156-172), best/last checkpoints (train.py:151-161) and the test loop
 (src/model.py:119-147).  Under torchrun (WORLD_SIZE > 1) it is data parallel: each rank takes its share
-of every global batch and gradients are summed (pre-scaled by 1/W) with bucketed all-reduces issued
-per layer on a communication stream while the lower layers' backward kernels are still running.
+of every epoch like Lightning's DistributedSampler (`datamodule.batch_size` is per rank, global batch = W x
+batch_size) and gradients are summed (pre-scaled by 1/W) with bucketed all-reduces (b200_dp_allreduce: NCCL from
+inside the library) issued per layer on a communication stream while the lower layers' backward kernels are still
+running.  A local batch whose activations do not fit the device is processed in micro-batches inside ONE optimiser
+step (engine.forward_backward).
 """
 from __future__ import annotations
 
@@ -96,13 +99,15 @@ def _precision_to_mode(precision, engine):
 class B200Trainer:
     def __init__(self, max_epochs=4, gradient_clip_val=None, precision="32-true", enable_progress_bar=False,
                  enable_model_summary=True, logger=None, callbacks=None, check_val_every_n_epoch=1, *,
-                 devices=1, max_steps=-1, seed=1234, bucket_mb=0.25, engine="auto", eval_batch_windows=512,
-                 checkpoint_dir=None, log_dir=None, limit_val_windows=None, limit_test_windows=None, verbose=True):
+                 devices=1, max_steps=-1, seed=1234, bucket_mb=0.05, engine="auto", eval_batch_windows=512,
+                 checkpoint_dir=None, log_dir=None, limit_val_windows=None, limit_test_windows=None, verbose=True,
+                 micro_batch_windows=4096):
         self.max_epochs, self.clip = int(max_epochs), gradient_clip_val
         self.precision, self.check_val_every_n_epoch = precision, int(check_val_every_n_epoch)
         self.max_steps, self.seed, self.bucket_mb = int(max_steps), int(seed), float(bucket_mb)
         self.mode = _precision_to_mode(precision, engine)
         self.eval_batch_windows = int(eval_batch_windows)
+        self.micro_batch_windows = int(micro_batch_windows) if micro_batch_windows else 0
         self.limit_val_windows, self.limit_test_windows = limit_val_windows, limit_test_windows
         self.verbose = verbose and int(os.environ.get("RANK", "0")) == 0
         self.checkpoint_callback = _CheckpointState(checkpoint_dir)
@@ -117,14 +122,50 @@ class B200Trainer:
         self.record_steps = False
         self._tb = None
         self._sync = None
+        self._comm = None
+        # optional callable(engine, global_step) invoked after the gradients of a step are complete (all-reduced under
+        # data parallelism) and before clip + Adam consume them: Lightning's on_before_optimizer_step hook
+        self.on_before_optimizer_step = None
 
     # ------------------------------------------------------------------ plumbing
     def _init_distributed(self):
-        if self.world > 1:
+        """torch.distributed is the rendezvous (it carries the NCCL unique id and the per-epoch scalar reductions); the
+        gradient exchange itself goes through the library's own communicator (b200_dp_init / b200_dp_allreduce)."""
+        if self.world > 1 and self._sync is None:
+            import ctypes
             import torch.distributed as dist
+            from . import _lib
             if not dist.is_initialized():
                 dist.init_process_group("nccl", device_id=self.device)
-            self._sync = GradBucketer(self.world, self.bucket_mb, device=self.device)
+            lib = _lib.load()
+            torch.cuda.set_device(self.device)
+            uid = ctypes.create_string_buffer(128)
+            if self.rank == 0:
+                _lib.check(lib.b200_dp_unique_id(uid), "b200_dp_unique_id")
+            box = [uid.raw]
+            dist.broadcast_object_list(box, src=0)
+            comm = ctypes.c_void_p()
+            _lib.check(lib.b200_dp_init(box[0], self.world, self.rank, ctypes.byref(comm)), "b200_dp_init")
+            self._comm = comm
+            self._sync = GradBucketer(self.world, self.bucket_mb, device=self.device, comm=comm, lib=lib)
+
+    def close(self):
+        """Destroy the library communicator (optional; the process exit does the same)."""
+        if self._comm is not None:
+            from . import _lib
+            _lib.load().b200_dp_destroy(self._comm)
+            self._comm, self._sync = None, None
+
+    def micro_windows(self, engine, batch_windows):
+        """Windows per micro-batch: the configured cap, lowered when the device's free memory cannot hold the activation
+        stash and workspaces of that many windows (engine buffers already allocated count as free)."""
+        cap = self.micro_batch_windows or batch_windows
+        free, _ = torch.cuda.mem_get_info(self.device)
+        held = sum(getattr(engine, n).numel() * getattr(engine, n).element_size()
+                   for n in ("stash_h", "stash_c", "lstm_ws") if hasattr(engine, n))
+        fit = int(0.85 * (free + held) / engine.bytes_per_window())
+        m = max(1, min(cap, batch_windows, fit))
+        return m if m >= batch_windows else max(1, m // 64 * 64 if m >= 64 else m)
 
     def _writer(self):
         if self._tb is None and self.log_dir and self.rank == 0:
@@ -154,23 +195,24 @@ class B200Trainer:
 
     # ------------------------------------------------------------------ one step
     def training_step(self, model, batch, lr):
+        """One optimiser step on this rank's batch (a DeviceBatch, or a ChunkedBatch of micro-batches)."""
         e = model.engine
+        if getattr(batch, "chunks", None) is None:       # a whole batch handed in by the caller (host-fed path): split here
+            m = self.micro_windows(e, batch.n_windows)
+            if batch.n_windows > m:
+                from .data import ChunkedBatch
+                batch = ChunkedBatch.split(batch, m)
         sync = self._sync
-        on_layer = None
+        ready = None
         if sync is not None:
             sync.begin(e.grads, e.P)
-            lo, ln = e.layer_slice(e.L)
-
-            def on_layer(layer, _e=e, _s=sync):
-                _s.layer_ready(*_e.layer_slice(layer), last=(layer == 0))
-        e.forward(batch, training=True, dropout_seed=self.dropout_seed(self.global_step))
-        losses = e.heads(batch, model.loss_kind, model.hparams.get("mse_weight", 100.0), None,
-                         1.0 / self.world, want_grad=True)
-        if sync is not None:
-            sync.layer_ready(lo, ln, last=False)          # heads slice opens the first bucket
-        e.backward(batch, True, self.dropout_seed(self.global_step), on_layer)
+            ready = sync.layer_ready                      # (offset, length, last): heads slice first, then layers top-down
+        losses = e.forward_backward(batch, model.loss_kind, model.hparams.get("mse_weight", 100.0),
+                                    self.dropout_seed(self.global_step), 1.0 / self.world, ready)
         if sync is not None:
             sync.wait()
+        if self.on_before_optimizer_step is not None:
+            self.on_before_optimizer_step(e, self.global_step)
         e.optimizer_step(lr, self.clip if self.clip else 0.0, model.hparams["weight_decay"])
         self.global_step += 1
         return losses
@@ -184,15 +226,27 @@ class B200Trainer:
         limit = self.limit_val_windows if split == "val" else self.limit_test_windows
         if limit:
             hi = min(hi, lo + int(limit))
-        acc = torch.zeros(4, dtype=torch.float64, device=self.device)
+        # data parallel: every rank evaluates a contiguous share of the split; the sums are all-reduced (every window
+        # is its own batch, so the split's means do not depend on how it is cut)
+        sharded = self.world > 1 and self._sync is not None
+        if sharded:
+            per = (hi - lo + self.world - 1) // self.world
+            lo, hi = min(hi, lo + self.rank * per), min(hi, lo + (self.rank + 1) * per)
+        acc = torch.zeros(5, dtype=torch.float64, device=self.device)
         done = 0
         kind = model.loss_kind if split == "val" else "combined"
+        nb_max = min(self.eval_batch_windows, self.micro_windows(e, self.eval_batch_windows))
         while done < hi - lo:
-            nb = min(self.eval_batch_windows, hi - lo - done)
+            nb = min(nb_max, hi - lo - done)
             batch = dm.source.generate(first_window=lo + done, n_windows=nb)
-            acc += e.eval_windows(batch, kind, model.hparams.get("mse_weight", 100.0)).double() * nb
+            acc[:4] += e.eval_windows(batch, kind, model.hparams.get("mse_weight", 100.0)).double() * nb
             done += nb
-        mse, nll, total, mae = (acc / max(done, 1)).tolist()
+        acc[4] = done
+        if sharded:
+            import torch.distributed as dist
+            dist.all_reduce(acc)
+        done = int(acc[4].item())
+        mse, nll, total, mae = (acc[:4] / max(done, 1)).tolist()
         return {"mse": mse, "nll": nll, "total": total, "mae": mae, "windows": done}
 
     def fit(self, model, datamodule=None):
@@ -202,6 +256,8 @@ class B200Trainer:
         dm.setup("fit")
         e = self._attach(model, dm)
         self._init_distributed()
+        if getattr(dm, "micro_batch_windows", None) is None:
+            dm.micro_batch_windows = self.micro_windows(e, int(dm.hparams["batch_size"]))
         sched = PlateauSchedule(model.hparams["learning_rate"])
         ck = self.checkpoint_callback
         kind = model.loss_kind
@@ -231,7 +287,9 @@ class B200Trainer:
                 metrics["loss/mse/train"] = mse
             if kind in ("nll", "combined"):
                 metrics["loss/nll/train"] = nll
-            if (epoch + 1) % self.check_val_every_n_epoch == 0 or stop or epoch == self.max_epochs - 1:
+            # validation, scheduler and checkpoints run on Lightning's cadence only (multiples of check_val_every_n_epoch,
+            # also when max_steps ends the epoch early): best score, lr history and checkpoint names then match the reference
+            if (epoch + 1) % self.check_val_every_n_epoch == 0:
                 v = self.evaluate(model, dm, "val")
                 metrics["loss/total/val"] = v["total"]
                 if kind in ("mse", "combined"):

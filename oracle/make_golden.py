@@ -136,9 +136,68 @@ def variants():
     np.savez_compressed(OUT / "golden_variants.npz", **out)
 
 
+BATCH_CASES = [(kind, 64, 2, B) for kind in ("mse", "nll", "combined") for B in (1, 8, 64)] + [("combined", 128, 3, 8)]
+BATCH_SEED_DATA, BATCH_FIRST_WINDOW = 4321, 500
+
+
+def batch_goldens():
+    """golden_batches.npz: the reference's FinancialLstm{Mse,Nll,Combined}, dropout 0, for
+    batch_size B in {1, 8, 64} on the small model plus one widened shape (hidden 128 x 3 layers): 3 optimisation steps
+    in Lightning's order with gradient_clip_val 5.0 -- per-step losses, step-0 gradients (pre-clip) and their norm.
+    Inputs are NOT stored: step s uses windows BATCH_FIRST_WINDOW + s*B .. + B of the written generator specification
+    (oracle/lstm_oracle.py generate_days, seed BATCH_SEED_DATA), pushed here through the REFERENCE's own
+    lookback_target_split / add_quadratic_features / ols_features / _append_feature; the tests rebuild the same
+    batches with lstm_oracle.generate_windows (pinned bit-equal to the reference's prep by test_oracle.py)."""
+    src = ref_stubs.install()
+    from src.common import lookback_target_split, add_quadratic_features, ols_features
+    from src.data import _append_feature
+    import lstm_oracle as O
+    torch.set_num_threads(8)
+    torch.set_float32_matmul_precision("highest")
+    classes = {"mse": src.FinancialLstmMse, "nll": src.FinancialLstmNll, "combined": src.FinancialLstmCombined}
+
+    def ref_batch(first, B):
+        r_s, r_m, a, b = O.generate_days(first * 90, 90 * B, 100, BATCH_SEED_DATA)
+        X, y = lookback_target_split(torch.from_numpy(r_s), torch.from_numpy(r_m), 60, 30, 90, True)
+        X = add_quadratic_features(X, interaction_only=True)
+        _, _, factor, inv_psi = ols_features(y)
+        y = _append_feature(_append_feature(y, torch.from_numpy(a)), torch.from_numpy(b))
+        return [X.contiguous(), y.contiguous(), factor, inv_psi]
+
+    out = {"cases": np.array([f"{k}_h{H}_l{L}_b{B}" for k, H, L, B in BATCH_CASES]),
+           "meta": np.array([BATCH_SEED_DATA, SEED_MODEL, BATCH_FIRST_WINDOW, STEPS]), "clip": np.float64(CLIP)}
+    for kind, H, L, B in BATCH_CASES:
+        tag = f"{kind}_h{H}_l{L}_b{B}"
+        torch.manual_seed(SEED_MODEL)
+        model = classes[kind](input_size=3, hidden_size=H, num_layers=L, dropout=0.0, learning_rate=1e-4)
+        opt = model.configure_optimizers()["optimizer"]
+        model.train()
+        losses, grads0, gnorm0 = [], None, None
+        for s in range(STEPS):
+            batch = ref_batch(BATCH_FIRST_WINDOW + s * B, B)
+            loss = model.training_step(batch, s)
+            opt.zero_grad()
+            loss.backward()
+            if s == 0:
+                grads0 = torch.cat([p.grad.reshape(-1) for p in model.parameters()]).numpy().copy()
+            gn = torch.nn.utils.clip_grad_norm_(model.parameters(), CLIP)
+            if s == 0:
+                gnorm0 = float(gn)
+            opt.step()
+            losses.append(float(loss.detach()))
+        out[f"{tag}_losses"] = np.array(losses)
+        out[f"{tag}_grads0"] = grads0
+        out[f"{tag}_gnorm0"] = np.float64(gnorm0)
+        print(tag, losses, gnorm0, flush=True)
+    np.savez_compressed(OUT / "golden_batches.npz", **out)
+
+
 if __name__ == "__main__":
     if "--variants-only" in sys.argv:
         variants()
+    elif "--batches-only" in sys.argv:
+        batch_goldens()
     else:
         main()
         variants()
+        batch_goldens()

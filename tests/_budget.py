@@ -1,0 +1,120 @@
+"""Fixed-step-budget parity harness (-m gpu tests): B200Trainer on the device against the oracle loop on the SAME windows
+and the SAME dropout masks (north_star: per-step loss within 1e-4 relative, gradients within 1e-3, identical final
+metrics over a fixed step budget; reference loop: train.py:187, src/model.py:204-209).
+
+The device generator is authoritative for the inputs: every chunk the oracle sees is the device's
+own batch copied to the host in the reference layout.  Dropout masks come from b200_dropout_mask, which a separate test
+pins bit-exactly against the written numpy specification.  Large batches are accumulated on the CPU over chunks of at
+most 256 windows (exact for the mse objective: a mean over rows)."""
+import os
+
+import numpy as np
+import torch
+
+import lstm_oracle as O
+import masters_thesis_b200 as B
+from masters_thesis_b200._lib import check, load, ptr
+
+S, T, H = 100, 60, 64
+
+
+def device_masks(seed, layers, n_seq, p, dev):
+    """[layers-1] tensors (T, N, H) on the device: the keep masks the kernels apply to the inputs of layers 1.."""
+    lib, out = load(), []
+    for l in range(1, layers):
+        m = torch.empty(T, n_seq, H, dtype=torch.float32, device=dev)
+        check(lib.b200_dropout_mask(int(seed), l, n_seq, T, H, float(p), ptr(m), None), "b200_dropout_mask")
+        out.append(m)
+    return out
+
+
+def oracle_accumulated_step(om, em, src, first_window, n_windows, kind, masks, chunk=256):
+    """Loss and gradients (left in p.grad) of one batch, accumulated over chunks of <= `chunk` windows."""
+    om.zero_grad()
+    total = 0.0
+    for lo in range(0, n_windows, chunk):
+        nb = min(chunk, n_windows - lo)
+        ref = [t.cpu() for t in src.generate(first_window=first_window + lo, n_windows=nb).to_reference()]
+        fwd = None
+        if masks:
+            mk = [m[:, lo * S:(lo + nb) * S].permute(1, 0, 2).cpu() for m in masks]
+            fwd = lambda x, _mk=mk: em(x, _mk)
+        ls = O.batch_losses(om, ref, kind, forward=fwd)
+        w = nb / n_windows
+        (ls["total"] * w).backward()
+        total += float(ls["total"]) * w
+    return total
+
+
+def run_budget(dev, batch_windows, steps, dropout, engine="tc_precise", kind="mse", clip=5.0, seed=1234, limit_eval=48,
+               want_grads_at=(0,)):
+    """Returns a dict of device-side and oracle-side records of a `steps`-step run at `batch_windows` windows per step."""
+    torch.set_num_threads(os.cpu_count() or 8)
+    torch.set_float32_matmul_precision("highest")
+    torch.manual_seed(seed)
+    cls = {"mse": B.FinancialLstmMse, "nll": B.FinancialLstmNll, "combined": B.FinancialLstmCombined}[kind]
+    model = cls(3, H, 2, dropout, 1e-4)
+    init = model.flat_parameters().clone()
+    dm = B.FinancialLstmDataModule(lookback_window=T, target_window=30, stride=90, batch_size=batch_windows, seed=seed,
+                                   device=dev, streaming=True, steps_per_epoch=steps)
+    tr = B.B200Trainer(max_epochs=1, gradient_clip_val=clip, engine=engine, verbose=False, seed=seed,
+                       limit_val_windows=limit_eval, limit_test_windows=limit_eval, micro_batch_windows=batch_windows)
+    tr.record_steps = True
+    dev_grads = {}
+    tr.on_before_optimizer_step = lambda e, step: dev_grads.__setitem__(step, e.grads[: e.P].clone()) if step in want_grads_at else None
+    tr.fit(model, dm)
+    tr.test(model, dm)
+    torch.cuda.synchronize()
+    rec = {"dev_losses": [float(l[2]) for l in tr.step_losses], "dev_grads": {k: v.cpu().numpy() for k, v in dev_grads.items()},
+           "dev_best_val": float(tr.checkpoint_callback.best_model_score), "dev_test": dict(model.test_results["test_loss"]),
+           "dev_final": model.flat_parameters().numpy().copy()}
+    # ---- the oracle on the same windows and masks
+    om = O.OracleLstm(3, H, 2, 0.0)
+    off = 0
+    with torch.no_grad():
+        for p_ in om.parameters():
+            p_.copy_(init[off:off + p_.numel()].reshape(p_.shape)); off += p_.numel()
+    em = O.ExplicitMaskLstm(om)
+    opt = O.make_optimizer(om)
+    src = B.data.DeviceBatchSource(dev, seed)
+    rec["ref_losses"], rec["ref_grads"] = [], {}
+    N = batch_windows * S
+    for s in range(steps):
+        masks = device_masks(tr.dropout_seed(s), 2, N, dropout, dev) if dropout > 0 else None
+        om.train()
+        loss = oracle_accumulated_step(om, em, src, dm.n_windows + s * batch_windows, batch_windows, kind, masks)
+        del masks
+        if s in want_grads_at:
+            rec["ref_grads"][s] = O.flat_grads(om).numpy().copy()
+        O.clip_global_norm(list(om.parameters()), clip)
+        opt.step()
+        rec["ref_losses"].append(loss)
+    nv = min(limit_eval, dm.val_end - dm.train_end)
+    vb = [t.cpu() for t in src.generate(first_window=dm.train_end, n_windows=nv).to_reference()]
+    rec["ref_best_val"] = O.eval_windows(om, *vb, kind)["total"]
+    tb = [t.cpu() for t in src.generate(first_window=dm.val_end, n_windows=nv).to_reference()]
+    rec["ref_test"] = O.test_windows(om, *tb)
+    rec["ref_final"] = O.flat_params(om).numpy().copy()
+    rec["names"], rec["shapes"] = model.names, B.model._param_shapes(3, H, 2)
+    return rec
+
+
+def check_budget(rec, loss_rtol=1e-4, grad_rtol=1e-3, metric_rtol=2e-4):
+    from _gpu_util import rel_err
+    for s, (a, b) in enumerate(zip(rec["dev_losses"], rec["ref_losses"])):
+        assert abs(a - b) <= loss_rtol * abs(b), f"step {s}: device loss {a} vs oracle {b}"
+    for s, g in rec["dev_grads"].items():
+        r = rec["ref_grads"][s]
+        assert rel_err(g, r) < grad_rtol, f"step {s}: whole gradient vector"
+        off = 0
+        for name, shape in zip(rec["names"], rec["shapes"]):
+            n = int(np.prod(shape))
+            assert rel_err(g[off:off + n], r[off:off + n]) < grad_rtol, f"step {s}: {name}"
+            off += n
+    assert abs(rec["dev_best_val"] - rec["ref_best_val"]) <= metric_rtol * abs(rec["ref_best_val"])
+    for k in ("mae", "nll"):
+        assert abs(rec["dev_test"][k] - rec["ref_test"][k]) <= metric_rtol * abs(rec["ref_test"][k]), k
+    # Adam divides by sqrt(v): a parameter whose gradient is ~0 turns a 1e-7 gradient difference into a different fraction
+    # of the lr = 1e-4 step, so the bound is on the bulk plus a cap far below steps * lr
+    diff = np.abs(rec["dev_final"] - rec["ref_final"])
+    assert np.mean(diff > 5e-6) < 2e-3 and diff.max() < 2e-4, (float(np.mean(diff > 5e-6)), float(diff.max()))

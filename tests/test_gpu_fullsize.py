@@ -62,3 +62,19 @@ def test_full_size_step_properties(engine):
     assert rel_err((g_a + g_b).cpu().numpy(), g_full.cpu().numpy()) < 2e-5
     assert float(l_full[0]) == pytest.approx(0.5 * (float(l_a[0]) + float(l_b[0])), rel=1e-6)
     assert np.isfinite(g_full.cpu().numpy()).all() and float(g_full.abs().max()) > 0
+
+
+def test_full_size_fixed_budget_vs_oracle():
+    """The headline configuration under the north_star gate, on the engine and through the object the bench uses
+    (BASELINE.json configs[1]: small model, mse, dropout 0.2, 4096 windows = 409,600 sequences per step, tc_precise,
+    B200Trainer): five optimisation steps against the CPU oracle accumulated over 256-window chunks on the same windows and
+    the same Philox dropout masks -- per-step loss within 1e-4 relative, the FULL step-0 gradient within 1e-3 (whole
+    vector and per tensor), then best_val_loss, test mae and test nll (train.py:204-211) and the final parameters."""
+    if not load().b200_mode_available(B.MODES["tc_precise"]):
+        pytest.skip("tcgen05 engine unavailable")
+    free, _ = torch.cuda.mem_get_info(0)
+    if free < 100e9:
+        pytest.skip("needs ~85 GB of device memory")
+    from _budget import check_budget, run_budget
+    rec = run_budget(DEV, BW, 5, 0.2, engine="tc_precise", kind="mse", want_grads_at=(0,))
+    check_budget(rec)

@@ -161,6 +161,147 @@ def test_chunked_backward_equals_unchunked(engine, data):
         e.lstm_ws = torch.empty(fixed + 60 * 128 * 256 * 4 + 4096, dtype=torch.uint8, device=DEV)   # room for 128 sequences
         e.backward(batch, True)
         assert rel_err(e.grads[: e.P].cpu().numpy(), full.cpu().numpy()) < 1e-5
+    else:
+        # the tcgen05 engine has no da chunks (the weight gradient never leaves the SM); its way of bounding memory is the
+        # micro-batched step: the same batch as four 1-window micro-batches, accumulated inside one step
+        g = e.forward_backward(B.ChunkedBatch.split(batch, 1), "mse")
+        torch.cuda.synchronize()
+        assert rel_err(e.grads[: e.P].cpu().numpy(), full.cpu().numpy()) < 1e-5
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("kind", ["mse", "nll", "combined"])
+@pytest.mark.parametrize("micro", [1, 3])
+def test_micro_batched_step_equals_whole_batch(engine, kind, micro, data):
+    """One optimiser step's loss and gradient do not depend on how the batch is cut into micro-batches (even and ragged
+    cuts): mse by weighted accumulation, nll / combined by the two-pass joint path -- equal to fp32 summation order.
+    Also against the oracle on the whole batch (the reference never splits a batch, src/model.py:204-209)."""
+    torch.manual_seed(17)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    e = make_engine(O.flat_params(m), 2, 0.0, engine)
+    whole = B.DeviceBatch.from_reference(ref_batch(data, 0, 5), DEV)
+    l_w = e.forward_backward(whole, kind).clone()
+    g_w = e.grads[: e.P].clone()
+    e.grads.zero_()
+    l_c = e.forward_backward(B.ChunkedBatch.split(whole, micro), kind).clone()
+    g_c = e.grads[: e.P].clone()
+    torch.cuda.synchronize()
+    assert float(l_c[2]) == pytest.approx(float(l_w[2]), rel=2e-6)
+    assert rel_err(g_c.cpu().numpy(), g_w.cpu().numpy()) < 1e-5
+    ls = O.batch_losses(m, ref_batch(data, 0, 5), kind)
+    m.zero_grad()
+    ls["total"].backward()
+    assert float(l_c[2]) == pytest.approx(float(ls["total"]), rel=LOSS_RTOL)
+    assert rel_err(g_c.cpu().numpy(), O.flat_grads(m).numpy()) < GRAD_RTOL
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_micro_batched_dropout_step_vs_oracle(engine, data):
+    """Micro-batches under dropout: micro-batch c uses the seed LstmEngine.chunk_seed(seed, c); the oracle gets the same masks."""
+    torch.manual_seed(23)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    p, seed = 0.2, 987654321
+    e = make_engine(O.flat_params(m), 2, p, engine)
+    whole = B.DeviceBatch.from_reference(ref_batch(data, 0, 4), DEV)
+    losses = e.forward_backward(B.ChunkedBatch.split(whole, 2), "mse", dropout_seed=seed).clone()
+    torch.cuda.synchronize()
+    em = O.ExplicitMaskLstm(m)
+    m.zero_grad()
+    total = 0.0
+    for c in range(2):
+        mk = [torch.from_numpy(O.dropout_mask(e.chunk_seed(seed, c), 1, 200, 60, 64, p)).permute(1, 0, 2)]
+        ls = O.batch_losses(m, ref_batch(data, 2 * c, 2 * c + 2), "mse", forward=lambda x, _mk=mk: em(x, _mk))
+        (0.5 * ls["total"]).backward()
+        total += 0.5 * float(ls["total"])
+    assert float(losses[2]) == pytest.approx(total, rel=LOSS_RTOL)
+    assert rel_err(e.grads[: e.P].cpu().numpy(), O.flat_grads(m).numpy()) < GRAD_RTOL
+
+
+BATCH_CASES = [(kind, 64, 2, B_) for kind in ("mse", "nll", "combined") for B_ in (1, 8, 64)] + [("combined", 128, 3, 8)]
+
+
+@pytest.mark.parametrize("kind,H,L,B_", BATCH_CASES)
+def test_training_steps_vs_reference_golden_batches(kind, H, L, B_, golden_dir):
+    """the reference's own modules at batch_size 1, 8, 64 (and one widened shape) for three
+    optimisation steps -- per-step loss, step-0 gradient (whole and per tensor) and its norm on the tcgen05 engine."""
+    g = np.load(golden_dir / "golden_batches.npz")
+    tag = f"{kind}_h{H}_l{L}_b{B_}"
+    seed_data, seed_model, first, steps = (int(v) for v in g["meta"])
+    torch.manual_seed(seed_model)
+    cls = {"mse": B.FinancialLstmMse, "nll": B.FinancialLstmNll, "combined": B.FinancialLstmCombined}[kind]
+    model = cls(3, H, L, 0.0, 1e-4)
+    e = model.attach(DEV, "tc_precise")
+    for s in range(steps):
+        ref = list(O.generate_windows(range(first + s * B_, first + (s + 1) * B_), seed=seed_data))
+        batch = B.DeviceBatch.from_reference(ref, DEV)
+        losses = e.forward_backward(batch, kind).clone()
+        if s == 0:
+            got, want = e.grads[: e.P].cpu().numpy(), g[f"{tag}_grads0"]
+            assert rel_err(got, want) < GRAD_RTOL
+            off = 0
+            for name, shape in zip(model.names, B.model._param_shapes(3, H, L)):
+                n = int(np.prod(shape))
+                assert rel_err(got[off:off + n], want[off:off + n]) < GRAD_RTOL, name
+                off += n
+        e.optimizer_step(1e-4, float(g["clip"]))
+        assert float(losses[2]) == pytest.approx(float(g[f"{tag}_losses"][s]), rel=LOSS_RTOL), (tag, s)
+        if s == 0:
+            assert float(torch.sqrt(e.sqnorm)) == pytest.approx(float(g[f"{tag}_gnorm0"]), rel=GRAD_RTOL)
+
+
+def test_fixed_budget_256_windows_through_trainer_tc_precise():
+    """north_star's fixed step budget on the engine the bench uses: 20 optimisation steps of 256 windows (25,600 sequences,
+    dropout 0.2 with shared masks) through B200Trainer, then validation and test -- per-step loss 1e-4, step-0 and
+    step-19 gradients 1e-3 (whole vector and per tensor), best_val_loss / test mae / test nll, final parameters."""
+    from _budget import check_budget, run_budget
+    rec = run_budget(DEV, 256, 20, 0.2, engine="tc_precise", kind="mse", want_grads_at=(0, 19))
+    check_budget(rec)
+
+
+# Tolerance the single-bf16 engine (`precision: bf16-mixed` -> tc_fast) is sold at (DESIGN.md section 4): it is NOT an fp32
+# parity engine.  One bf16 product has a relative error of 2^-9 per operand; through 60 recurrent steps the per-step loss
+# stays within 2e-3 relative and the gradient within 3e-2 of its largest entry (cosine > 0.9995) at 200..800 sequences.
+FAST_LOSS_RTOL, FAST_GRAD_RTOL = 2e-3, 3e-2
+
+
+@pytest.mark.parametrize("kind", ["mse", "combined"])
+def test_tc_fast_accuracy_hidden64(kind, data):
+    if not B._lib.load().b200_mode_available(B.MODES["tc_fast"]):
+        pytest.skip("tcgen05 engine unavailable")
+    torch.manual_seed(31)
+    m = O.OracleLstm(3, 64, 2, 0.0)
+    e = make_engine(O.flat_params(m), 2, 0.0, "tc_fast")
+    batch = B.DeviceBatch.from_reference(ref_batch(data, 0, 4), DEV)
+    losses = e.forward_backward(batch, kind).clone()
+    torch.cuda.synchronize()
+    ls = O.batch_losses(m, ref_batch(data, 0, 4), kind)
+    m.zero_grad()
+    ls["total"].backward()
+    got, want = e.grads[: e.P].cpu().numpy().astype(np.float64), O.flat_grads(m).numpy().astype(np.float64)
+    assert float(losses[2]) == pytest.approx(float(ls["total"]), rel=FAST_LOSS_RTOL)
+    assert rel_err(got, want) < FAST_GRAD_RTOL
+    assert float(got @ want / (np.linalg.norm(got) * np.linalg.norm(want))) > 0.9995
+
+
+def test_dp_entry_points_single_rank():
+    """b200_dp_unique_id / init / allreduce / destroy through the C-ABI with a world of one rank: the sum over one rank is
+    the input, on the default and on a side stream (multi-rank behaviour: tools/dp_parity.py and the N > 1 bench)."""
+    import ctypes
+    lib = B._lib.load()
+    assert lib.b200_dp_nccl_version() >= 20000
+    uid = ctypes.create_string_buffer(128)
+    B._lib.check(lib.b200_dp_unique_id(uid), "b200_dp_unique_id")
+    comm = ctypes.c_void_p()
+    torch.cuda.set_device(0)
+    B._lib.check(lib.b200_dp_init(uid.raw, 1, 0, ctypes.byref(comm)), "b200_dp_init")
+    x = torch.arange(1000, dtype=torch.float32, device=DEV)
+    side = torch.cuda.Stream(device=DEV)
+    side.wait_stream(torch.cuda.current_stream())
+    B._lib.check(lib.b200_dp_allreduce(comm, x.data_ptr(), 1000, side.cuda_stream), "b200_dp_allreduce")
+    side.synchronize()
+    assert torch.equal(x.cpu(), torch.arange(1000, dtype=torch.float32))
+    assert lib.b200_dp_allreduce(comm, None, 10, None) == -1
+    B._lib.check(lib.b200_dp_destroy(comm), "b200_dp_destroy")
 
 
 @pytest.mark.parametrize("engine", ENGINES)
@@ -182,7 +323,8 @@ def test_data_parallel_semantics_emulated_two_ranks(engine, kind, data):
     assert rel_err(total.cpu().numpy(), O.flat_grads(m).numpy()) < GRAD_RTOL
 
 
-def test_trainer_fit_matches_oracle_loop():
+@pytest.mark.parametrize("engine", ENGINES)
+def test_trainer_fit_matches_oracle_loop(engine):
     """End to end through B200Trainer (the trainer=b200 object): 6 steps of batch 2 on device-generated
     windows, then validation and test -- against the oracle loop fed the SAME windows."""
     torch.manual_seed(1234)
@@ -190,7 +332,7 @@ def test_trainer_fit_matches_oracle_loop():
     init = model.flat_parameters().clone()
     dm = B.FinancialLstmDataModule(lookback_window=60, target_window=30, stride=90, batch_size=2, seed=77,
                                    n_samples=90 * 40, device=DEV)
-    tr = B.B200Trainer(max_epochs=1, gradient_clip_val=5.0, max_steps=6, engine="ffma", verbose=False)
+    tr = B.B200Trainer(max_epochs=1, gradient_clip_val=5.0, max_steps=6, engine=engine, verbose=False)
     tr.record_steps = True
     tr.fit(model, dm)
     tr.test(model, dm)
@@ -209,7 +351,11 @@ def test_trainer_fit_matches_oracle_loop():
     t = O.test_windows(om, *O.generate_windows(list(range(dm.val_end, dm.n_windows)), seed=77))
     assert model.test_results["test_loss"]["mae"] == pytest.approx(t["mae"], rel=5e-4)
     assert model.test_results["test_loss"]["nll"] == pytest.approx(t["nll"], rel=5e-4)
-    np.testing.assert_allclose(model.flat_parameters().numpy(), O.flat_params(om).numpy(), atol=5e-6)
+    diff = np.abs(model.flat_parameters().numpy() - O.flat_params(om).numpy())
+    if engine == "ffma":
+        assert diff.max() < 5e-6
+    else:       # Adam's 1/sqrt(v) amplifies 1e-7 gradient differences of near-zero gradients: bound the bulk, cap the rest
+        assert np.mean(diff > 5e-6) < 1e-3 and diff.max() < 2e-4
 
 
 def test_model_forward_api():

@@ -160,21 +160,23 @@ def test_wide_config_through_trainer():
     assert np.isfinite(float(tr.checkpoint_callback.best_model_score))
 
 
-def test_wide_fused_cell_path_matches_unfused(data, monkeypatch):
-    """B200_WIDE_FUSE=1 (cell update in the epilogue of the recurrent GEMM, gate-interleaved weight images): same hidden
+def test_wide_fused_cell_path_matches_unfused(data):
+    """b200_set_option("wide_fuse", 1) (cell update in the epilogue of the recurrent GEMM, gate-interleaved weight images): same hidden
     states and gradients as the default path."""
     H, layers = 256, 2
     torch.manual_seed(8)
     flat = O.flat_params(O.OracleLstm(3, H, layers, 0.0)).clone()
     batch = B.DeviceBatch.from_reference(ref_batch(data, 0, 2), DEV)
     outs = []
-    for fuse in ("0", "1"):
-        monkeypatch.setenv("B200_WIDE_FUSE", fuse)
+    lib = B._lib.load()
+    for fuse in (0, 1):
+        assert lib.b200_set_option(b"wide_fuse", fuse) == 0
         e = make_engine(flat, layers, 0.0, "tc_precise", 3, H)
         e.forward(batch, training=True)
         losses = e.heads(batch, "combined", 100.0, None, 1.0, True).clone()
         e.backward(batch, True)
         outs.append((e.stash_h.clone(), losses, e.grads[: e.P].clone()))
+    lib.b200_set_option(b"wide_fuse", 0)
     assert float((outs[0][0] - outs[1][0]).abs().max()) < 2e-6
     assert float(outs[0][1][2]) == pytest.approx(float(outs[1][1][2]), rel=1e-6)
     assert rel_err(outs[1][2].cpu().numpy(), outs[0][2].cpu().numpy()) < 1e-5

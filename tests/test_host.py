@@ -106,6 +106,76 @@ def test_datamodule_split_matches_reference_arithmetic():
         B.FinancialLstmDataModule(lookback_window=10, target_window=20, prediction_task=False)
 
 
+class _FakeSource:
+    device = "cpu"
+
+    def generate(self, window_idx=None, first_window=0, n_windows=None, checked=False, micro=None, out=None):
+        return window_idx.tolist() if window_idx is not None else list(range(first_window, first_window + n_windows))
+
+
+def test_loader_rank_shares_follow_distributed_sampler():
+    """Under data parallelism batch_size is per rank (Lightning DDP on the reference, train.py:169) and every rank sees its
+    DistributedSampler share of the epoch: the reference default batch_size 1 with WORLD_SIZE 2 trains on every window
+    (nothing skipped, nothing dropped), ragged epochs are padded by wrapping around."""
+    from masters_thesis_b200.data import _Loader, _StreamLoader, rank_share
+    n, world = 11, 2
+    seen = []
+    for rank in range(world):
+        gen = torch.Generator().manual_seed(3)
+        batches = list(_Loader(_FakeSource(), 100, 100 + n, 1, True, gen, rank, world))
+        assert len(batches) == 6 == len(_Loader(_FakeSource(), 100, 100 + n, 1, True, gen, rank, world))
+        assert all(len(b) == 1 for b in batches)
+        seen.append([b[0] for b in batches])
+    order = (torch.randperm(n, generator=torch.Generator().manual_seed(3)) + 100).tolist()
+    padded = order + order[:1]
+    assert seen[0] == padded[0::2] and seen[1] == padded[1::2]
+    assert set(seen[0]) | set(seen[1]) == set(range(100, 100 + n))
+    # torch's own sampler agrees (shuffle off: same order in, same share out)
+    from torch.utils.data.distributed import DistributedSampler
+    for rank in range(3):
+        want = list(DistributedSampler(range(10), num_replicas=3, rank=rank, shuffle=False))
+        assert rank_share(torch.arange(10), rank, 3).tolist() == want
+    # batch_size 4 per rank: ceil(6 / 4) = 2 batches, the last one ragged
+    b = list(_Loader(_FakeSource(), 0, n, 4, False, None, 1, 2))
+    assert [len(x) for x in b] == [4, 2] and b[0] == [1, 3, 5, 7]
+    # streaming: step k of rank r = windows first + (k * W + r) * B .. + B, disjoint over ranks and steps
+    s0 = list(_StreamLoader(_FakeSource(), 1000, 8, 2, 0, 2))
+    s1 = list(_StreamLoader(_FakeSource(), 1000, 8, 2, 1, 2))
+    assert s0[0] == list(range(1000, 1008)) and s1[0] == list(range(1008, 1016)) and s0[1] == list(range(1016, 1024))
+    with pytest.raises(ValueError):
+        _Loader(_FakeSource(), 0, 4, 0, False)
+
+
+def test_stale_library_is_detected(tmp_path, monkeypatch):
+    """_lib.load() compares the hash compiled into the binary with the sources next to it."""
+    from masters_thesis_b200 import build as builder
+    lib = B._lib.load()
+    assert lib.b200_build_hash().decode() == builder.source_hash(builder._extra_flags())
+    monkeypatch.setattr(builder, "source_hash", lambda extra=(): "0" * 16)
+    with pytest.raises(B.B200Error, match="built from other sources"):
+        B._lib.load(B._lib.LIB_PATH)
+
+
+def test_train_entry_names_b200_for_reference_trainers(capsys):
+    """`python train.py` with the reference's untouched defaults (trainer: fast) is the reference's Lightning path: without
+    lightning/hydra and a reference checkout it must say so and name trainer=b200, not train something else."""
+    sys.path.insert(0, str(ROOT))
+    import importlib
+    import importlib.util
+    if importlib.util.find_spec("lightning") is not None:
+        pytest.skip("lightning present: the fallthrough would run the reference")
+    train = importlib.import_module("train")
+    with pytest.raises(SystemExit) as ei:
+        train.main([])
+    assert "trainer=b200" in str(ei.value) and "trainer=fast" in str(ei.value)
+    for name, (epochs, clip, cadence) in {"b200_fast": (4, 5.0, None), "b200_slow": (32, 2.0, 4), "b200_slowest": (1024, 1.0, 64)}.items():
+        cfg = B.compose_config(CONFIGS, overrides=[f"trainer={name}"])
+        ref = B.compose_config(CONFIGS, overrides=[f"trainer={name[5:]}"])
+        assert train.is_b200_trainer(cfg) and not train.is_b200_trainer(ref)
+        assert (cfg.trainer.max_epochs, cfg.trainer.gradient_clip_val, cfg.trainer.get("check_val_every_n_epoch")) == (epochs, clip, cadence)
+        assert (ref.trainer.max_epochs, ref.trainer.gradient_clip_val, ref.trainer.get("check_val_every_n_epoch")) == (epochs, clip, cadence)
+
+
 def test_plateau_schedule_matches_torch():
     from masters_thesis_b200.trainer import PlateauSchedule
     p = torch.nn.Parameter(torch.zeros(1))
@@ -160,6 +230,8 @@ def test_grad_bucketer_world2_gloo(tmp_path):
 def test_sweep_plan_assigns_one_gpu_per_job():
     sys.path.insert(0, str(ROOT / "sweeps"))
     import run_sweep
+    grid = ["datamodule=synthetic", "model=small,medium,large", "loss=mse,nll,combined", "trainer=b200_fast,b200_slow"]
+    assert len(run_sweep.plan(grid, 8)) == 18           # the reference's sweeps/experiment_synthetic.sh grid
     jobs = run_sweep.plan(["datamodule=synthetic", "model=small,medium,large", "loss=mse,nll,combined", "trainer=b200"], 8)
     assert len(jobs) == 9
     assert [j["gpu"] for j in jobs] == [0, 1, 2, 3, 4, 5, 6, 7, 0]

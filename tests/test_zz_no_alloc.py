@@ -35,6 +35,22 @@ def test_static_scratch_matches_workspace_version_twice_in_a_row():
         assert float(got) == pytest.approx(float((x.double() ** 2).sum()), rel=1e-5)
 
 
+def test_static_scratch_on_a_side_stream():
+    """The same comparison with both calls enqueued on a non-default stream (the caller's stream is honoured)."""
+    lib = load()
+    side = torch.cuda.Stream(device=DEV)
+    x = torch.randn(117 * 1024, generator=torch.Generator().manual_seed(5)).to(DEV)
+    ws = torch.empty(lib.b200_sqnorm_workspace_bytes(x.numel()), dtype=torch.uint8, device=DEV)
+    got, want = torch.zeros(1, device=DEV), torch.zeros(1, device=DEV)
+    side.wait_stream(torch.cuda.current_stream())
+    for _ in range(2):
+        check(lib.b200_grad_sqnorm_static(ptr(x), x.numel(), ptr(got), side.cuda_stream), "b200_grad_sqnorm_static")
+        check(lib.b200_grad_sqnorm(ptr(x), x.numel(), ptr(want), ptr(ws), ws.numel(), side.cuda_stream), "b200_grad_sqnorm")
+    side.synchronize()
+    assert float(got) == pytest.approx(float(want), rel=1e-5)
+    assert float(got) == pytest.approx(float((x.double() ** 2).sum()), rel=1e-5)
+
+
 def test_static_scratch_rejects_oversize_and_bad_arguments():
     lib = load()
     x = torch.zeros(8, device=DEV)

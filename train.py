@@ -1,16 +1,22 @@
 """Drop-in entry point: `python train.py [group=option ...] [a.b=value ...] [-m]`.
 
 Same command line, config groups (configs/**) and printed report as the reference's train.py
-(/root/reference/train.py:70-220).  `trainer=b200` selects the B200-native path: the device batch
-generator, fused LSTM/objective/optimiser kernels and B200Trainer of `masters-thesis_b200`; any other
-trainer option is the reference's own Lightning path, which needs lightning + hydra installed (they are
-not part of this image), so it reports that instead of silently training something else.
+(/root/reference/train.py:70-220).  A trainer option from the b200 family (`trainer=b200`, `b200_fast`, `b200_slow`,
+`b200_slowest`: the files of configs/trainer/ that carry an `engine:` key) selects the B200-native path: the device
+batch generator, fused LSTM/objective/optimiser kernels and B200Trainer of `masters-thesis_b200`.
+
+Any other trainer option (`fast`, `slow`, `slowest` -- `fast` is the default of configs/config.yaml) is the
+reference's own Lightning path and is NOT re-implemented here: the untouched command line is handed to the
+reference's own train.py (`reference_fallthrough`) when a reference checkout is reachable ($B200_REFERENCE_ROOT, or a
+`src/` package next to this file) and lightning + hydra are importable.  Neither is part of this image, so here the
+default `python train.py` stops with a message that says so and names `trainer=b200`.
 
 Differences from the reference entry point, all forced by the environment:
   * no import-time dataset bootstrap: the synthetic series is a pure function of (seed, stock, day)
     evaluated on the device, and the real-data CSV bootstrap (train.py:19-28) is skipped because the raw
     files are not shipped;
-  * Hydra is used when importable, otherwise masters_thesis_b200.config composes the same groups;
+  * configuration: Hydra composes the job when it is importable (`hydra_main`); otherwise
+    masters_thesis_b200.config composes the same groups, overrides, interpolations and `-m` grids on PyYAML;
   * `-m` grids run one job after the other in this process (the reference's joblib launcher is
     configured with n_jobs: 1); sweeps/run_sweep.py spreads a grid over the 8 GPUs of a box.
 """
@@ -49,11 +55,6 @@ def run(cfg):
     print(f"Logger: {cfg.logger.name}/{cfg.logger.version}")
     print("=" * 70 + "\n")
 
-    if cfg.trainer.name != "b200" and "engine" not in cfg.trainer:
-        raise SystemExit(f"trainer={cfg.trainer.name} is the reference's Lightning path; lightning/hydra are not "
-                         "installed here.  Use trainer=b200 (optionally with trainer.max_epochs=..., "
-                         "trainer.gradient_clip_val=... to mirror fast/slow/slowest).")
-
     tcfg = cfg.trainer
     seed = int(tcfg.get("seed", 1234))
     torch.manual_seed(seed)
@@ -83,8 +84,9 @@ def run(cfg):
     trainer = b200.B200Trainer(
         max_epochs=tcfg.max_epochs, gradient_clip_val=tcfg.gradient_clip_val, precision=tcfg.precision,
         enable_progress_bar=tcfg.enable_progress_bar, enable_model_summary=tcfg.enable_model_summary,
-        max_steps=tcfg.get("max_steps", -1), seed=seed, bucket_mb=tcfg.get("bucket_mb", 0.25),
+        max_steps=tcfg.get("max_steps", -1), seed=seed, bucket_mb=tcfg.get("bucket_mb", 0.05),
         engine=tcfg.get("engine", "auto"), eval_batch_windows=tcfg.get("eval_batch_windows", 512),
+        micro_batch_windows=tcfg.get("micro_batch_windows", 4096),
         checkpoint_dir=str(run_dir / "checkpoints"), log_dir=str(run_dir), **extra)
 
     banner("Starting Training...")
@@ -97,7 +99,7 @@ def run(cfg):
 
     trainer.test(model, datamodule=dm)
 
-    config_dict = to_container(cfg)
+    config_dict = to_container(cfg)        # plain dict (resolved) from either composer
     config_dict.pop('logger', None)
     final = {'test/mae': model.test_results['test_loss']['mae'], 'test/nll': model.test_results['test_loss']['nll'],
              'test/best_val_loss': trainer.checkpoint_callback.best_model_score.item()}
@@ -122,15 +124,85 @@ def run(cfg):
     return trainer.checkpoint_callback.best_model_score.item()
 
 
+def is_b200_trainer(cfg):
+    return "engine" in cfg.trainer
+
+
+def reference_root():
+    """A checkout of the reference this entry point can hand non-b200 trainers to, or None."""
+    cands = [os.environ.get("B200_REFERENCE_ROOT"), str(Path(__file__).resolve().parent)]
+    for c in cands:
+        if c and (Path(c) / "src" / "model.py").exists() and (Path(c) / "train.py").exists() \
+                and Path(c, "train.py").resolve() != Path(__file__).resolve():
+            return Path(c)
+    return None
+
+
+def reference_fallthrough(argv, trainer_name):
+    """trainer=fast|slow|slowest: the reference's own Lightning path (/root/reference/train.py:110-187), run unmodified with
+    the same command line.  Needs the reference checkout plus lightning, hydra and torchmetrics."""
+    import importlib.util
+    import runpy
+    missing = [m for m in ("lightning", "hydra", "omegaconf", "torchmetrics") if importlib.util.find_spec(m) is None]
+    root = reference_root()
+    if missing or root is None:
+        why = []
+        if missing:
+            why.append("not installed: " + ", ".join(missing))
+        if root is None:
+            why.append("no reference checkout found (set B200_REFERENCE_ROOT)")
+        raise SystemExit(f"trainer={trainer_name} is the reference's own Lightning path, which this entry point hands to the "
+                         f"reference's train.py unchanged -- unavailable here ({'; '.join(why)}).\n"
+                         "Use the B200-native path instead:  python train.py trainer=b200   "
+                         "(b200_fast / b200_slow / b200_slowest carry the epochs, clip value and validation cadence of "
+                         "fast / slow / slowest).")
+    os.chdir(root)
+    sys.path.insert(0, str(root))
+    sys.argv = [str(root / "train.py"), *argv]
+    runpy.run_path(str(root / "train.py"), run_name="__main__")
+    return None
+
+
+def hydra_main(argv):
+    """Composition by Hydra itself (used when hydra is importable): same config directory, same resolver
+    (/root/reference/train.py:39-42, 70)."""
+    import hydra
+    from omegaconf import OmegaConf
+    if not OmegaConf.has_resolver("input_size_from_interaction"):
+        OmegaConf.register_new_resolver("input_size_from_interaction", lambda interaction_only: 3 if interaction_only else 5)
+    out = []
+
+    @hydra.main(version_base=None, config_path=str(CONFIG_DIR), config_name="config")
+    def _main(cfg):
+        if not is_b200_trainer(cfg):
+            return reference_fallthrough(argv, cfg.trainer.name)
+        out.append(run(cfg))
+        return out[-1]
+
+    sys.argv = [sys.argv[0], *argv]
+    _main()
+    return out[0] if len(out) == 1 else out
+
+
 def main(argv=None):
     argv = sys.argv[1:] if argv is None else argv
+    try:
+        import hydra  # noqa: F401
+        have_hydra = True
+    except ImportError:
+        have_hydra = False
+    if have_hydra:
+        return hydra_main(argv)
     multirun, overrides = split_cli(argv)
     jobs = expand_multirun(overrides) if multirun else [overrides]
     results = []
     for i, ov in enumerate(jobs):
         if multirun:
             print(f"[multirun] job {i + 1}/{len(jobs)}: {' '.join(ov)}")
-        results.append(run(compose_config(CONFIG_DIR, "config", ov)))
+        cfg = compose_config(CONFIG_DIR, "config", ov)
+        if not is_b200_trainer(cfg):
+            return reference_fallthrough(argv, cfg.trainer.name)
+        results.append(run(cfg))
     return results[0] if len(results) == 1 else results
 
 
