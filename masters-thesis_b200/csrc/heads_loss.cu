@@ -108,20 +108,39 @@ heads_stats_kernel(const float* __restrict__ hp, const float* __restrict__ hT, c
 }
 
 // K2 ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+// One CTA per NLL group.  In training the whole batch is ONE group (src/model.py:237-247), so this CTA alone sums
+// windows_per_group x PW doubles: 1024 threads = 16 window slices x 64 columns, four independent accumulators per thread
+// (a 256-thread version with one serial chain of 1024 dependent adds per thread took as long as the whole heads_grad
+// kernel, 70 us at 4096 windows).  Fixed order: the result does not depend on scheduling.
+constexpr int GROUP_SLICES = 16;
+__global__ void __launch_bounds__(64 * GROUP_SLICES)
 heads_group_kernel(const double* __restrict__ wpart, const float* __restrict__ factor, int S, int n, int64_t wpg,
                    bool do_nll, float* __restrict__ gstat, double* __restrict__ gloss) {
     const int PW = PW_FIXED + n;
     const int64_t g = blockIdx.x;
-    __shared__ double part[4][64];
+    __shared__ double part[GROUP_SLICES][64];
     __shared__ double tot[64];
     const int c = threadIdx.x & 63, q = threadIdx.x >> 6;
-    double v = 0.0;
-    if (c < PW)
-        for (int64_t i = q; i < wpg; i += 4) v += wpart[(g * wpg + i) * PW + c];
-    part[q][c] = v;
+    double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0;
+    if (c < PW) {
+        const double* base = wpart + g * wpg * PW + c;
+        int64_t i = q;
+        for (; i + 3 * GROUP_SLICES < wpg; i += 4 * GROUP_SLICES) {
+            v0 += base[i * PW];
+            v1 += base[(i + GROUP_SLICES) * PW];
+            v2 += base[(i + 2 * GROUP_SLICES) * PW];
+            v3 += base[(i + 3 * GROUP_SLICES) * PW];
+        }
+        for (; i < wpg; i += GROUP_SLICES) v0 += base[i * PW];
+    }
+    part[q][c] = (v0 + v1) + (v2 + v3);
     __syncthreads();
-    if (threadIdx.x < 64) tot[c] = (part[0][c] + part[1][c]) + (part[2][c] + part[3][c]);
+    if (threadIdx.x < 64) {
+        double t = 0.0;
+#pragma unroll
+        for (int k = 0; k < GROUP_SLICES; ++k) t += part[k][c];
+        tot[c] = t;
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
         double nll = 0.0;
@@ -265,7 +284,7 @@ static int heads_launch(int loss_kind, float mse_weight, const float* hp, const 
     { TimedLaunch _t("heads_stats_kernel", st); heads_stats_kernel<H><<<(unsigned)B, HEADS_THREADS, 0, st>>>(hp, hT, y_stock, y_market, factor, inv_psi, S, n, wpg,
                                                                  do_nll, al, be, ws.wpart); }
     B200_LAUNCH_CHECK("heads_stats_kernel");
-    { TimedLaunch _t("heads_group_kernel", st); heads_group_kernel<<<(unsigned)G, 256, 0, st>>>(ws.wpart, factor, S, n, wpg, do_nll, ws.gstat, ws.gloss); }
+    { TimedLaunch _t("heads_group_kernel", st); heads_group_kernel<<<(unsigned)G, 64 * GROUP_SLICES, 0, st>>>(ws.wpart, factor, S, n, wpg, do_nll, ws.gstat, ws.gloss); }
     B200_LAUNCH_CHECK("heads_group_kernel");
     const double n_elems = (double)B * S * n;
     { TimedLaunch _t("heads_final_kernel", st); heads_final_kernel<<<1, 256, 0, st>>>(ws.gloss, G, n_elems, loss_kind, mse_weight, losses_out); }

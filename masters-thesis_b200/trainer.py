@@ -123,6 +123,7 @@ class B200Trainer:
         self._tb = None
         self._sync = None
         self._comm = None
+        self._micro_cache = {}
         # optional callable(engine, global_step) invoked after the gradients of a step are complete (all-reduced under
         # data parallelism) and before clip + Adam consume them: Lightning's on_before_optimizer_step hook
         self.on_before_optimizer_step = None
@@ -159,13 +160,18 @@ class B200Trainer:
     def micro_windows(self, engine, batch_windows):
         """Windows per micro-batch: the configured cap, lowered when the device's free memory cannot hold the activation
         stash and workspaces of that many windows (engine buffers already allocated count as free)."""
+        key = (id(engine), int(batch_windows))
+        if key in self._micro_cache:                       # cudaMemGetInfo per step would sit in the launch path
+            return self._micro_cache[key]
         cap = self.micro_batch_windows or batch_windows
         free, _ = torch.cuda.mem_get_info(self.device)
         held = sum(getattr(engine, n).numel() * getattr(engine, n).element_size()
                    for n in ("stash_h", "stash_c", "lstm_ws") if hasattr(engine, n))
         fit = int(0.85 * (free + held) / engine.bytes_per_window())
         m = max(1, min(cap, batch_windows, fit))
-        return m if m >= batch_windows else max(1, m // 64 * 64 if m >= 64 else m)
+        m = m if m >= batch_windows else max(1, m // 64 * 64 if m >= 64 else m)
+        self._micro_cache[key] = m
+        return m
 
     def _writer(self):
         if self._tb is None and self.log_dir and self.rank == 0:

@@ -105,12 +105,14 @@ def check_budget(rec, loss_rtol=1e-4, grad_rtol=1e-3, metric_rtol=2e-4):
         assert abs(a - b) <= loss_rtol * abs(b), f"step {s}: device loss {a} vs oracle {b}"
     for s, g in rec["dev_grads"].items():
         r = rec["ref_grads"][s]
-        assert rel_err(g, r) < grad_rtol, f"step {s}: whole gradient vector"
-        off = 0
+        assert rel_err(g, r) < grad_rtol, f"step {s}: whole gradient vector {rel_err(g, r):.3e}"
+        off, per = 0, {}
         for name, shape in zip(rec["names"], rec["shapes"]):
             n = int(np.prod(shape))
-            assert rel_err(g[off:off + n], r[off:off + n]) < grad_rtol, f"step {s}: {name}"
+            per[name] = rel_err(g[off:off + n], r[off:off + n])
             off += n
+        bad = {k: f"{v:.3e}" for k, v in per.items() if not v < grad_rtol}
+        assert not bad, f"step {s}: per-tensor gradient error above {grad_rtol}: {bad} (all: { {k: f'{v:.1e}' for k, v in per.items()} })"
     assert abs(rec["dev_best_val"] - rec["ref_best_val"]) <= metric_rtol * abs(rec["ref_best_val"])
     for k in ("mae", "nll"):
         assert abs(rec["dev_test"][k] - rec["ref_test"][k]) <= metric_rtol * abs(rec["ref_test"][k]), k

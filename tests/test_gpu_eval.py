@@ -94,3 +94,29 @@ def test_loss_mailbox_matches_direct_reads():
     assert len(got) == 5
     for g, w in zip(got, want):
         assert g == w.cpu().tolist()
+
+
+def test_warm_start_from_synthetic_checkpoint_on_a_real_layout_series(tmp_path, monkeypatch):
+    """SURVEY.md f3, the thesis' warm-up recipe (tex/diplomski_rad.tex:1134-1147): stage 1 trains on the synthetic datamodule,
+    stage 2 continues on `datamodule=real` (here a 25-portfolio series saved in the reference's stocks.pt / market.pt
+    layout, stride 5) from stage 1's best checkpoint given as `checkpoint=`.  The second run must START from the first
+    run's parameters: with a zero learning rate its checkpoint equals stage 1's."""
+    import train as train_script
+    monkeypatch.chdir(tmp_path)
+    common = ["trainer=b200", "trainer.engine=ffma", "trainer.max_epochs=1", f"logger.save_dir={tmp_path / 'logs'}", "trainer.seed=5"]
+    train_script.main(common + ["loss=combined", "datamodule.batch_size=4", "trainer.n_samples=1800"])
+    run1 = tmp_path / "logs" / "FinancialLstm" / "synthetic" / "combined_small_lr0.0001_b200"
+    best = sorted((run1 / "checkpoints").glob("best_*.ckpt"))[-1]
+    real = tmp_path / "data" / "real"
+    real.mkdir(parents=True)
+    stocks, market = B.data.generator_series(DEV, 9, 25, 700)
+    torch.save(stocks.cpu(), real / "stocks.pt")
+    torch.save(market.cpu(), real / "market.pt")
+    train_script.main(common + ["datamodule=real", f"datamodule.data_dir={real}", "loss=mse", "datamodule.batch_size=8",
+                                "model.learning_rate=0.0", f"checkpoint={best}"])
+    run2 = tmp_path / "logs" / "FinancialLstm" / "real" / "mse_small_lr0.0_b200"
+    sd1 = torch.load(best, weights_only=False)["state_dict"]
+    sd2 = torch.load(run2 / "checkpoints" / "last.ckpt", weights_only=False)["state_dict"]
+    assert list(sd1) == list(sd2)
+    for k in sd1:
+        assert torch.equal(sd1[k], sd2[k]), k

@@ -73,6 +73,13 @@ def run(cfg):
     if cfg.loss.name == 'combined':
         model_params['mse_weight'] = cfg.loss.mse_weight
     model = ModelClass(**model_params)
+    if cfg.get("checkpoint"):
+        # Warm start (configs/config.yaml:15 `checkpoint: null`; thesis tex/diplomski_rad.tex:1134-1147 "zagrijavanje"): continue
+        # training -- typically on datamodule=real -- from the parameters of a model trained on the synthetic datamodule.
+        # Parameters only: optimiser state, learning-rate schedule and epoch counter start fresh, as in a new run.
+        state = torch.load(cfg.checkpoint, map_location="cpu", weights_only=False)
+        model.load_state_dict(state["state_dict"] if "state_dict" in state else state)
+        print(f"Warm start from checkpoint: {cfg.checkpoint}")
     model.compile()
     print(model)
     print(f"\nUsing Lightning Module: {ModelClass.__name__}\n")
