@@ -331,6 +331,9 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     H, L, p = MODELS[args.model]
     lib = _lib.load()
+    for o in args.opt:
+        k, _, v = o.partition("=")
+        _lib.check(lib.b200_set_option(k.encode(), int(v)), f"b200_set_option({o})")
     batch = per_gpu_batch(args, world)
     strong = world > 1 and not args.batch
 
@@ -490,6 +493,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (default: --steps)")
     ap.add_argument("--wide-batch", type=int, default=4096, help="windows per optimiser step of the configs[2] line")
     ap.add_argument("--dropout", type=float, default=None, help="override the model's inter-layer dropout (diagnostics)")
+    ap.add_argument("--opt", action="append", default=[], help="library tuning knob name=value (b200_set_option), repeatable")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-cpu-variants", action="store_true")

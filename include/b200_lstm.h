@@ -31,6 +31,9 @@
  *        with I_0 = F, I_l = H; gate row order i,f,g,o (torch.nn.LSTM)
  *   stash_h, stash_c  [L][T][N][H]  hidden and cell state of every layer and step
  *   hT         = stash_h + ((L-1)*T + (T-1)) * N * H      (final hidden of the top layer)
+ *        The tcgen05 engines at hidden 64 (B200_MODE_TC_*) write ONLY hT into stash_h: they keep the hidden states of all
+ *        steps inside `workspace` as bf16 hi/lo operand images that later kernels fetch with bulk copies (csrc/lstm_tc.cu);
+ *        b200_lstm_hidden_states() returns any layer's states as fp32 for every engine.  stash_c is always fp32.
  */
 #ifndef B200_LSTM_H
 #define B200_LSTM_H
@@ -137,7 +140,10 @@ B200_API int b200_dropout_mask(uint64_t seed, int layer, int64_t n_seq, int T, i
  * reducing a layer's gradients while the layers below are still running.
  *
  * training != 0 applies inter-layer dropout p with the Philox mask of b200_dropout_mask.
- * workspace: at least b200_lstm_workspace_bytes(...) bytes, shared by fwd and bwd calls of a step. */
+ * workspace: at least b200_lstm_workspace_bytes(...) bytes, shared by fwd and bwd calls of a step.  In the tcgen05 modes
+ * the forward pass leaves state in it that the backward pass of the same step reads (hidden-state operand images, dropout
+ * keep bits): pass the SAME pointer and size, untouched in between, with the same dropout_p / dropout_seed / training.
+ * A backward launch that finds keep bits of another step (seed, layer or size mismatch) aborts (CUDA launch failure). */
 B200_API size_t b200_lstm_workspace_bytes(int mode, int64_t n_seq, int T, int n_features, int hidden, int layers);
 B200_API int b200_lstm_fwd(int mode, const float* params, int n_features, int hidden, int layers,
                   const float* x, int64_t n_seq, int T, float* stash_h, float* stash_c,
@@ -156,6 +162,11 @@ B200_API int b200_lstm_bwd(int mode, const float* params, int n_features, int hi
                   const float* dhT, float* grads,
                   float dropout_p, uint64_t dropout_seed, int training,
                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Hidden states of one layer as fp32 out[T][N][H] after b200_lstm_fwd (no counterpart in the reference: lstm_out of
+ * src/model.py:104 for a lower layer): decoded from the workspace images in the tcgen05 modes, copied from stash_h otherwise. */
+B200_API int b200_lstm_hidden_states(int mode, int layer, int n_features, int hidden, int layers, int64_t n_seq, int T,
+                            const float* stash_h, const void* workspace, size_t workspace_bytes, float* out, void* stream);
 
 /* Unit test hook of the tcgen05 engine (no counterpart in the reference): one GEMM with M = 128 through the
  * same UMMA descriptors, bf16x3 split, tcgen05.mma and TMEM load path as the LSTM kernels (fp32 in/out).

@@ -79,6 +79,7 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
 int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
                  const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
                  int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+int tc_hidden_states(int mode, int layer, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st);
 // wide engine (lstm_wide.cu): hidden sizes other than 64 in the tensor-core modes
 size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L);
 int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
@@ -217,5 +218,19 @@ extern "C" int b200_lstm_bwd(int mode, const float* params, int n_features, int 
                                      dropout_p, dropout_seed, training, workspace, workspace_bytes, stream);
         if (rc) return rc;
     }
+    return B200_OK;
+}
+
+extern "C" int b200_lstm_hidden_states(int mode, int layer, int n_features, int hidden, int layers, int64_t n_seq, int T,
+                                       const float* stash_h, const void* workspace, size_t workspace_bytes, float* out, void* stream) {
+    (void)n_features;
+    B200_CHECK_ARG(mode >= 0 && mode <= 2 && layer >= 0 && layer < layers && n_seq > 0 && T > 0 && out, "lstm_hidden_states: bad arguments");
+    if (hidden == 64 && mode != B200_MODE_FFMA) {
+        B200_CHECK_ARG(workspace != nullptr, "lstm_hidden_states: the tcgen05 engines keep the hidden states in the workspace");
+        return tc_hidden_states(mode, layer, layers, n_seq, T, workspace, workspace_bytes, out, (cudaStream_t)stream);
+    }
+    B200_CHECK_ARG(stash_h != nullptr, "lstm_hidden_states: null stash");
+    const size_t lsz = (size_t)T * n_seq * hidden;
+    B200_CUDA(cudaMemcpyAsync(out, stash_h + (size_t)layer * lsz, lsz * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return B200_OK;
 }

@@ -19,8 +19,15 @@
 //     fp32 accumulate -- three tcgen05.mma per K-step, error ~2^-16 per product; NSPLIT = 1 (fast): bf16.
 // Per step and tile the tensor pipe does (KX + 64)/16 K-steps x (3 | 1) MMAs of 128x256x16.
 //
-// The stash format is the same transparent fp32 [L][T][N][H] as the CUDA-core engine, so backward can
-// run on either engine.
+// Hidden-state stash.  The cell state is kept as fp32 [L][T][N][H] (caller's stash_c).  The hidden state of every layer and
+// step is kept in OPERAND-IMAGE format inside the workspace: per (step, 128-row tile) one [128 x 64] bf16 hi image and one
+// lo image (16 KB each, UMMA interleaved K-major layout) exactly as the forward epilogue writes them to shared memory for
+// its own recurrence.  Every later consumer -- the next layer's forward (x operand), the backward kernels (the
+// [x_t | h_{t-1}] image of gate recompute and weight gradient) -- is then a cp.async.bulk copy global -> shared with
+// mbarrier complete_tx: no registers, no bf16 split, no generic-proxy stores, no proxy fence.  When inter-layer dropout
+// is on, the forward epilogue of layer l also writes the MASKED image (the input of layer l + 1) next to the plain one.
+// Only the top layer's final step is also written as fp32 into the caller's stash_h (the heads read it);
+// b200_lstm_hidden_states decodes the images for tests and tools.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -70,6 +77,12 @@ constexpr int TH = 64;              // hidden size of this engine
 constexpr int TG = 4 * TH;          // gate columns = UMMA N
 constexpr int TM = 128;             // sequences per tile = UMMA M
 constexpr int LOADER_WARPS = 2;
+constexpr uint32_t IMG_HALF = 128 * 64 * 2;          // one [128 x 64] bf16 image: 16 KB
+constexpr uint32_t IMG_TILE = 2 * IMG_HALF;          // hi image then lo image of one (step, tile)
+__host__ __device__ inline int64_t img_off(int64_t t, int64_t tile, int64_t ntiles) { return (t * ntiles + tile) * (int64_t)IMG_TILE; }
+__device__ __forceinline__ void st_global_v4u(void* p, const uint4& v) {
+    asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 constexpr int FW_EH_L0 = 1;          // forward layer 0: epilogue threads per row (see lstm_tc_fwd_kernel); 2 measured SLOWER (5.14 vs 4.83 ms)
 
 __host__ __device__ constexpr int kx_of(bool layer0) { return layer0 ? 16 : TH; }
@@ -252,8 +265,14 @@ struct FwdSmem {
 // what is missing is a third tile in flight, which TMEM (2 x 256 columns) does not allow.
 template <int NSPLIT, int NTILE, bool LAYER0, int EH>
 __global__ void __launch_bounds__(32 * (4 * NTILE * EH + LOADER_WARPS + 1), 1)
-lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
-                   float* __restrict__ h_out, float* __restrict__ c_out, const uint64_t* __restrict__ drop_bits, float p, int pf_mask) {
+lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, const uint8_t* __restrict__ ximg_in, int kin,
+                   int64_t N, int T, float* __restrict__ h_last, float* __restrict__ c_out, uint8_t* __restrict__ himg_out,
+                   uint8_t* __restrict__ ximg_out, const uint64_t* __restrict__ next_bits, float p,
+                   const uint8_t* __restrict__ zero_blk, int pf_mask) {
+    // xin: fp32 [T][N][kin] input of layer 0; ximg_in: operand images of the input of a layer > 0 (the masked images of the
+    // layer below under dropout, else its plain images).  h_last: fp32 [N][64] final hidden state (top layer) or null.
+    // himg_out: this layer's hidden-state images; ximg_out / next_bits: masked images for the layer above and the keep
+    // bits of ITS input (both null without dropout or for the top layer).
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     constexpr int KX = S::KX;
     constexpr int EPI_WARPS = 4 * NTILE * EH;
@@ -283,7 +302,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     }
     if (threadIdx.x == 0) {
         for (int s = 0; s < NTILE; ++s) {
-            mbar_init(&bars[s * 3 + 0], LOADER_WARPS);
+            mbar_init(&bars[s * 3 + 0], LAYER0 ? LOADER_WARPS : 1);      // layer > 0: one expect_tx arrival + the bulk copy's bytes
             mbar_init(&bars[s * 3 + 1], 4 * EH);
             mbar_init(&bars[s * 3 + 2], 1);
         }
@@ -319,7 +338,9 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             const int64_t tile = grp * NTILE + slot;
             const int64_t row = tile * TM + r;
-            const bool live = tile < ntiles && row < N;
+            const bool tile_live = tile < ntiles;
+            const bool live = tile_live && row < N;
+            const float inv_keep = 1.0f / (1.0f - p);
 #pragma unroll
             for (int u = 0; u < TH / EH; ++u) cst[u] = 0.f;
             for (int t = 0; t < T; ++t, ++g) {
@@ -327,8 +348,13 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 mbar_wait(acc_full, (uint32_t)(g & 1));
                 tc_fence_after();
                 if (tracer) trace_ev(0, 1, 0, g, ntr);
-                float* hdst = h_out + ((int64_t)t * N + row) * TH;
                 float* cdst = c_out + ((int64_t)t * N + row) * TH;
+                const int64_t ioff = img_off(t, tile, ntiles) + row_off;
+                uint8_t* hg = himg_out + ioff;                               // this row's 16-byte slots of the (t, tile) images
+                uint8_t* xg = ximg_out ? ximg_out + ioff : nullptr;
+                const bool h32 = h_last != nullptr && t == T - 1 && live;
+                uint64_t keep = 0ull;
+                if (xg != nullptr && live) keep = next_bits[(int64_t)t * N + row];
 #pragma unroll
                 for (int ucl = 0; ucl < UCN; ++ucl) {
                     const int uc = uh * UCN + ucl;
@@ -384,11 +410,31 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     split2(hv[6], hv[7], hi4.w, lo4.w);
                     *reinterpret_cast<uint4*>(h_hi + row_off + uc * LBO_BYTES) = hi4;
                     if (NSPLIT == 2) *reinterpret_cast<uint4*>(h_lo + row_off + uc * LBO_BYTES) = lo4;
-                    if (ucl < UCN - 1) {
-                        if (live) {
-                            st_global_v8(hdst + uc * 8, hv);
-                            st_global_v8(cdst + uc * 8, cv);
+                    // stash: the same two 16-byte slots go to the global images (all 128 rows of a live tile, so that the rows
+                    // beyond N of the last tile hold finite values); under dropout also the masked copy for the layer above
+                    auto stash = [&]() {
+                        if (tile_live) {
+                            st_global_v4u(hg + uc * LBO_BYTES, hi4);
+                            if (NSPLIT == 2) st_global_v4u(hg + IMG_HALF + uc * LBO_BYTES, lo4);
+                            if (xg != nullptr) {
+                                const uint32_t kb = (uint32_t)(keep >> (uc * 8)) & 0xFFu;
+                                float mv[8];
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) mv[j] = ((kb >> j) & 1u) ? hv[j] * inv_keep : 0.f;
+                                uint4 mh, ml;
+                                split2(mv[0], mv[1], mh.x, ml.x);
+                                split2(mv[2], mv[3], mh.y, ml.y);
+                                split2(mv[4], mv[5], mh.z, ml.z);
+                                split2(mv[6], mv[7], mh.w, ml.w);
+                                st_global_v4u(xg + uc * LBO_BYTES, mh);
+                                if (NSPLIT == 2) st_global_v4u(xg + IMG_HALF + uc * LBO_BYTES, ml);
+                            }
                         }
+                        if (live) st_global_v8(cdst + uc * 8, cv);
+                        if (h32) st_global_v8(h_last + row * TH + uc * 8, hv);
+                    };
+                    if (ucl < UCN - 1) {
+                        stash();
                     } else {
                         // last chunk: hand h_t to the tensor core first.  The proxy fence is a full memory barrier that
                         // waits for outstanding global stores, so the youngest stores are issued after it.
@@ -397,10 +443,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         __syncwarp();
                         if (lane == 0) mbar_arrive(h_ready);
                         if (tracer) trace_ev(0, 6, 0, g, ntr);
-                        if (live) {
-                            st_global_v8(hdst + uc * 8, hv);
-                            st_global_v8(cdst + uc * 8, cv);
-                        }
+                        stash();
                     }
                 }
             }
@@ -408,19 +451,17 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     } else if (warp < EPI_WARPS + LOADER_WARPS) {
         // ================================ loader: x_t operand of every slot ==================================
         const int lw = warp - EPI_WARPS;
-        const bool drop = drop_bits != nullptr;
-        const float inv_keep = 1.0f / (1.0f - p);
         int64_t g = 0;
         int ntr = 0;
         const bool tracer = lw == 0 && lane == 0;
         for (int64_t grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
             for (int t = 0; t < T; ++t, ++g) {
                 if ((pf_mask & 1) && !LAYER0 && lw == 0 && lane == 0 && t + 1 < T) {
-                    // next step's input rows of both slots -> L2 (the tiles of a group are consecutive)
-                    const int64_t r0 = grp * NTILE * TM;
-                    if (r0 < N) {
-                        const int64_t nrow = (N - r0) < NTILE * TM ? (N - r0) : NTILE * TM;
-                        prefetch_l2(xin + ((int64_t)(t + 1) * N + r0) * TH, (uint32_t)nrow * TH * 4);
+                    // next step's input images of both slots -> L2 (the tiles of a group are consecutive)
+                    const int64_t t0 = grp * NTILE;
+                    if (t0 < ntiles) {
+                        const int64_t nt = (ntiles - t0) < NTILE ? (ntiles - t0) : NTILE;
+                        prefetch_l2(ximg_in + img_off(t + 1, t0, ntiles), (uint32_t)nt * IMG_TILE);
                     }
                 }
 #pragma unroll
@@ -430,18 +471,19 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     uint8_t* x_lo = x_hi + S::XB;
                     const int64_t xuse = g * NTILE + slot;                     // running use index of the shared x buffer
                     if (!LAYER0) {
-                        // all global loads of the tile are issued before the wait for the x buffer
-                        const int64_t r0 = tile * TM;
-                        const int64_t rows_live = tile < ntiles ? N - r0 : 0;
-                        float4 v[8][4];
-                        uint64_t m[8];
-                        tile_load<8>(v, xin + ((int64_t)t * N + r0) * TH, rows_live, lw * 8, lane);
-                        if (drop) tile_load_bits<8>(m, drop_bits + (int64_t)t * N + r0, rows_live, lw * 8, lane);
-                        if (tracer) trace_ev(1, 0, slot, g, ntr);
-                        if (XSHARE) { if (xuse > 0) mbar_wait(x_free, (uint32_t)((xuse - 1) & 1)); }   // previous user's x MMAs done
-                        else if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));       // MMA of the previous step consumed x
-                        if (tracer) trace_ev(1, 1, slot, g, ntr);
-                        tile_store<NSPLIT, 8>(v, x_hi, x_lo, sbo_of(KX), 0, lw * 8, lane, drop, m, inv_keep);
+                        // x_t of a layer > 0 is the operand image the layer below stashed: ONE bulk copy (hi and lo images are adjacent
+                        // in global and in shared memory) by one thread, completion on x_full through complete_tx
+                        if (lw == 0 && lane == 0) {
+                            if (tracer) trace_ev(1, 0, slot, g, ntr);
+                            if (XSHARE) { if (xuse > 0) mbar_wait(x_free, (uint32_t)((xuse - 1) & 1)); }   // previous user's x MMAs done
+                            else if (g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));       // MMA of the previous step consumed x
+                            if (tracer) trace_ev(1, 1, slot, g, ntr);
+                            const uint8_t* src = tile < ntiles ? ximg_in + img_off(t, tile, ntiles) : zero_blk;
+                            mbar_arrive_expect_tx(&bars[slot * 3 + 0], NSPLIT * IMG_HALF);
+                            bulk_copy_g2s(x_hi, src, NSPLIT * IMG_HALF, &bars[slot * 3 + 0]);
+                            if (tracer) trace_ev(1, 2, slot, g, ntr);
+                        }
+                        continue;
                     }
                     if (LAYER0 && g > 0) mbar_wait(&bars[slot * 3 + 2], (uint32_t)((g - 1) & 1));
                     if (LAYER0) {
@@ -702,19 +744,19 @@ __device__ __forceinline__ void ld_global_vn<4>(const float* p, float (&v)[4]) {
 
 template <int NSPLIT, bool LAYER0, int XB, int DB>
 __global__ void __launch_bounds__(BW_THREADS, 1)
-lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, int kin, int64_t N, int T,
-                   const float* __restrict__ h_st, const float* __restrict__ c_st, const float* __restrict__ d_out,
+lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, const uint8_t* __restrict__ ximg_in, int kin,
+                   int64_t N, int T, const uint8_t* __restrict__ himg, const uint8_t* __restrict__ zero_blk,
+                   const float* __restrict__ c_st, const float* __restrict__ d_out,
                    const float* __restrict__ dhT, float* __restrict__ d_in, float* __restrict__ wpart,
                    float* __restrict__ bpart, const uint64_t* __restrict__ drop_bits, float p, uint64_t drop_seed, int drop_layer,
                    uint32_t drop_thr, int pf_mask) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
-    if (drop_bits != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    if (!LAYER0 && drop_bits != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+        // the keep bits (and operand images) in the workspace must be the ones the forward pass of THIS step wrote: a mismatch
+        // (foreign, reused or differently sized workspace, other seed) aborts the launch -- the caller sees a CUDA launch failure
+        // instead of gradients for other masks.  No printf here: it costs the epilogue warps registers.
         const uint64_t* tag = drop_bits + (int64_t)T * N;
-        if (tag[0] != drop_seed || tag[1] != (uint64_t)drop_layer || tag[2] != (uint64_t)N || tag[3] != drop_tag3(T, drop_thr)) {
-            printf("lstm_tc_bwd_kernel: the dropout keep bits in the workspace were not written by the forward pass of this step "
-                   "(seed/layer/size mismatch); pass the SAME workspace, untouched, to b200_lstm_fwd and b200_lstm_bwd_layer\n");
-            __trap();
-        }
+        if (tag[0] != drop_seed || tag[1] != (uint64_t)drop_layer || tag[2] != (uint64_t)N || tag[3] != drop_tag3(T, drop_thr)) __trap();
     }
     constexpr int KX = S::KX, KC = S::KC;
     // da quarter images: with two buffers (DB == 2) both quarters of a pair live in ONE [128 x 128] image (buffer b = column block
@@ -724,11 +766,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     constexpr uint32_t DA_LO = DB * S::DAB;                              // lo image after the hi image(s)
     constexpr int DH_COL0 = LAYER0 ? 0 : TH;                 // column of dh inside the d region
     constexpr int ND = LAYER0 ? TH : 2 * TH;                  // dgrad N
-    // With a single image buffer the reload sits on the critical path between two steps, exactly when the eight
-    // epilogue warps are idle: they then stage the next image themselves (2 row groups each, loads issued before the
-    // buffer is released) and the loader warps only prefetch into L2.
-    constexpr bool EPI_LOADS = (XB == 1) && !LAYER0;
-    constexpr bool ROLLQ = !EPI_LOADS;                     // see the quarter loop of the epilogue
+    // The [x_t | h_{t-1}] image is assembled by the TMA engine from the stashed operand images (1 KB per row group and part);
+    // only layer 0's 16 x-columns (fp32 input, K = 3 plus the constant-one column) are staged by the loader warps.
+    constexpr bool EPI_LOADS = false;
+    constexpr bool ROLLQ = true;                           // see the quarter loop of the epilogue
     // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
     // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -755,7 +796,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         if (LAYER0) for (int i = threadIdx.x; i < 256; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + S::off_pad)[i] = 0u;
     }
     if (threadIdx.x == 0) {
-        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], EPI_LOADS ? BW_EPI_WARPS : LOADER_WARPS); mbar_init(&xh_free[b], 2); }
+        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], LAYER0 ? LOADER_WARPS + 1 : 1); mbar_init(&xh_free[b], 2); }
         for (int b = 0; b < DB; ++b) { mbar_init(&da_full[b], BW_EPI_WARPS); mbar_init(&da_free[b], 2); }
         for (int b = 0; b < 2; ++b) { mbar_init(&a_full[b], 1); mbar_init(&a_free[b], BW_EPI_WARPS); }
         mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS); mbar_init(done, 2);
@@ -774,8 +815,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     const int64_t total_q = 4 * total_steps;
 
     // register rebalancing between warpgroups: the loader/MMA group releases registers, the epilogue groups take them
-    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(EPI_LOADS ? BW_EPI_REGS_EL : BW_EPI_REGS));
-    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(EPI_LOADS ? BW_AUX_REGS_EL : BW_AUX_REGS));
+    if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(LAYER0 ? BW_EPI_REGS : BW_EPI_REGS_EL));
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(LAYER0 ? BW_AUX_REGS : BW_AUX_REGS_EL));
 
     if (warp < BW_EPI_WARPS) {
         // ===================================== epilogue warps =====================================================
@@ -827,29 +868,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         int ntr = 0;
         const bool tracer = warp == 0 && lane == 0;
         const int dbg = TC_DBG();
-        // EPI_LOADS: this warp stages its share of the row groups of the [x | h] image of step (tile_n, t_n); the image of
-        // running step g_n may be written once the MMAs of step g_n - 1 have released the (single) buffer
-        auto stage_image = [&](int64_t tile_n, int t_n, int64_t g_n) {
-            constexpr int RG = 16 / BW_EPI_WARPS;                            // row groups per warp
-            const int64_t r0 = tile_n * TM;
-            const int64_t rows_live = N - r0;
-            uint8_t* xh_hi = smem + S::off_xh;
-            uint8_t* xh_lo = xh_hi + S::XHB;
-            float4 vx[RG][4], vh[RG][4];
-            uint64_t m[RG];
-#pragma unroll
-            for (int i = 0; i < RG; ++i) m[i] = 0ull;
-            tile_load<RG>(vx, xin + ((int64_t)t_n * N + r0) * TH, rows_live, RG * warp, lane);
-            tile_load<RG>(vh, h_st + ((int64_t)(t_n > 0 ? t_n - 1 : 0) * N + r0) * TH, t_n > 0 ? rows_live : 0, RG * warp, lane);
-            if (drop) tile_load_bits<RG>(m, drop_bits + (int64_t)t_n * N + r0, rows_live, RG * warp, lane);
-            if (g_n > 0) mbar_wait(&xh_free[0], (uint32_t)((g_n - 1) & 1));
-            tile_store<NSPLIT, RG>(vx, xh_hi, xh_lo, SBO_W, 0, RG * warp, lane, drop, m, inv_keep);
-            tile_store<NSPLIT, RG>(vh, xh_hi, xh_lo, SBO_W, KX, RG * warp, lane, false, m, 1.f);
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&xh_full[0]);
-        };
-        if (EPI_LOADS && blockIdx.x < ntiles) stage_image(blockIdx.x, T - 1, 0);
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int64_t row = tile * TM + r;
             const bool live = row < N;
@@ -988,10 +1006,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         db[0] = db[1]; db[1] = db[2]; db[2] = db[3]; db[3] = t2;
                     }
                 }
-                if (EPI_LOADS) {
-                    if (t > 0) stage_image(tile, t - 1, g + 1);
-                    else if (tile + gridDim.x < ntiles) stage_image(tile + gridDim.x, T - 1, g + 1);
-                }
             }
             read_back(g - 1, row, live, 0);                 // dx_0 of this tile; releases d for the next tile
         }
@@ -1032,53 +1046,59 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         }
     } else if (warp < BW_EPI_WARPS + LOADER_WARPS) {
         // ===================================== loader warps =======================================================
+        // Warp 0, lanes 0..15: one row group each of the [x_t | h_{t-1}] image -- bulk copies of the 1 KB row-group slices of
+        // the stashed hi / lo images (h_{t-1} of this layer; for layers > 0 also x_t = the images of the layer below) into
+        // their columns of the combined image; completion through complete_tx on xh_full.  Layer 0: both warps stage the
+        // 16 x-columns from the fp32 input.
         const int lw = warp - BW_EPI_WARPS;
-        const bool drop = drop_bits != nullptr;
-        const float inv_keep = 1.0f / (1.0f - p);
         const int rg_r = tile_rr(lane), qq = tile_q(lane);
         int64_t g = 0;
         int ntr = 0;
         const bool tracer = lw == 0 && lane == 0;
+        constexpr uint32_t XH_TX = NSPLIT * TM * TH * 2 * (LAYER0 ? 1 : 2);      // bytes the bulk copies deliver per image
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int64_t r0 = tile * TM;
             const int64_t rows_live = N - r0;
             for (int t = T - 1; t >= 0; --t, ++g) {
                 if (tracer) trace_ev(1, 0, 0, g, ntr);
                 const int pf = pf_mask;
-                if (EPI_LOADS && (pf & 28) && lw == 0 && lane == 0) {
-                    // time the prefetch into the middle of the step (after its second quarter): at the step boundary the epilogue
-                    // warps' image loads are on the critical path and a 128 KB L2 fill in front of them costs more than it saves
+                if (XB == 1 && (pf & 28) && lw == 0 && lane == 0) {
+                    // single image buffer: time the L2 prefetch of the next image into the middle of the step (after its second quarter)
                     mbar_wait(&da_full[0], 0u);
                     mbar_wait(&da_full[0], 1u);
                 }
                 if ((LAYER0 ? (pf & 2) : (pf & 60)) && lw == 0 && lane == 0 && t >= 1) {
-                    // pull the NEXT step's rows (x_{t-1}, h_{t-2}, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
+                    // pull the NEXT step's operands (x_{t-1}, h_{t-2} images, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
                     const int64_t nrow = rows_live < TM ? rows_live : TM;
                     const uint32_t rb = (uint32_t)nrow * TH * 4;
-                    if (!LAYER0 && (pf & 4)) prefetch_l2(xin + ((int64_t)(t - 1) * N + r0) * TH, rb);
+                    if (!LAYER0 && (pf & 4)) prefetch_l2(ximg_in + img_off(t - 1, tile, ntiles), NSPLIT * IMG_HALF);
                     if (t >= 2) {
-                        if (LAYER0 || (pf & 8)) prefetch_l2(h_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
+                        if (LAYER0 || (pf & 8)) prefetch_l2(himg + img_off(t - 2, tile, ntiles), NSPLIT * IMG_HALF);
                         if (LAYER0 || (pf & 16)) prefetch_l2(c_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
                     }
                     if (d_out && (pf & 32)) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
                 }
-                if (EPI_LOADS) continue;               // the epilogue warps stage the image; this warp only prefetches
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
-                // batches of 2 row groups (32 registers: this warpgroup runs on a small register budget); the first batch
-                // is in flight while we wait for the buffer
-                uint64_t m[2] = {0ull, 0ull};
-                float4 v[2][4];
-                const float* hsrc = h_st + ((int64_t)(t > 0 ? t - 1 : 0) * N + r0) * TH;
-                const int64_t h_live = t > 0 ? rows_live : 0;
-                tile_load<2>(v, hsrc, h_live, lw * 8, lane);
+                if (!LAYER0 && lw != 0) continue;
                 if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
                 if (tracer) trace_ev(1, 1, 0, g, ntr);
-#pragma unroll 1
-                for (int b2 = 0; b2 < 4; ++b2) {
-                    if (b2 > 0) tile_load<2>(v, hsrc, h_live, lw * 8 + 2 * b2, lane);
-                    tile_store<NSPLIT, 2>(v, xh_hi, xh_lo, SBO_W, KX, lw * 8 + 2 * b2, lane, false, m, 1.f);
+                if (lw == 0) {
+                    if (lane == 0) mbar_arrive_expect_tx(&xh_full[buf], XH_TX);
+                    __syncwarp();
+                    if (lane < 16) {
+                        const uint8_t* hsrc = (t > 0 ? himg + img_off(t - 1, tile, ntiles) : zero_blk) + (uint32_t)lane * 1024u;
+                        uint8_t* dh_ = xh_hi + (uint32_t)lane * SBO_W + (uint32_t)(KX / 8) * LBO_BYTES;
+                        bulk_copy_g2s(dh_, hsrc, 1024u, &xh_full[buf]);
+                        if (NSPLIT == 2) bulk_copy_g2s(dh_ + S::XHB, hsrc + IMG_HALF, 1024u, &xh_full[buf]);
+                        if (!LAYER0) {
+                            const uint8_t* xsrc = ximg_in + img_off(t, tile, ntiles) + (uint32_t)lane * 1024u;
+                            uint8_t* dx_ = xh_hi + (uint32_t)lane * SBO_W;
+                            bulk_copy_g2s(dx_, xsrc, 1024u, &xh_full[buf]);
+                            if (NSPLIT == 2) bulk_copy_g2s(dx_ + S::XHB, xsrc + IMG_HALF, 1024u, &xh_full[buf]);
+                        }
+                    }
                 }
                 if (LAYER0) {
                     // x part: 16 columns, lane quarter qq covers columns 4qq .. 4qq+3 of its row
@@ -1103,19 +1123,10 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         *reinterpret_cast<uint2*>(xh_hi + o) = hi2;
                         if (NSPLIT == 2) *reinterpret_cast<uint2*>(xh_lo + o) = lo2;
                     }
-                } else {
-                    const float* xsrc = xin + ((int64_t)t * N + r0) * TH;
-                    const uint64_t* bsrc = drop_bits + (int64_t)t * N + r0;
-#pragma unroll 1
-                    for (int b2 = 0; b2 < 4; ++b2) {
-                        tile_load<2>(v, xsrc, rows_live, lw * 8 + 2 * b2, lane);
-                        if (drop) tile_load_bits<2>(m, bsrc, rows_live, lw * 8 + 2 * b2, lane);
-                        tile_store<NSPLIT, 2>(v, xh_hi, xh_lo, SBO_W, 0, lw * 8 + 2 * b2, lane, drop, m, inv_keep);
-                    }
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&xh_full[buf]);
                 }
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&xh_full[buf]);
                 if (tracer) trace_ev(1, 2, 0, g, ntr);
             }
         }
@@ -1360,21 +1371,38 @@ static size_t tc_fwd_pack_total(int L) {
     return tot;
 }
 static size_t tc_bits_bytes(int64_t N, int T) { return (((size_t)T * N * 8 + 255) & ~(size_t)255) + 256; }   // + tag
-// tail of the workspace: dropout keep bits of layers 1..L-1, forward packs, one backward pack
+static size_t tc_img_bytes(int64_t N, int T) { return (size_t)T * (size_t)((N + TM - 1) / TM) * IMG_TILE; }   // images of one layer
+// tail of the workspace: hidden-state images of every layer, masked input images of layers 1..L-1, a zero image,
+// dropout keep bits of layers 1..L-1, forward packs, one backward pack
 static size_t tc_tail_total(int64_t N, int T, int L) {
-    return (size_t)(L - 1) * tc_bits_bytes(N, T) + tc_fwd_pack_total(L) + ((bwd_pack_bytes(false) + 255) & ~(size_t)255);
+    return (size_t)(2 * L - 1) * tc_img_bytes(N, T) + IMG_TILE + (size_t)(L - 1) * tc_bits_bytes(N, T) + tc_fwd_pack_total(L) +
+           ((bwd_pack_bytes(false) + 255) & ~(size_t)255);
 }
 struct TcTail {
-    uint64_t* bits;      // [L-1][T][N]
+    uint8_t* himg;       // [L] images of h
+    uint8_t* ximg;       // [L-1] masked images: input of layers 1..L-1 under dropout
+    uint8_t* zero;       // one all-zero image (h_{-1}, dead tiles)
+    uint64_t* bits;      // [L-1][T][N] (+ tag)
     uint8_t* fwd_packs;
     uint8_t* bwd_pack;
+    size_t img_bytes;
     size_t usable;       // bytes in front of the tail (dx buffers, partial gradients)
 };
 static bool tc_tail(void* workspace, size_t ws_bytes, int64_t N, int T, int L, TcTail* t) {
     const size_t tail = tc_tail_total(N, T, L);
-    if (ws_bytes <= tail + 256) return false;
-    t->usable = (ws_bytes - tail) & ~(size_t)255;
-    uint8_t* p = (uint8_t*)workspace + t->usable;
+    if (ws_bytes <= tail + 1280) return false;
+    // the tail starts on a 1 KB boundary (bulk copies need 16-byte aligned sources; keep whole images aligned)
+    uint8_t* end = (uint8_t*)workspace + ws_bytes;
+    uint8_t* p = (uint8_t*)(((uintptr_t)(end - tail)) & ~(uintptr_t)1023);
+    if (p <= (uint8_t*)workspace) return false;
+    t->usable = (size_t)(p - (uint8_t*)workspace);
+    t->img_bytes = tc_img_bytes(N, T);
+    t->himg = p;
+    p += (size_t)L * t->img_bytes;
+    t->ximg = p;
+    p += (size_t)(L - 1) * t->img_bytes;
+    t->zero = p;
+    p += IMG_TILE;
     t->bits = (uint64_t*)p;
     p += (size_t)(L - 1) * tc_bits_bytes(N, T);
     t->fwd_packs = p;
@@ -1385,12 +1413,13 @@ static bool tc_tail(void* workspace, size_t ws_bytes, int64_t N, int T, int L, T
 // workspace = [dx buffers, partial gradients (layout shared with the CUDA-core engine)][tail]
 size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L) {
     (void)mode; (void)F; (void)H;
-    return ((ffma_workspace_bytes(N, T, L) + 255) & ~(size_t)255) + tc_tail_total(N, T, L) + 512;
+    return ((ffma_workspace_bytes(N, T, L) + 255) & ~(size_t)255) + tc_tail_total(N, T, L) + 2048;
 }
 
 template <int NSPLIT, int NTILE, bool LAYER0, int EH>
-static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, float* h_out, float* c_out,
-                      const uint64_t* drop_bits, float p, cudaStream_t st) {
+static int launch_fwd(const uint8_t* packed, const float* xin, const uint8_t* ximg_in, int kin, int64_t N, int T, float* h_last,
+                      float* c_out, uint8_t* himg_out, uint8_t* ximg_out, const uint64_t* next_bits, float p, const uint8_t* zero,
+                      cudaStream_t st) {
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     auto kern = lstm_tc_fwd_kernel<NSPLIT, NTILE, LAYER0, EH>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
@@ -1399,7 +1428,8 @@ static int launch_fwd(const uint8_t* packed, const float* xin, int kin, int64_t 
     const int threads = 32 * (4 * NTILE * EH + LOADER_WARPS + 1);
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_fwd_kernel_l0" : "lstm_tc_fwd_kernel_lN", st);
-        kern<<<grid, threads, S::total, st>>>(packed, xin, kin, N, T, h_out, c_out, drop_bits, p, g_tc_prefetch);
+        kern<<<grid, threads, S::total, st>>>(packed, xin, ximg_in, kin, N, T, h_last, c_out, himg_out, ximg_out, next_bits, p, zero,
+                                              g_tc_prefetch);
     }
     B200_LAUNCH_CHECK("lstm_tc_fwd_kernel");
     return B200_OK;
@@ -1416,6 +1446,17 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
     const bool drop = training && p > 0.f;
     const int64_t lsz = (int64_t)T * N * TH;
     const bool precise = mode == B200_MODE_TC_PRECISE;
+    B200_CUDA(cudaMemsetAsync(tail.zero, 0, IMG_TILE, st));
+    const size_t bits_stride = tc_bits_bytes(N, T) / 8;
+    if (drop) {
+        // keep bits of the inputs of layers 1..L-1: the forward epilogue of the layer BELOW applies them when it writes the
+        // masked images, so they are all built before the first layer runs
+        for (int l = 1; l < L; ++l) {
+            TimedLaunch _t("tc_dropout_bits_kernel", st);
+            tc_dropout_bits_kernel<<<num_sms() * 8, 256, 0, st>>>(seed, l, N, T, dropout_threshold(p), tail.bits + (size_t)(l - 1) * bits_stride);
+        }
+        B200_LAUNCH_CHECK("tc_dropout_bits_kernel");
+    }
     for (int l = 0; l < L; ++l) {
         const int kin = l == 0 ? F : TH;
         const float* base = params + b200_param_offset(F, TH, L, l);
@@ -1425,23 +1466,21 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
         const float* b_hh = b_ih + TG;
         { TimedLaunch _t("tc_pack_weights_kernel", st); tc_pack_weights_kernel<<<32, 256, 0, st>>>(w_ih, w_hh, b_ih, b_hh, kin, kx_of(l == 0), pk); }
         B200_LAUNCH_CHECK("tc_pack_weights_kernel");
-        const float* xin = l == 0 ? x : stash_h + (l - 1) * lsz;
-        float* ho = stash_h + l * lsz;
         float* co = stash_c + l * lsz;
-        const uint64_t* bits = nullptr;
-        if (l > 0 && drop) {
-            uint64_t* b = tail.bits + (size_t)(l - 1) * (tc_bits_bytes(N, T) / 8);
-            { TimedLaunch _t("tc_dropout_bits_kernel", st); tc_dropout_bits_kernel<<<num_sms() * 8, 256, 0, st>>>(seed, l, N, T, dropout_threshold(p), b); }
-            B200_LAUNCH_CHECK("tc_dropout_bits_kernel");
-            bits = b;
-        }
+        float* h_last = l == L - 1 ? stash_h + ((int64_t)l * T + (T - 1)) * N * TH : nullptr;     // fp32 final hidden state for the heads
+        uint8_t* himg_out = tail.himg + (size_t)l * tail.img_bytes;
+        const bool mask_next = drop && l < L - 1;
+        uint8_t* ximg_out = mask_next ? tail.ximg + (size_t)l * tail.img_bytes : nullptr;          // input images of layer l + 1
+        const uint64_t* next_bits = mask_next ? tail.bits + (size_t)l * bits_stride : nullptr;
+        // input of a layer > 0: the masked images under dropout, else the plain images of the layer below
+        const uint8_t* ximg_in = l == 0 ? nullptr : (drop ? tail.ximg + (size_t)(l - 1) * tail.img_bytes : tail.himg + (size_t)(l - 1) * tail.img_bytes);
         int rc;
         if (l == 0) {
-            rc = precise ? launch_fwd<2, 2, true, FW_EH_L0>(pk, xin, kin, N, T, ho, co, nullptr, p, st)
-                         : launch_fwd<1, 2, true, FW_EH_L0>(pk, xin, kin, N, T, ho, co, nullptr, p, st);
+            rc = precise ? launch_fwd<2, 2, true, FW_EH_L0>(pk, x, nullptr, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st)
+                         : launch_fwd<1, 2, true, FW_EH_L0>(pk, x, nullptr, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st);
         } else {
-            rc = precise ? launch_fwd<2, 2, false, 1>(pk, xin, kin, N, T, ho, co, bits, p, st)
-                         : launch_fwd<1, 2, false, 1>(pk, xin, kin, N, T, ho, co, bits, p, st);
+            rc = precise ? launch_fwd<2, 2, false, 1>(pk, nullptr, ximg_in, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st)
+                         : launch_fwd<1, 2, false, 1>(pk, nullptr, ximg_in, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st);
         }
         if (rc) return rc;
         pk += (pack_bytes(l == 0) + 255) & ~(size_t)255;
@@ -1450,16 +1489,16 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
 }
 
 template <int NSPLIT, bool LAYER0, int XB, int DB>
-static int launch_bwd(const uint8_t* packed, const float* xin, int kin, int64_t N, int T, const float* h_st, const float* c_st,
-                      const float* d_out, const float* dhT, float* d_in, float* wpart, float* bpart, const uint64_t* drop_bits,
-                      float p, uint64_t seed, int layer, int grid, cudaStream_t st) {
+static int launch_bwd(const uint8_t* packed, const float* xin, const uint8_t* ximg_in, int kin, int64_t N, int T, const uint8_t* himg,
+                      const uint8_t* zero, const float* c_st, const float* d_out, const float* dhT, float* d_in, float* wpart,
+                      float* bpart, const uint64_t* drop_bits, float p, uint64_t seed, int layer, int grid, cudaStream_t st) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     auto kern = lstm_tc_bwd_kernel<NSPLIT, LAYER0, XB, DB>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_bwd_kernel_l0" : "lstm_tc_bwd_kernel_lN", st);
-        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, drop_bits, p, seed, layer,
-                                                 dropout_threshold(p), g_tc_prefetch);
+        kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, ximg_in, kin, N, T, himg, zero, c_st, d_out, dhT, d_in, wpart, bpart, drop_bits,
+                                                 p, seed, layer, dropout_threshold(p), g_tc_prefetch);
     }
     B200_LAUNCH_CHECK("lstm_tc_bwd_kernel");
     return B200_OK;
@@ -1469,6 +1508,7 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
                  const float* stash_h, const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed,
                  int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
     if (H != TH) { set_error("tcgen05 engine supports hidden=64 only, got %d", H); return B200_ERR_UNSUPPORTED; }
+    (void)stash_h;           // the hidden states live in the workspace as operand images (written by tc_fwd)
     TcTail tail;
     B200_CHECK_ARG(tc_tail(workspace, ws_bytes, N, T, L, &tail), "lstm_bwd (tcgen05): workspace too small (%zu bytes)", ws_bytes);
     float *dx0, *dx1, *wpart, *bpart;
@@ -1488,8 +1528,8 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     B200_LAUNCH_CHECK("tc_pack_bwd_weights_kernel");
     const bool drop = training && p > 0.f;
     const int64_t lsz = (int64_t)T * N * TH;
-    const float* xin = layer0 ? x : stash_h + (layer - 1) * lsz;
-    const float* h_st = stash_h + layer * lsz;
+    const uint8_t* himg = tail.himg + (size_t)layer * tail.img_bytes;
+    const uint8_t* ximg_in = layer0 ? nullptr : (drop ? tail.ximg + (size_t)(layer - 1) * tail.img_bytes : tail.himg + (size_t)(layer - 1) * tail.img_bytes);
     const float* c_st = stash_c + layer * lsz;
     const float* d_out = layer == L - 1 ? nullptr : dx[(layer + 1) & 1];
     float* d_in = layer0 ? nullptr : dx[layer & 1];
@@ -1500,11 +1540,11 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     // the tag behind them against (seed, layer, N, T, p) and aborts on a mismatch
     const uint64_t* bits = (!layer0 && drop) ? tail.bits + (size_t)(layer - 1) * (tc_bits_bytes(N, T) / 8) : nullptr;
     if (layer0)
-        rc = precise ? launch_bwd<2, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, st)
-                     : launch_bwd<1, true, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, st);
+        rc = precise ? launch_bwd<2, true, 2, 2>(pk, x, nullptr, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, st)
+                     : launch_bwd<1, true, 2, 2>(pk, x, nullptr, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, st);
     else
-        rc = precise ? launch_bwd<2, false, 1, 1>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, st)
-                     : launch_bwd<1, false, 2, 2>(pk, xin, kin, N, T, h_st, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, st);
+        rc = precise ? launch_bwd<2, false, 1, 1>(pk, nullptr, ximg_in, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, st)
+                     : launch_bwd<1, false, 2, 2>(pk, nullptr, ximg_in, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, st);
     if (rc) return rc;
     float* gbase = grads + b200_param_offset(F, TH, L, layer);
     float* gw_ih = gbase;
@@ -1512,6 +1552,38 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     float* gb_ih = gw_hh + (int64_t)TG * TH;
     float* gb_hh = gb_ih + TG;
     return launch_grad_reduce(wpart, grid, bpart, grid * 4, kin, kx_of(layer0), gw_ih, gw_hh, gb_ih, gb_hh, st);
+}
+
+// operand images -> fp32 [T][N][64] (hi + lo): tests and tools
+__global__ void __launch_bounds__(256)
+tc_unpack_images_kernel(const uint8_t* __restrict__ img, int64_t N, int T, int nsplit, float* __restrict__ out) {
+    const int64_t ntiles = (N + TM - 1) / TM;
+    const int64_t total = (int64_t)T * N * (TH / 8);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int kg = (int)(i % (TH / 8));
+        const int64_t row = (i / (TH / 8)) % N;
+        const int64_t t = i / ((TH / 8) * N);
+        const int r = (int)(row % TM);
+        const uint8_t* src = img + img_off(t, row / TM, ntiles) + (uint32_t)(r >> 3) * 1024u + (uint32_t)kg * LBO_BYTES + (uint32_t)(r & 7) * 16u;
+        const uint4 hi = *reinterpret_cast<const uint4*>(src);
+        uint4 lo = make_uint4(0, 0, 0, 0);
+        if (nsplit == 2) lo = *reinterpret_cast<const uint4*>(src + IMG_HALF);
+        const uint32_t hw[4] = {hi.x, hi.y, hi.z, hi.w}, lw[4] = {lo.x, lo.y, lo.z, lo.w};
+        float* dst = out + (t * N + row) * TH + kg * 8;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            dst[2 * j] = __uint_as_float(hw[j] << 16) + __uint_as_float(lw[j] << 16);
+            dst[2 * j + 1] = __uint_as_float(hw[j] & 0xFFFF0000u) + __uint_as_float(lw[j] & 0xFFFF0000u);
+        }
+    }
+}
+
+int tc_hidden_states(int mode, int layer, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st) {
+    TcTail tail;
+    B200_CHECK_ARG(tc_tail(const_cast<void*>(workspace), ws_bytes, N, T, L, &tail), "lstm_hidden_states (tcgen05): workspace too small (%zu bytes)", ws_bytes);
+    tc_unpack_images_kernel<<<num_sms() * 8, 256, 0, st>>>(tail.himg + (size_t)layer * tail.img_bytes, N, T, mode == B200_MODE_TC_PRECISE ? 2 : 1, out);
+    B200_LAUNCH_CHECK("tc_unpack_images_kernel");
+    return B200_OK;
 }
 
 }  // namespace b200

@@ -82,6 +82,14 @@ class LstmEngine:
         self.launches += self.L
         self._N = N
 
+    def hidden_states(self, layer, n_windows):
+        """fp32 [T][N][H] hidden states of one layer after forward() (lstm_out of src/model.py:104 for that layer)."""
+        N = n_windows * self.S
+        out = torch.empty(self.T, N, self.H, dtype=torch.float32, device=self.device)
+        check(self.lib.b200_lstm_hidden_states(self.mode, int(layer), self.F, self.H, self.L, N, self.T, ptr(self.stash_h),
+                                               ptr(self.lstm_ws), self.lstm_ws.numel(), ptr(out), self.stream), "b200_lstm_hidden_states")
+        return out
+
     def final_hidden(self, n_windows):
         N = n_windows * self.S
         off = ((self.L - 1) * self.T + (self.T - 1)) * N * self.H

@@ -5,7 +5,7 @@ metrics over a fixed step budget; reference loop: train.py:187, src/model.py:204
 The device generator is authoritative for the inputs: every chunk the oracle sees is the device's
 own batch copied to the host in the reference layout.  Dropout masks come from b200_dropout_mask, which a separate test
 pins bit-exactly against the written numpy specification.  Large batches are accumulated on the CPU over chunks of at
-most 256 windows (exact for the mse objective: a mean over rows)."""
+most 32 windows (exact for the mse objective: a mean over rows)."""
 import os
 
 import numpy as np
@@ -28,10 +28,16 @@ def device_masks(seed, layers, n_seq, p, dev):
     return out
 
 
-def oracle_accumulated_step(om, em, src, first_window, n_windows, kind, masks, chunk=256):
-    """Loss and gradients (left in p.grad) of one batch, accumulated over chunks of <= `chunk` windows."""
+def oracle_accumulated_step(om, em, src, first_window, n_windows, kind, masks, chunk=32):
+    """Loss and gradients (left in p.grad) of one batch, accumulated over chunks of <= `chunk` windows.
+
+    The chunk gradients are summed in fp64.  Chunks are SMALL on purpose: oneDNN's fp32 LSTM backward sums the bias
+    gradient of a chunk over rows x steps in fp32, and at 256 windows (1.5 M terms) that sum alone is off by 1-2e-3 of the
+    largest bias gradient against an fp64 evaluation of the same network (tools/fullsize_grad_diag.py: CPU fp32 1.8e-3,
+    device 2.4e-4 at 4096 windows) -- more than the 1e-3 gate this harness checks."""
     om.zero_grad()
     total = 0.0
+    acc = [torch.zeros_like(p_, dtype=torch.float64) for p_ in om.parameters()]
     for lo in range(0, n_windows, chunk):
         nb = min(chunk, n_windows - lo)
         ref = [t.cpu() for t in src.generate(first_window=first_window + lo, n_windows=nb).to_reference()]
@@ -41,8 +47,13 @@ def oracle_accumulated_step(om, em, src, first_window, n_windows, kind, masks, c
             fwd = lambda x, _mk=mk: em(x, _mk)
         ls = O.batch_losses(om, ref, kind, forward=fwd)
         w = nb / n_windows
+        om.zero_grad()
         (ls["total"] * w).backward()
-        total += float(ls["total"]) * w
+        for a, p_ in zip(acc, om.parameters()):
+            a += p_.grad.double()
+        total += float(ls["total"].detach()) * w
+    for a, p_ in zip(acc, om.parameters()):
+        p_.grad = a.float()
     return total
 
 

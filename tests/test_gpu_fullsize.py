@@ -20,8 +20,8 @@ def test_full_size_step_properties(engine):
     if not load().b200_mode_available(B.MODES[engine]):
         pytest.skip("tcgen05 engine unavailable")
     free, _ = torch.cuda.mem_get_info(0)
-    if free < 90e9:
-        pytest.skip("needs ~75 GB of device memory")
+    if free < 110e9:
+        pytest.skip("needs ~95 GB of device memory")
     torch.manual_seed(7)
     model = B.FinancialLstmMse(3, 64, 2, 0.0, 1e-4)
     flat = model.flat_parameters().clone()
@@ -67,14 +67,14 @@ def test_full_size_step_properties(engine):
 def test_full_size_fixed_budget_vs_oracle():
     """The headline configuration under the north_star gate, on the engine and through the object the bench uses
     (BASELINE.json configs[1]: small model, mse, dropout 0.2, 4096 windows = 409,600 sequences per step, tc_precise,
-    B200Trainer): five optimisation steps against the CPU oracle accumulated over 256-window chunks on the same windows and
+    B200Trainer): five optimisation steps against the CPU oracle accumulated over 32-window chunks (fp64 sums across chunks) on the same windows and
     the same Philox dropout masks -- per-step loss within 1e-4 relative, the FULL step-0 gradient within 1e-3 (whole
     vector and per tensor), then best_val_loss, test mae and test nll (train.py:204-211) and the final parameters."""
     if not load().b200_mode_available(B.MODES["tc_precise"]):
         pytest.skip("tcgen05 engine unavailable")
     free, _ = torch.cuda.mem_get_info(0)
-    if free < 100e9:
-        pytest.skip("needs ~85 GB of device memory")
+    if free < 120e9:
+        pytest.skip("needs ~105 GB of device memory")
     from _budget import check_budget, run_budget
     rec = run_budget(DEV, BW, 5, 0.2, engine="tc_precise", kind="mse", want_grads_at=(0,))
     check_budget(rec)

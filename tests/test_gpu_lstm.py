@@ -27,7 +27,7 @@ def data(golden_dir):
 
 def _stash(e, n_windows):
     N = n_windows * e.S
-    return e.stash_h[: e.L * e.T * N * e.H].reshape(e.L, e.T, N, e.H), e.stash_c[: e.L * e.T * N * e.H].reshape(e.L, e.T, N, e.H)
+    return [e.hidden_states(l, n_windows) for l in range(e.L)], e.stash_c[: e.L * e.T * N * e.H].reshape(e.L, e.T, N, e.H)
 
 
 @pytest.mark.parametrize("engine", ENGINES)
