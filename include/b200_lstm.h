@@ -81,7 +81,7 @@ B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
 
 /* Tuning knobs for experiments (no counterpart in the reference); process-wide, read at launch time, defaults are
  * the measured best.  The library reads no environment variables.
- *   "tc_prefetch"  bit mask of L2 prefetches in the tcgen05 kernels (csrc/lstm_tc.cu, default 35)
+ *   "tc_prefetch"  bit mask of L2 prefetches in the tcgen05 kernels (csrc/lstm_tc.cu, default 39)
  *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM (default 0) */
 B200_API int b200_set_option(const char* name, int value);
 

@@ -402,7 +402,7 @@ lstm_ffma_wgrad_kernel(LayerGeom g, const float* __restrict__ xin, int64_t N, in
 // partials -> the layer's slice of the flat gradient vector (fixed summation order)
 __global__ void __launch_bounds__(256)
 lstm_grad_reduce_kernel(const float* __restrict__ wpart, int nsplit, const float* __restrict__ bpart, int nbpart, int kin,
-                        int kp, float* __restrict__ gw_ih, float* __restrict__ gw_hh, float* __restrict__ gb_ih,
+                        int kp, float ih_scale, float* __restrict__ gw_ih, float* __restrict__ gw_hh, float* __restrict__ gb_ih,
                         float* __restrict__ gb_hh) {
     const int n_ih = LG * kin, n_hh = LG * LH;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -413,7 +413,7 @@ lstm_grad_reduce_kernel(const float* __restrict__ wpart, int nsplit, const float
         else { int i = idx - n_ih; j = i / LH; k = kp + (i - j * LH); dst = gw_hh + i; }
         float s = 0.f;
         for (int sp = 0; sp < nsplit; ++sp) s += wpart[((int64_t)sp * LG + j) * 128 + k];
-        *dst = s;
+        *dst = idx < n_ih ? s * ih_scale : s;        // ih_scale: a factor folded into the packed W_ih by the caller (tcgen05 dropout), else 1
     } else if (idx < n_ih + n_hh + LG) {
         const int j = idx - n_ih - n_hh;
         float s = 0.f;
@@ -488,10 +488,10 @@ int ffma_ws_pointers(int64_t N, int T, int L, void* workspace, size_t ws_bytes, 
     return B200_OK;
 }
 
-int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float* gw_ih,
+int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float ih_scale, float* gw_ih,
                        float* gw_hh, float* gb_ih, float* gb_hh, cudaStream_t st) {
     const int total = LG * kin + LG * LH + LG;
-    { TimedLaunch _t("lstm_grad_reduce_kernel", st); lstm_grad_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, nsplit, bpart, nbpart, kin, kp, gw_ih, gw_hh, gb_ih, gb_hh); }
+    { TimedLaunch _t("lstm_grad_reduce_kernel", st); lstm_grad_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(wpart, nsplit, bpart, nbpart, kin, kp, ih_scale, gw_ih, gw_hh, gb_ih, gb_hh); }
     B200_LAUNCH_CHECK("lstm_grad_reduce_kernel");
     return B200_OK;
 }
@@ -574,7 +574,7 @@ int ffma_bwd_layer(int layer, const float* params, int F, int H, int L, const fl
     float* gb_hh = gb_ih + LG;
     const int total = LG * g.kin + LG * LH + LG;
     { TimedLaunch _t("lstm_grad_reduce_kernel", st); lstm_grad_reduce_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws.wpart, ws.nsplit, ws.bpart, ws.bwd_grid * L_WARPS, g.kin, g.kp,
-                                                                 gw_ih, gw_hh, gb_ih, gb_hh); }
+                                                                 1.0f, gw_ih, gw_hh, gb_ih, gb_hh); }
     B200_LAUNCH_CHECK("lstm_grad_reduce_kernel");
     return B200_OK;
 }

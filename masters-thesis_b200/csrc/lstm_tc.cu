@@ -37,14 +37,13 @@ namespace b200 {
 
 using namespace tc;
 
-// L2 prefetch (cp.async.bulk.prefetch.L2 of the next step's rows, one thread per CTA) -- bit mask, env B200_TC_PREFETCH:
-//   1 forward layers > 0: x     2 backward layer 0: h, c     backward layers > 0: 4 x, 8 h, 16 c, 32 d_out
-// Measured (B = 4096, 1xB200, tools/kbench.sh with B200_TC_PREFETCH=...): bit 2 is worth 0.5 ms in the layer-0 backward
-// kernel; in the layer > 0 backward kernel (whose epilogue warps stage the image themselves, loads issued a wait ahead)
-// each of bits 4, 8, 16 COST 0.9-1.0 ms (20.1 -> 21.1 ms) when issued at the step boundary and are neutral when issued after
-// the second quarter of the step (as they are now); bit 32 is neutral; bit 1 is worth < 0.1 ms.
-// The mask is a kernel argument; b200_set_option("tc_prefetch", mask) changes it for later launches of this process.
-constexpr int PF_DEFAULT = 1 | 2 | 32;
+// L2 prefetch (cp.async.bulk.prefetch.L2 of the next step's operands, one thread per CTA) -- bit mask, option "tc_prefetch":
+//   1 forward layers > 0: x images   2 backward layer 0: h images, c     backward layers > 0: 4 x images, 8 h images, 16 c, 32 d_out
+// Measured (B = 4096, 1xB200, tools/kbench.sh --opt tc_prefetch=...), layer > 0 backward kernel (single image buffer: the bulk
+// copies of the next image can only be issued once the last weight-gradient MMA of the step has released the buffer, so an
+// L2 miss there is fully exposed): no image prefetch 21.2 ms, x images 19.6 ms, h images 20.0 ms, both 19.7 ms, c instead 19.8 ms.
+// Bit 2 is worth 0.5 ms in the layer-0 backward kernel, bit 1 < 0.1 ms.
+constexpr int PF_DEFAULT = 1 | 2 | 4 | 32;
 static int g_tc_prefetch = PF_DEFAULT;
 void tc_set_prefetch(int mask) { g_tc_prefetch = mask; }
 #ifdef B200_ABLATE                    // timing experiments only (build with B200_ABLATE=1): env B200_TC_DBG is a bit mask of backward
@@ -117,7 +116,9 @@ constexpr float LOG2E = 1.4426950408889634f;
 
 __global__ void __launch_bounds__(256)
 tc_pack_weights_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, const float* __restrict__ b_ih,
-                       const float* __restrict__ b_hh, int kin, int kx, uint8_t* __restrict__ out) {
+                       const float* __restrict__ b_hh, int kin, int kx, float in_scale, uint8_t* __restrict__ out) {
+    // in_scale: 1/(1-p) of the inter-layer dropout folded into W_ih (x W_ih^T with x = mask * h / (1-p) becomes
+    // (mask * h) (W_ih / (1-p))^T), so that the masked operand images are the plain hi/lo images with dropped units zeroed
     const uint32_t win_bytes = op_bytes(TG, kx), whh_bytes = op_bytes(TG, TH);
     uint8_t* win_hi = out;
     uint8_t* win_lo = out + win_bytes;
@@ -127,7 +128,7 @@ tc_pack_weights_kernel(const float* __restrict__ w_ih, const float* __restrict__
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
     for (int i = tid; i < TG * kx; i += nthr) {
         const int j = i / kx, k = i - j * kx;
-        const float v = k < kin ? w_ih[j * kin + k] : 0.f;
+        const float v = k < kin ? w_ih[j * kin + k] * in_scale : 0.f;
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
         const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
         const uint32_t o = op_offset(j, k, kx);
@@ -340,7 +341,6 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             const int64_t row = tile * TM + r;
             const bool tile_live = tile < ntiles;
             const bool live = tile_live && row < N;
-            const float inv_keep = 1.0f / (1.0f - p);
 #pragma unroll
             for (int u = 0; u < TH / EH; ++u) cst[u] = 0.f;
             for (int t = 0; t < T; ++t, ++g) {
@@ -417,17 +417,14 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                             st_global_v4u(hg + uc * LBO_BYTES, hi4);
                             if (NSPLIT == 2) st_global_v4u(hg + IMG_HALF + uc * LBO_BYTES, lo4);
                             if (xg != nullptr) {
+                                // 1/(1-p) lives in the next layer's packed W_ih: the masked image is the plain one with dropped units zeroed
                                 const uint32_t kb = (uint32_t)(keep >> (uc * 8)) & 0xFFu;
-                                float mv[8];
+                                uint32_t km[4];
 #pragma unroll
-                                for (int j = 0; j < 8; ++j) mv[j] = ((kb >> j) & 1u) ? hv[j] * inv_keep : 0.f;
-                                uint4 mh, ml;
-                                split2(mv[0], mv[1], mh.x, ml.x);
-                                split2(mv[2], mv[3], mh.y, ml.y);
-                                split2(mv[4], mv[5], mh.z, ml.z);
-                                split2(mv[6], mv[7], mh.w, ml.w);
-                                st_global_v4u(xg + uc * LBO_BYTES, mh);
-                                if (NSPLIT == 2) st_global_v4u(xg + IMG_HALF + uc * LBO_BYTES, ml);
+                                for (int j = 0; j < 4; ++j) km[j] = (((kb >> (2 * j)) & 1u) ? 0x0000FFFFu : 0u) | (((kb >> (2 * j + 1)) & 1u) ? 0xFFFF0000u : 0u);
+                                st_global_v4u(xg + uc * LBO_BYTES, make_uint4(hi4.x & km[0], hi4.y & km[1], hi4.z & km[2], hi4.w & km[3]));
+                                if (NSPLIT == 2)
+                                    st_global_v4u(xg + IMG_HALF + uc * LBO_BYTES, make_uint4(lo4.x & km[0], lo4.y & km[1], lo4.z & km[2], lo4.w & km[3]));
                             }
                         }
                         if (live) st_global_v8(cdst + uc * 8, cv);
@@ -637,7 +634,7 @@ __host__ __device__ inline size_t bwd_pack_bytes(bool layer0) {
 // Wcat images (hi, lo): row = packed gate column, col = [x part (KX, zero padded) | h part (64)]; then bias'
 __global__ void __launch_bounds__(256)
 tc_pack_bwd_weights_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, const float* __restrict__ b_ih,
-                           const float* __restrict__ b_hh, int kin, int kx, uint8_t* __restrict__ out) {
+                           const float* __restrict__ b_hh, int kin, int kx, float in_scale, uint8_t* __restrict__ out) {
     const int KC = kx + TH;
     const uint32_t wb = op_bytes(TG, KC);
     uint8_t* w_hi = out;
@@ -647,7 +644,7 @@ tc_pack_bwd_weights_kernel(const float* __restrict__ w_ih, const float* __restri
     for (int i = tid; i < TG * KC; i += nthr) {
         const int j = i / KC, k = i - j * KC;
         float v = 0.f;
-        if (k < kx) { if (k < kin) v = w_ih[j * kin + k]; }
+        if (k < kx) { if (k < kin) v = w_ih[j * kin + k] * in_scale; }
         else v = w_hh[j * TH + (k - kx)];
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
         const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
@@ -851,7 +848,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     for (int c = 0; c < DXC; ++c) {
                         if (drop) {
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) dx[c][i] = ((mb >> (8 * c + i)) & 1u) ? dx[c][i] * inv_keep : 0.f;
+                            for (int i = 0; i < 8; ++i) dx[c][i] = ((mb >> (8 * c + i)) & 1u) ? dx[c][i] : 0.f;      // 1/(1-p) is in the packed W_ih
                         }
                         st_global_v8(d_in + ((int64_t)t_done * N + row) * TH + 8 * DXC * sub + 8 * c, dx[c]);
                     }
@@ -1061,23 +1058,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             const int64_t rows_live = N - r0;
             for (int t = T - 1; t >= 0; --t, ++g) {
                 if (tracer) trace_ev(1, 0, 0, g, ntr);
-                const int pf = pf_mask;
-                if (XB == 1 && (pf & 28) && lw == 0 && lane == 0) {
-                    // single image buffer: time the L2 prefetch of the next image into the middle of the step (after its second quarter)
-                    mbar_wait(&da_full[0], 0u);
-                    mbar_wait(&da_full[0], 1u);
-                }
-                if ((LAYER0 ? (pf & 2) : (pf & 60)) && lw == 0 && lane == 0 && t >= 1) {
-                    // pull the NEXT step's operands (x_{t-1}, h_{t-2} images, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
-                    const int64_t nrow = rows_live < TM ? rows_live : TM;
-                    const uint32_t rb = (uint32_t)nrow * TH * 4;
-                    if (!LAYER0 && (pf & 4)) prefetch_l2(ximg_in + img_off(t - 1, tile, ntiles), NSPLIT * IMG_HALF);
-                    if (t >= 2) {
-                        if (LAYER0 || (pf & 8)) prefetch_l2(himg + img_off(t - 2, tile, ntiles), NSPLIT * IMG_HALF);
-                        if (LAYER0 || (pf & 16)) prefetch_l2(c_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
-                    }
-                    if (d_out && (pf & 32)) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
-                }
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
@@ -1126,6 +1106,24 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     fence_proxy_async();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&xh_full[buf]);
+                }
+                const int pf = pf_mask;
+                if (XB == 1 && (pf & 28) && lw == 0 && lane == 0) {
+                    // single image buffer: this step's image is on its way; time the L2 prefetch of the NEXT step's operands into the
+                    // middle of this step (after its second quarter), when the epilogue's own loads are not on the critical path
+                    mbar_wait(&da_full[0], 0u);
+                    mbar_wait(&da_full[0], 1u);
+                }
+                if ((LAYER0 ? (pf & 2) : (pf & 60)) && lw == 0 && lane == 0 && t >= 1) {
+                    // pull the NEXT step's operands (x_{t-1}, h_{t-2} images, c_{t-2}, d_out_{t-1}) of this tile into L2 one step ahead
+                    const int64_t nrow = rows_live < TM ? rows_live : TM;
+                    const uint32_t rb = (uint32_t)nrow * TH * 4;
+                    if (!LAYER0 && (pf & 4)) prefetch_l2(ximg_in + img_off(t - 1, tile, ntiles), NSPLIT * IMG_HALF);
+                    if (t >= 2) {
+                        if (LAYER0 || (pf & 8)) prefetch_l2(himg + img_off(t - 2, tile, ntiles), NSPLIT * IMG_HALF);
+                        if (LAYER0 || (pf & 16)) prefetch_l2(c_st + ((int64_t)(t - 2) * N + r0) * TH, rb);
+                    }
+                    if (d_out && (pf & 32)) prefetch_l2(d_out + ((int64_t)(t - 1) * N + r0) * TH, rb);
                 }
                 if (tracer) trace_ev(1, 2, 0, g, ntr);
             }
@@ -1361,7 +1359,7 @@ static void tc_apply_env() {
 
 int ffma_ws_pointers(int64_t N, int T, int L, void* workspace, size_t ws_bytes, float** dx0, float** dx1, float** wpart,
                      float** bpart, int* nsplit);
-int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float* gw_ih,
+int launch_grad_reduce(const float* wpart, int nsplit, const float* bpart, int nbpart, int kin, int kp, float ih_scale, float* gw_ih,
                        float* gw_hh, float* gb_ih, float* gb_hh, cudaStream_t st);
 
 // tail of the workspace: forward packs of every layer, then one backward pack (rebuilt per layer)
@@ -1464,7 +1462,7 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
         const float* w_hh = w_ih + (int64_t)TG * kin;
         const float* b_ih = w_hh + (int64_t)TG * TH;
         const float* b_hh = b_ih + TG;
-        { TimedLaunch _t("tc_pack_weights_kernel", st); tc_pack_weights_kernel<<<32, 256, 0, st>>>(w_ih, w_hh, b_ih, b_hh, kin, kx_of(l == 0), pk); }
+        { TimedLaunch _t("tc_pack_weights_kernel", st); tc_pack_weights_kernel<<<32, 256, 0, st>>>(w_ih, w_hh, b_ih, b_hh, kin, kx_of(l == 0), (l > 0 && drop) ? 1.0f / (1.0f - p) : 1.0f, pk); }
         B200_LAUNCH_CHECK("tc_pack_weights_kernel");
         float* co = stash_c + l * lsz;
         float* h_last = l == L - 1 ? stash_h + ((int64_t)l * T + (T - 1)) * N * TH : nullptr;     // fp32 final hidden state for the heads
@@ -1524,9 +1522,10 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     const float* w_hh = w_ih + (int64_t)TG * kin;
     const float* b_ih = w_hh + (int64_t)TG * TH;
     const float* b_hh = b_ih + TG;
-    { TimedLaunch _t("tc_pack_bwd_weights_kernel", st); tc_pack_bwd_weights_kernel<<<32, 256, 0, st>>>(w_ih, w_hh, b_ih, b_hh, kin, kx_of(layer0), pk); }
-    B200_LAUNCH_CHECK("tc_pack_bwd_weights_kernel");
     const bool drop = training && p > 0.f;
+    const float in_scale = (!layer0 && drop) ? 1.0f / (1.0f - p) : 1.0f;      // see tc_pack_weights_kernel
+    { TimedLaunch _t("tc_pack_bwd_weights_kernel", st); tc_pack_bwd_weights_kernel<<<32, 256, 0, st>>>(w_ih, w_hh, b_ih, b_hh, kin, kx_of(layer0), in_scale, pk); }
+    B200_LAUNCH_CHECK("tc_pack_bwd_weights_kernel");
     const int64_t lsz = (int64_t)T * N * TH;
     const uint8_t* himg = tail.himg + (size_t)layer * tail.img_bytes;
     const uint8_t* ximg_in = layer0 ? nullptr : (drop ? tail.ximg + (size_t)(layer - 1) * tail.img_bytes : tail.himg + (size_t)(layer - 1) * tail.img_bytes);
@@ -1551,7 +1550,8 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     float* gw_hh = gw_ih + (int64_t)TG * kin;
     float* gb_ih = gw_hh + (int64_t)TG * TH;
     float* gb_hh = gb_ih + TG;
-    return launch_grad_reduce(wpart, grid, bpart, grid * 4, kin, kx_of(layer0), gw_ih, gw_hh, gb_ih, gb_hh, st);
+    // the accumulator holds da^T (mask * h): the gradient of W_ih itself carries the folded 1/(1-p)
+    return launch_grad_reduce(wpart, grid, bpart, grid * 4, kin, kx_of(layer0), in_scale, gw_ih, gw_hh, gb_ih, gb_hh, st);
 }
 
 // operand images -> fp32 [T][N][64] (hi + lo): tests and tools
