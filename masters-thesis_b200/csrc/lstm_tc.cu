@@ -46,6 +46,8 @@ using namespace tc;
 constexpr int PF_DEFAULT = 1 | 2 | 4 | 32;
 static int g_tc_prefetch = PF_DEFAULT;
 void tc_set_prefetch(int mask) { g_tc_prefetch = mask; }
+static int g_tc_fwd_eh = 1;          // (default: layer > 0 only; measured 5.15 vs 5.72 ms there, neutral in layer 0) option "tc_fwd_eh": bit 0 = two epilogue threads per row in the layer > 0 forward kernel, bit 1 = in layer 0
+void tc_set_fwd_eh(int mask) { g_tc_fwd_eh = mask & 3; }
 #ifdef B200_ABLATE                    // timing experiments only (build with B200_ABLATE=1): env B200_TC_DBG is a bit mask of backward
 __constant__ int c_tc_dbg = 0;        // epilogue pieces to skip (1 bias butterfly, 2 math, 4 operand stores, 8 loads, 16 proxy fence);
 #define TC_DBG() c_tc_dbg             // results are wrong when set.  Compiled out otherwise: the run-time test alone costs 2 ms.
@@ -265,7 +267,7 @@ struct FwdSmem {
 // EH = 1 -- while an epilogue runs, the MUFU pipe is already ~80 % busy (7 MUFU per unit and row at 16 lanes/clk/SM);
 // what is missing is a third tile in flight, which TMEM (2 x 256 columns) does not allow.
 template <int NSPLIT, int NTILE, bool LAYER0, int EH>
-__global__ void __launch_bounds__(32 * (4 * NTILE * EH + LOADER_WARPS + 1), 1)
+__global__ void __launch_bounds__(32 * (4 * NTILE * EH + (LAYER0 ? LOADER_WARPS : 1) + 1), 1)
 lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__ xin, const uint8_t* __restrict__ ximg_in, int kin,
                    int64_t N, int T, float* __restrict__ h_last, float* __restrict__ c_out, uint8_t* __restrict__ himg_out,
                    uint8_t* __restrict__ ximg_out, const uint64_t* __restrict__ next_bits, float p,
@@ -277,6 +279,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     using S = FwdSmem<NSPLIT, NTILE, LAYER0>;
     constexpr int KX = S::KX;
     constexpr int EPI_WARPS = 4 * NTILE * EH;
+    constexpr int NLW = LAYER0 ? LOADER_WARPS : 1;                        // layers > 0: one thread issues the bulk copies
     constexpr int UCN = TH / 8 / EH;                                      // 8-unit chunks per epilogue thread
     // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
     // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
@@ -303,14 +306,14 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     }
     if (threadIdx.x == 0) {
         for (int s = 0; s < NTILE; ++s) {
-            mbar_init(&bars[s * 3 + 0], LAYER0 ? LOADER_WARPS : 1);      // layer > 0: one expect_tx arrival + the bulk copy's bytes
+            mbar_init(&bars[s * 3 + 0], LAYER0 ? NLW : 1);      // layer > 0: one expect_tx arrival + the bulk copy's bytes
             mbar_init(&bars[s * 3 + 1], 4 * EH);
             mbar_init(&bars[s * 3 + 2], 1);
         }
         mbar_init(x_free, 1);
         fence_barrier_init();
     }
-    if (warp == EPI_WARPS + LOADER_WARPS) tmem_alloc(tmem_slot, NTILE * TG);
+    if (warp == EPI_WARPS + NLW) tmem_alloc(tmem_slot, NTILE * TG);
     fence_proxy_async();          // weights written with generic stores, read by the tensor core (async proxy)
     tc_fence_before();
     __syncthreads();
@@ -445,7 +448,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 }
             }
         }
-    } else if (warp < EPI_WARPS + LOADER_WARPS) {
+    } else if (warp < EPI_WARPS + NLW) {
         // ================================ loader: x_t operand of every slot ==================================
         const int lw = warp - EPI_WARPS;
         int64_t g = 0;
@@ -577,7 +580,7 @@ lstm_tc_fwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // ---- teardown ----------------------------------------------------------------------------------------
     tc_fence_before();
     __syncthreads();
-    if (warp == EPI_WARPS + LOADER_WARPS) tmem_dealloc(tmem_base, NTILE * TG);
+    if (warp == EPI_WARPS + NLW) tmem_dealloc(tmem_base, NTILE * TG);
 }
 
 // --------------------------------------------------------------------------------------------- backward
@@ -618,7 +621,11 @@ constexpr int BW_LAUNCH_REGS = BW_EU == 8 ? 168 : 96;      // 65,536 / threads r
 constexpr int BW_EPI_REGS = BW_EU == 8 ? 200 : 104, BW_AUX_REGS = BW_EU == 8 ? 104 : 64;
 // kernels whose epilogue warps stage the operand image themselves (idle loader warps): 208 / 88 measured 0.6 ms faster in the
 // layer > 0 kernel (fewer epilogue spills) and 1.3 ms SLOWER in the layer-0 kernel (its loader warps then spill)
-constexpr int BW_EPI_REGS_EL = BW_EU == 8 ? 208 : 104, BW_AUX_REGS_EL = BW_EU == 8 ? 88 : 64;   // 216/72 and 224/56 measured slower
+#ifndef B200_EL_EPI
+#define B200_EL_EPI 208
+#define B200_EL_AUX 88
+#endif
+constexpr int BW_EPI_REGS_EL = BW_EU == 8 ? B200_EL_EPI : 104, BW_AUX_REGS_EL = BW_EU == 8 ? B200_EL_AUX : 64;
 static_assert(BW_EPI_WARPS * 32 * BW_EPI_REGS_EL + 4 * 32 * BW_AUX_REGS_EL <= BW_THREADS * BW_LAUNCH_REGS,
               "setmaxnreg targets exceed the CTA's register pool");
 static_assert(BW_EPI_WARPS * 32 * BW_EPI_REGS + 4 * 32 * BW_AUX_REGS <= BW_THREADS * BW_LAUNCH_REGS,
@@ -1423,7 +1430,7 @@ static int launch_fwd(const uint8_t* packed, const float* xin, const uint8_t* xi
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     const int64_t ntiles = (N + TM - 1) / TM, ngroups = (ntiles + NTILE - 1) / NTILE;
     const int grid = (int)(ngroups < num_sms() ? ngroups : num_sms());
-    const int threads = 32 * (4 * NTILE * EH + LOADER_WARPS + 1);
+    const int threads = 32 * (4 * NTILE * EH + (LAYER0 ? LOADER_WARPS : 1) + 1);
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_fwd_kernel_l0" : "lstm_tc_fwd_kernel_lN", st);
         kern<<<grid, threads, S::total, st>>>(packed, xin, ximg_in, kin, N, T, h_last, c_out, himg_out, ximg_out, next_bits, p, zero,
@@ -1474,9 +1481,15 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
         const uint8_t* ximg_in = l == 0 ? nullptr : (drop ? tail.ximg + (size_t)(l - 1) * tail.img_bytes : tail.himg + (size_t)(l - 1) * tail.img_bytes);
         int rc;
         if (l == 0) {
+            if ((g_tc_fwd_eh & 2) && precise)
+                rc = launch_fwd<2, 2, true, 2>(pk, x, nullptr, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st);
+            else
             rc = precise ? launch_fwd<2, 2, true, FW_EH_L0>(pk, x, nullptr, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st)
                          : launch_fwd<1, 2, true, FW_EH_L0>(pk, x, nullptr, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st);
         } else {
+            if ((g_tc_fwd_eh & 1) && precise)
+                rc = launch_fwd<2, 2, false, 2>(pk, nullptr, ximg_in, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st);
+            else
             rc = precise ? launch_fwd<2, 2, false, 1>(pk, nullptr, ximg_in, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st)
                          : launch_fwd<1, 2, false, 1>(pk, nullptr, ximg_in, kin, N, T, h_last, co, himg_out, ximg_out, next_bits, p, tail.zero, st);
         }
