@@ -28,7 +28,8 @@ import masters_thesis_b200 as B
 world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
 torch.manual_seed(1234)
 model = B.FinancialLstmMse(3, 64, 2, 0.0, 1e-4)       # dropout 0: masks are per rank-local row, not per global row
-dm = B.FinancialLstmDataModule(lookback_window=60, target_window=30, stride=90, batch_size=a.global_batch, seed=1234,
+dm = B.FinancialLstmDataModule(lookback_window=60, target_window=30, stride=90, batch_size=a.global_batch // world, seed=1234,      # batch_size is per rank (Lightning DDP semantics)
+                              
                                device=f"cuda:{local}", streaming=True, steps_per_epoch=2)
 tr = B.B200Trainer(max_epochs=a.steps // 2, gradient_clip_val=5.0, engine=a.engine, verbose=False, limit_val_windows=8)
 tr.fit(model, dm)
