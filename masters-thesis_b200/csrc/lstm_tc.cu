@@ -773,7 +773,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // The [x_t | h_{t-1}] image is assembled by the TMA engine from the stashed operand images (1 KB per row group and part);
     // only layer 0's 16 x-columns (fp32 input, K = 3 plus the constant-one column) are staged by the loader warps.
     constexpr bool EPI_LOADS = false;
-    constexpr bool ROLLQ = true;                           // see the quarter loop of the epilogue
+#ifndef B200_ROLLQ_L0
+#define B200_ROLLQ_L0 false     // measured (B = 4096, image-stash kernels): layer 0 unrolled 13.55 ms, rolled 14.3 ms;
+#define B200_ROLLQ_LN true      //          layer > 0 rolled 19.5 ms, unrolled 21.1 ms
+#endif
+    constexpr bool ROLLQ = LAYER0 ? B200_ROLLQ_L0 : B200_ROLLQ_LN;      // see the quarter loop of the epilogue
     // dynamic shared memory is the only shared allocation of the kernel, so it starts at offset 0 of the CTA window
     // (the UMMA descriptors need 16-byte alignment); no pointer arithmetic on integers, so accesses stay LDS/STS
     extern __shared__ __align__(1024) uint8_t smem[];
