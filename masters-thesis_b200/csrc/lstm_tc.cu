@@ -773,6 +773,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // The [x_t | h_{t-1}] image is assembled by the TMA engine from the stashed operand images (1 KB per row group and part);
     // only layer 0's 16 x-columns (fp32 input, K = 3 plus the constant-one column) are staged by the loader warps.
     constexpr bool EPI_LOADS = false;
+    constexpr bool RB_EARLY = XB == 1;                     // see the top of the quarter loop
 #ifndef B200_ROLLQ_L0
 #define B200_ROLLQ_L0 false     // measured (B = 4096, image-stash kernels): layer 0 unrolled 13.55 ms, rolled 14.3 ms;
 #define B200_ROLLQ_LN true      //          layer > 0 rolled 19.5 ms, unrolled 21.1 ms
@@ -908,6 +909,16 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     const int u0 = 16 * q + EU * sub;                        // first hidden unit of this thread's slice
                     const int64_t qi = 4 * g + q;                              // running quarter index
                     const int slot = q & 1;
+                    // Single image buffer (XB == 1): the first gate quarter of a step arrives late -- the image can only be reloaded after
+                    // the last weight-gradient MMA of the previous step, then the gates are recomputed (event trace: the epilogue
+                    // waits ~7 k of 27 k clk per step here).  The read-back of the previous step's [dx | dh] (3 k clk: TMEM loads,
+                    // masked dx stores) does not need the gates, so it goes INTO that wait.  With two buffers there is no such
+                    // wait and the read-back stays between the two halves of the quarter's math (hides the dgrad latency instead).
+                    if (RB_EARLY && q == 0 && t < T - 1) {
+                        if (tracer) trace_ev(0, 2, q, g, ntr);
+                        read_back(g - 1, row, live, t + 1);
+                        if (tracer) trace_ev(0, 3, q, g, ntr);
+                    }
                     if (tracer) trace_ev(0, 0, q, g, ntr);
                     mbar_wait(&a_full[slot], (uint32_t)((qi >> 1) & 1));
                     tc_fence_after();
@@ -944,7 +955,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     for (int i = 0; i < EU; ++i) { r1[i] = rcpa(av[0][i] * av[1][i] * av[2][i]); r2[i] = rcpa(av[3][i] * Dc[i]); }
                     }
                     // ---- dh of this step arrives from the previous step's dgrad (first quarter only) -----------------
-                    if (q == 0 && t < T - 1) {
+                    if (!RB_EARLY && q == 0 && t < T - 1) {
                         if (tracer) trace_ev(0, 2, q, g, ntr);
                         read_back(g - 1, row, live, t + 1);
                         if (tracer) trace_ev(0, 3, q, g, ntr);
