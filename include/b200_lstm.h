@@ -175,6 +175,11 @@ B200_API int b200_lstm_hidden_states(int mode, int layer, int n_features, int hi
  *   variant 2: D[128][N] = A[K][128]^T * B[K][N]   (weight gradient: A and B images read MN-major)
  * K, N multiples of 16, <= 256. */
 B200_API int b200_tc_selftest(const float* A, const float* B, int variant, int K, int N, float* D, void* stream);
+/* Microbenchmark hook (no counterpart in the reference): clocks per tcgen05.mma (M = 128, K = 16, bf16, N = n) when `iters` of
+ * them are issued back to back, for the interleaved (layout 0) and the 128-byte swizzled (layout 1) operand layout and the
+ * three operand orientations of b200_tc_selftest.  clk_per_mma_out: one float on the device. */
+B200_API int b200_tc_mma_bench(int layout, int variant, int n, int iters, float* clk_per_mma_out, void* stream);
+
 /* The GEMM of the wide engine (hidden != 64, csrc/lstm_wide.cu) on caller-supplied row-major fp32 device matrices
  * (no counterpart in the reference; what torch's addmm inside nn.LSTM does there): 128 x 256 output tiles, K chunks
  * of 64 double-buffered, operands split to bf16 hi(+lo) while staged, fp32 accumulation in TMEM.

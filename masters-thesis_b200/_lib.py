@@ -38,6 +38,7 @@ PROTOTYPES = {
     "b200_lstm_bwd": (_i, [_i, _p, _i, _i, _i, _p, _l, _i, _p, _p, _p, _p, _f, _u64, _i, _p, _sz, _p]),
     "b200_lstm_hidden_states": (_i, [_i, _i, _i, _i, _i, _l, _i, _p, _p, _sz, _p, _p]),
     "b200_tc_selftest": (_i, [_p, _p, _i, _i, _i, _p, _p]),
+    "b200_tc_mma_bench": (_i, [_i, _i, _i, _i, _p, _p]),
     "b200_wide_gemm": (_i, [_i, _i, _p, _p, _p, _l, _i, _l, _i, _p, _sz, _p]),
     "b200_debug_trace": (_i, [_p]),
     "b200_heads_workspace_bytes": (_sz, [_l, _i, _i, _i]),

@@ -1231,6 +1231,9 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 //      quarter 2 when its image is already staged (XB == 2)
                 if ((q == 0 || (q == 2 && XB == 2)) && qi + 2 < total_q) issue_recompute_pair(qi + 2);
                 trace_ev(2, 3, q, g, ntr);
+                // (Measured: making issuer B wait until dgrad and the following gate recompute are queued -- so that the weight-gradient MMAs
+                // line up BEHIND them in the in-order tensor pipe -- is slower, 15.8 vs 13.6 ms in layer 0 and 20.5 vs 17.7 ms above: the
+                // wgrad MMAs release the da and image buffers the epilogue and the loader wait for, they are just as critical.)
                 // single-buffered image: the next step's first pair can only be recomputed after the reload
                 if (XB == 1 && q == 3 && qi + 1 < total_q) {
                     issue_recompute_pair(qi + 1);
@@ -1361,6 +1364,67 @@ tc_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B, int
         tmem_ld8(tmem_base + ((uint32_t)(warp * 32) << 16) + c0, v);
         tmem_ld_wait();
         for (int j = 0; j < 8; ++j) D[r * Nn + c0 + j] = v[j];
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, 256);
+}
+
+// --------------------------------------------------------------------------------------------- operand-fetch microbenchmark
+// How long does ONE tcgen05.mma (M = 128, K = 16, bf16) of the shapes the LSTM kernels issue take when thousands are issued
+// back to back by one thread, as a function of the shared-memory operand layout?  layout 0 = the interleaved
+// (SWIZZLE_NONE) images of this engine, 1 = 128-byte swizzled images ([rows][64 elements] with the 16-byte chunk index
+// XOR row % 8).  variant 0: A and B read K-major; 1: A K-major, B MN-major; 2: both MN-major.  Results are garbage
+// numerically (uninitialised operands); only the clock count matters.  No counterpart in the reference.
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+           (1ull << 46) | (2ull << 61);
+}
+__global__ void __launch_bounds__(128, 1)
+tc_mma_bench_kernel(int layout, int variant, int Nn, int iters, float* __restrict__ out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    constexpr uint32_t A_BYTES = 128 * 128 * 2, B_BYTES = 256 * 128 * 2;      // a [128 x 128] and a [256 x 128] bf16 image
+    uint8_t* a_img = smem;
+    uint8_t* b_img = smem + A_BYTES;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(b_img + B_BYTES);
+    uint32_t* tslot = reinterpret_cast<uint32_t*>(bar + 1);
+    for (uint32_t i = threadIdx.x; i < (A_BYTES + B_BYTES) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3C003C00u;
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+    if (warp == 0) tmem_alloc(tslot, 256);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tslot;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = make_idesc_bf16(TM, Nn, variant == 2 ? 1 : 0, variant == 0 ? 0 : 1);
+        const uint32_t sa = smem_u32(a_img), sb = smem_u32(b_img);
+        uint64_t ad[8], bd[8];
+        for (int ks = 0; ks < 8; ++ks) {
+            if (layout == 0) {
+                // interleaved images with 128 columns: K-major LBO 128 / SBO 2048, k-step 256 B; MN-major: strides swapped, k-step 2 row groups
+                const uint32_t sbo = sbo_of(128);
+                ad[ks] = variant == 2 ? make_desc(sa + ks * 2 * sbo, sbo, LBO_BYTES) : make_desc(sa + ks * 2 * LBO_BYTES, LBO_BYTES, sbo);
+                bd[ks] = variant == 0 ? make_desc(sb + ks * 2 * LBO_BYTES, LBO_BYTES, sbo) : make_desc(sb + ks * 2 * sbo, sbo, LBO_BYTES);
+            } else {
+                // 128-byte swizzled [rows][64] blocks: K-major SBO 1024, k-step 32 B inside the row (second 64-column block after the
+                // first); MN-major: LBO = block stride, SBO 1024, k-step 16 rows = 2048 B
+                const uint32_t ablk = 128 * 128, bblk = 256 * 128;     // bytes of one 64-column block of A / B
+                ad[ks] = variant == 2 ? make_desc_sw128(sa + ks * 2048, ablk, 1024) : make_desc_sw128(sa + (ks >> 2) * ablk + (ks & 3) * 32, 16, 1024);
+                bd[ks] = variant == 0 ? make_desc_sw128(sb + (ks >> 2) * bblk + (ks & 3) * 32, 16, 1024) : make_desc_sw128(sb + ks * 2048, bblk, 1024);
+            }
+        }
+        // warm-up, then the timed chain
+        for (int i = 0; i < 64; ++i) umma_bf16(tmem_base, ad[i & 7], bd[i & 7], idesc, i > 0);
+        umma_commit(bar);
+        mbar_wait(bar, 0);
+        const long long t0 = clock64();
+        for (int i = 0; i < iters; ++i) umma_bf16(tmem_base, ad[i & 7], bd[i & 7], idesc, 1);
+        umma_commit(bar);
+        mbar_wait(bar, 1);
+        const long long t1 = clock64();
+        out[0] = (float)(t1 - t0) / (float)iters;
     }
     tc_fence_before();
     __syncthreads();
@@ -1636,5 +1700,16 @@ extern "C" int b200_tc_selftest(const float* A, const float* B, int variant, int
     B200_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, variant, K, Nn, D);
     B200_LAUNCH_CHECK("tc_selftest_kernel");
+    return B200_OK;
+}
+
+// see tc_mma_bench_kernel
+extern "C" int b200_tc_mma_bench(int layout, int variant, int Nn, int iters, float* clk_per_mma_out, void* stream) {
+    B200_CHECK_ARG(layout >= 0 && layout <= 1 && variant >= 0 && variant <= 2 && Nn >= 16 && Nn <= (variant == 0 ? 256 : 128) && Nn % 16 == 0 && iters > 0 &&
+                   clk_per_mma_out, "tc_mma_bench: bad arguments (N <= 256 K-major, <= 128 when B is read MN-major)");
+    const size_t smem = 128 * 128 * 2 + 256 * 128 * 2 + 64 + 128;
+    B200_CUDA(cudaFuncSetAttribute(tc_mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tc_mma_bench_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(layout, variant, Nn, iters, clk_per_mma_out);
+    B200_LAUNCH_CHECK("tc_mma_bench_kernel");
     return B200_OK;
 }
