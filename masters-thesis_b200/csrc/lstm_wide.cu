@@ -451,11 +451,16 @@ wide_cell_fwd_kernel(float* __restrict__ G, const float* __restrict__ b_ih, cons
 }
 
 // backward cell of step t: activated gates in G_t are overwritten with the pre-activation gradients
+// bsum (nullable): per-thread-group partial column sums of dG = the bias gradient.  The grid stride is a multiple of H (256 threads
+// per block, H in {128, 256}), so a thread sees ONE hidden unit u for all its rows: it adds its four gate-gradient sums of this
+// launch to its own slot bsum[group][gate * H + u], group = global thread index / H -- read-modify-write of a slot no other thread
+// touches, the same grid for every step of a layer: deterministic, and the 100 GB-per-layer column-sum pass over dG disappears.
 __global__ void __launch_bounds__(256)
 wide_cell_bwd_kernel(float* __restrict__ G, const float* __restrict__ c_t, const float* __restrict__ c_prev,
                      const float* __restrict__ d_out_t, const float* __restrict__ dhT, const float* __restrict__ dh_rec,
-                     float* __restrict__ dc, int first, int64_t N, int H) {
+                     float* __restrict__ dc, int first, int64_t N, int H, float* __restrict__ bsum) {
     const int64_t total = N * H;
+    float bs0 = 0.f, bs1 = 0.f, bs2 = 0.f, bs3 = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t n = i / H;
         const int u = (int)(i - n * H);
@@ -469,10 +474,19 @@ wide_cell_bwd_kernel(float* __restrict__ G, const float* __restrict__ c_t, const
         const float dcc = (first ? 0.f : dc[i]) + dh * og * (1.f - tc * tc);
         const float cp = c_prev ? c_prev[i] : 0.f;
         dc[i] = dcc * fg;
-        g[u] = dcc * gg * ig * (1.f - ig);
-        g[H + u] = dcc * cp * fg * (1.f - fg);
-        g[2 * H + u] = dcc * ig * (1.f - gg * gg);
-        g[3 * H + u] = dh * tc * og * (1.f - og);
+        const float d0 = dcc * gg * ig * (1.f - ig), d1 = dcc * cp * fg * (1.f - fg), d2 = dcc * ig * (1.f - gg * gg), d3 = dh * tc * og * (1.f - og);
+        g[u] = d0;
+        g[H + u] = d1;
+        g[2 * H + u] = d2;
+        g[3 * H + u] = d3;
+        bs0 += d0; bs1 += d1; bs2 += d2; bs3 += d3;
+    }
+    if (bsum != nullptr) {
+        const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (tid < total) {
+            float* o = bsum + (tid / H) * 4 * H + (tid % H);
+            o[0] += bs0; o[H] += bs1; o[2 * H] += bs2; o[3 * H] += bs3;
+        }
     }
 }
 
@@ -550,6 +564,7 @@ struct WideWs {
     float* dc;       // [N][H]
     float* part;     // split-K partials / column-sum partials
     size_t part_floats;
+    float* bsum;     // [groups][4H] bias-gradient partials accumulated by the backward cell kernel (layers > 0)
     uint8_t* pack[4];   // B-operand images of the current layer's weights: [W_ih, W_hh] x [hi, lo] (K-major in forward, MN-major in backward)
 };
 constexpr int COLSUM_SLABS = 64;
@@ -561,6 +576,8 @@ size_t wide_part_floats(int H, int F) {
     return gemm > cs ? gemm : cs;
 }
 size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
+// the backward cell kernel runs on at most num_sms * 16 blocks of 256 threads = groups of H threads with 4H floats each
+size_t wide_bsum_floats() { return (size_t)num_sms() * 16 * 256 * 4; }
 // one of hi / lo of a [4H x H] weight as B operand: [N = 4H][K = H] (variant 0) or [K = 4H][N = H] (variant 1); images are padded
 // to GN columns, so the two counts differ when H < GN
 size_t wide_pack_region(int H) {
@@ -581,6 +598,8 @@ bool wide_ws(void* workspace, size_t ws_bytes, int64_t N, int T, int F, int H, i
     w->part = (float*)(p + off);
     w->part_floats = wide_part_floats(H, F);
     off += al256(w->part_floats * 4);
+    w->bsum = (float*)(p + off);
+    off += al256(wide_bsum_floats() * 4);
     const size_t pk = wide_pack_region(H);
     for (int i = 0; i < 4; ++i) { w->pack[i] = p + off; off += pk; }
     return workspace != nullptr && off <= ws_bytes;
@@ -605,7 +624,7 @@ LayerParams layer_params(const float* params, int F, int H, int l) {
 size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L) {
     const size_t lsz = (size_t)T * N * H * 4;
     return al256((size_t)L * lsz * 4) + 3 * al256(lsz) + 2 * al256((size_t)N * H * 4) + al256(wide_part_floats(H, F) * 4) +
-           4 * wide_pack_region(H) + 256;
+           al256(wide_bsum_floats() * 4) + 4 * wide_pack_region(H) + 256;
 }
 
 static int g_wide_fuse = 0;
@@ -706,13 +725,18 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
     rc = wide_pack_b(lp.w_hh, 1, H, G4, w.pack[2], w.pack[3], st);
     if (rc) return rc;
     if (l > 0) { rc = wide_pack_b(lp.w_ih, 1, H, G4, w.pack[0], w.pack[1], st); if (rc) return rc; }
+    // layers > 0: the bias gradient is accumulated by the cell kernel itself (layer 0 keeps the column-sum pass, which also yields dW_ih)
+    const unsigned cell_grid = ew_grid(NH);
+    const int64_t bgroups = ((int64_t)cell_grid * 256 < NH ? (int64_t)cell_grid * 256 : NH + H - 1) / H;
+    float* bsum = l > 0 ? w.bsum : nullptr;
+    if (bsum) B200_CUDA(cudaMemsetAsync(bsum, 0, sizeof(float) * (size_t)bgroups * G4, st));
     for (int t = T - 1; t >= 0; --t) {
         float* Gt = G + (int64_t)t * N * G4;
         {
             TimedLaunch _t("wide_cell_bwd_kernel", st);
-            wide_cell_bwd_kernel<<<ew_grid(NH), 256, 0, st>>>(Gt, cs + (int64_t)t * NH, t > 0 ? cs + (int64_t)(t - 1) * NH : nullptr,
+            wide_cell_bwd_kernel<<<cell_grid, 256, 0, st>>>(Gt, cs + (int64_t)t * NH, t > 0 ? cs + (int64_t)(t - 1) * NH : nullptr,
                                                               d_out ? d_out + (int64_t)t * NH : nullptr, (top && t == T - 1) ? dhT : nullptr,
-                                                              t < T - 1 ? w.dh_rec : nullptr, w.dc, t == T - 1 ? 1 : 0, N, H);
+                                                              t < T - 1 ? w.dh_rec : nullptr, w.dc, t == T - 1 ? 1 : 0, N, H, bsum);
         }
         B200_LAUNCH_CHECK("wide_cell_bwd_kernel");
         if (t > 0) {
@@ -746,7 +770,10 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
         }
     }
     // bias gradients (and layer 0's dW_ih, K = F on CUDA cores)
-    {
+    if (bsum) {
+        { TimedLaunch _t("wide_colsum_reduce_kernel", st); wide_colsum_reduce_kernel<<<(unsigned)((G4 + 255) / 256), 256, 0, st>>>(bsum, (int)bgroups, (int)G4, 0, nullptr, gb_ih, gb_hh); }
+        B200_LAUNCH_CHECK("wide_colsum_reduce_kernel");
+    } else {
         const int Fx = l == 0 ? F : 0;
         int64_t rows_per = (R + COLSUM_SLABS - 1) / COLSUM_SLABS;
         const int nslab = (int)((R + rows_per - 1) / rows_per);
