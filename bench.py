@@ -136,8 +136,6 @@ def run_reference(args):
     sample = (f"each step = one optimisation step of the oracle port on {bw} windows ({bw * S} sequences), "
               f"a 1/{max(1, batch // bw)} sample of the {batch}-window batch; torch CPU fp32 eager, {cores} threads")
     cfg = workload_config(args, world, batch)
-    cfg["workload"] += f" -- CPU arm: every timed step processes a {bw}-window SAMPLE of that batch (samples/s is per window)"
-    cfg["cpu_step_windows"] = bw
     out = {"impl": "reference", "metric": "train samples/sec", "value": v, "unit": "samples/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
            "scaling": "weak" if world == 1 or args.batch else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -166,6 +164,8 @@ def workload_config(args, world, batch):
                         + f", H={H} L={L} dropout={p}",
             "global_batch_windows": batch * world, "sequences_per_step": batch * S * world, "lookback": T,
             "micro_batch_windows": micro, "engine": args.engine,
+            "reference_arm": f"`--impl reference` (the CPU oracle port on all host cores) times one optimisation step on a {args.cpu_batch}-window "
+                             "SAMPLE of this batch per timed step; samples/s is per window, so the two arms compare like for like",
             "l2": "per-step working set (activation stash, >= 25 GB at 4096 windows) exceeds the 126 MB L2",
             "parallelism": f"dp{world}"}
 
