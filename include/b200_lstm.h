@@ -255,6 +255,16 @@ B200_API int b200_grad_sqnorm(const float* grads, int64_t count, float* sqnorm_o
 #define B200_SQNORM_STATIC_MAX 4194304
 B200_API int b200_grad_sqnorm_static(const float* grads, int64_t count, float* sqnorm_out, void* stream);
 
+/* clip_grad_norm_ + Adam.step (train.py:171, src/model.py:150-154) in ONE launch for parameter vectors of at most
+ * B200_CLIP_ADAM_FUSED_MAX floats (the small and medium reference models): every CTA reduces ||g||^2 over the whole (L2-resident)
+ * vector in the same order, then updates its slice with the clip coefficient; sqnorm_out (nullable) receives ||g||^2.
+ * clip_val <= 0 disables clipping.  Unlike b200_adam_step it leaves g untouched (every backward call overwrites its slice).
+ * Larger vectors: B200_ERR_UNSUPPORTED -> use b200_grad_sqnorm + b200_adam_step. */
+#define B200_CLIP_ADAM_FUSED_MAX 131072
+B200_API int b200_clip_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t count, float lr,
+                        float beta1, float beta2, float eps, float weight_decay, int64_t step, float clip_val,
+                        float* sqnorm_out, void* stream);
+
 /* dst[i] += scale * src[i]: accumulates the gradient of one micro-batch into the step's gradient when a batch is
  * processed in several forward/backward passes (one optimiser step per datamodule.batch_size windows,
  * src/data.py:236-238, src/model.py:204-209 -- the reference never splits a batch; this is what lets batches whose

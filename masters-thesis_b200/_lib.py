@@ -48,6 +48,7 @@ PROTOTYPES = {
     "b200_sqnorm_workspace_bytes": (_sz, [_l]),
     "b200_grad_sqnorm": (_i, [_p, _l, _p, _p, _sz, _p]),
     "b200_grad_sqnorm_static": (_i, [_p, _l, _p, _p]),
+    "b200_clip_adam_step": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _l, _f, _p, _p]),
     "b200_grad_accumulate": (_i, [_p, _p, _l, _f, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _f, _l, _f, _p, _i, _p]),
     "b200_dp_nccl_version": (_i, []),

@@ -96,6 +96,53 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
         }
 }
 
+// Fused global-norm clip + Adam in ONE launch for small parameter vectors: every CTA first reduces ||g||^2 over the WHOLE vector
+// (same order in every CTA, fp64 accumulation: all CTAs arrive at the identical clip coefficient; the vector is L2-resident,
+// 200 KB for the small model), then updates its own slice.  g is only read, so no CTA can disturb another CTA's norm.
+__global__ void __launch_bounds__(256)
+clip_adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t count,
+                 AdamArgs a, float* __restrict__ sqnorm_out) {
+    __shared__ double red[8];
+    __shared__ float coef_s;
+    const int64_t n4 = count >> 2;
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    double acc = 0.0;
+    for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+        const float4 x = g4[i];
+        acc += (double)(x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w);
+    }
+    for (int64_t i = (n4 << 2) + threadIdx.x; i < count; i += blockDim.x) acc += (double)g[i] * (double)g[i];
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        const float sq = (float)t;
+        if (blockIdx.x == 0 && sqnorm_out) sqnorm_out[0] = sq;
+        coef_s = a.clip_val > 0.f ? fminf(1.0f, a.clip_val / (sqrtf(sq) + 1e-6f)) : 1.0f;
+    }
+    __syncthreads();
+    const float coef = coef_s;
+    float4* p4 = reinterpret_cast<float4*>(p);
+    float4* m4 = reinterpret_cast<float4*>(m);
+    float4* v4 = reinterpret_cast<float4*>(v);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 pp = p4[i], gg = g4[i], mm = m4[i], vv = v4[i];
+        adam_elem(pp.x, gg.x, mm.x, vv.x, coef, a);
+        adam_elem(pp.y, gg.y, mm.y, vv.y, coef, a);
+        adam_elem(pp.z, gg.z, mm.z, vv.z, coef, a);
+        adam_elem(pp.w, gg.w, mm.w, vv.w, coef, a);
+        p4[i] = pp; m4[i] = mm; v4[i] = vv;
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = (n4 << 2) + threadIdx.x; i < count; i += blockDim.x) {
+            float pp = p[i], gg = g[i], mm = m[i], vv = v[i];
+            adam_elem(pp, gg, mm, vv, coef, a);
+            p[i] = pp; m[i] = mm; v[i] = vv;
+        }
+}
+
 // Scratch of b200_grad_sqnorm_static: one fp64 partial per 4,096-gradient tile, so 1,024 slots cover
 // B200_SQNORM_STATIC_MAX gradients.  Lives in every CUDA context that loads the library until exit (8 KB).
 // In host code this name is only a handle; the device address comes from cudaGetSymbolAddress.
@@ -167,6 +214,30 @@ extern "C" int b200_grad_accumulate(float* dst, const float* src, int64_t count,
     if (nb > cap) nb = cap;
     { TimedLaunch _t("grad_accumulate_kernel", (cudaStream_t)stream); grad_accumulate_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(dst, src, count, scale); }
     B200_LAUNCH_CHECK("grad_accumulate_kernel");
+    return B200_OK;
+}
+
+extern "C" int b200_clip_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t count, float lr,
+                                   float beta1, float beta2, float eps, float weight_decay, int64_t step, float clip_val,
+                                   float* sqnorm_out, void* stream) {
+    B200_CHECK_ARG(count > 0 && params && grads && exp_avg && exp_avg_sq, "clip_adam_step: bad arguments");
+    B200_CHECK_ARG(step >= 1, "clip_adam_step: step is 1-based, got %lld", (long long)step);
+    B200_CHECK_ARG((((uintptr_t)params | (uintptr_t)grads | (uintptr_t)exp_avg | (uintptr_t)exp_avg_sq) & 15) == 0,
+                   "clip_adam_step: buffers must be 16-byte aligned");
+    if (count > (int64_t)B200_CLIP_ADAM_FUSED_MAX) {
+        set_error("clip_adam_step: %lld parameters exceed the fused kernel's limit (%lld): use b200_grad_sqnorm + b200_adam_step",
+                  (long long)count, (long long)B200_CLIP_ADAM_FUSED_MAX);
+        return B200_ERR_UNSUPPORTED;
+    }
+    AdamArgs a;
+    a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.wd = weight_decay; a.clip_val = clip_val;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    a.step_size = (float)((double)lr / bc1);
+    a.rsqrt_bc2 = (float)(1.0 / sqrt(bc2));
+    int64_t nb = (count / 4 + 255) / 256;
+    if (nb < 1) nb = 1;
+    { TimedLaunch _t("clip_adam_kernel", (cudaStream_t)stream); clip_adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, count, a, sqnorm_out); }
+    B200_LAUNCH_CHECK("clip_adam_kernel");
     return B200_OK;
 }
 

@@ -249,6 +249,13 @@ class LstmEngine:
         """Global-norm clip + Adam on the flat vector (train.py:171, src/model.py:150-154)."""
         self.opt_step += 1
         use_clip = clip_val is not None and clip_val > 0
+        if self.P_pad <= 131072:           # B200_CLIP_ADAM_FUSED_MAX: norm, clip and Adam in one launch
+            check(self.lib.b200_clip_adam_step(ptr(self.params), ptr(self.grads), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                                               self.P_pad, float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                               float(weight_decay), self.opt_step, float(clip_val) if use_clip else 0.0,
+                                               ptr(self.sqnorm), self.stream), "b200_clip_adam_step")
+            self.launches += 1
+            return
         if use_clip:
             check(self.lib.b200_grad_sqnorm(ptr(self.grads), self.P_pad, ptr(self.sqnorm), ptr(self.sq_ws),
                                             self.sq_ws.numel(), self.stream), "b200_grad_sqnorm")

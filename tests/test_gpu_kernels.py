@@ -177,6 +177,35 @@ def test_clip_and_adam_vs_torch(count, clip):
     assert float(dp[count:].abs().sum()) == 0.0
 
 
+@pytest.mark.parametrize("count,clip", [(51074, 5.0), (51076, 0.0), (117634, 0.5), (7, 1.0)])
+def test_fused_clip_adam_vs_torch(count, clip):
+    """b200_clip_adam_step (norm + clip + Adam in one launch, the path LstmEngine takes for the small and medium models) against
+    clip_grad_norm_ + torch.optim.Adam for three steps; larger vectors are refused with UNSUPPORTED."""
+    lib = load()
+    g = torch.Generator().manual_seed(count + 1)
+    p0 = torch.randn(count, generator=g) * 0.1
+    pad = (count + 3) // 4 * 4
+    tp = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([tp], lr=1e-3, weight_decay=1e-5)
+    dp, dg, dm, dv = (torch.zeros(pad, device=DEV) for _ in range(4))
+    dp[:count] = p0.to(DEV)
+    sq = torch.zeros(1, device=DEV)
+    for step in range(1, 4):
+        grad = torch.randn(count, generator=g) * (3.0 if step == 2 else 0.01)
+        tp.grad = grad.clone()
+        if clip > 0:
+            torch.nn.utils.clip_grad_norm_([tp], clip)
+        opt.step()
+        dg[:count] = grad.to(DEV)
+        check(lib.b200_clip_adam_step(ptr(dp), ptr(dg), ptr(dm), ptr(dv), pad, 1e-3, 0.9, 0.999, 1e-8, 1e-5, step, clip, ptr(sq), None), "clip_adam")
+        assert float(sq) == pytest.approx(float((grad.double() ** 2).sum()), rel=1e-5)
+        assert torch.equal(dg[:count].cpu(), grad)                    # gradients are left untouched
+        np.testing.assert_allclose(dp[:count].cpu().numpy(), tp.detach().numpy(), rtol=2e-5, atol=2e-7)
+    assert float(dp[count:].abs().sum()) == 0.0
+    big = torch.zeros(131072 + 4, device=DEV)
+    assert lib.b200_clip_adam_step(ptr(big), ptr(big), ptr(big), ptr(big), big.numel(), 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, 1.0, None, None) == -2
+
+
 @pytest.mark.parametrize("variant,K,N", [(0, 16, 256), (0, 64, 256), (0, 128, 128), (1, 64, 128), (1, 256, 64),
                                          (1, 128, 128), (2, 128, 64), (2, 128, 256), (2, 64, 128)])
 def test_tcgen05_gemm_selftest(variant, K, N):
