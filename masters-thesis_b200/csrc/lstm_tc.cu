@@ -10,9 +10,10 @@
 //     the natural torch row order of W), its own h operand buffer and its own x operand buffer
 //   * the layer's weights stay resident in shared memory for the whole launch as bf16 hi (+ lo) images
 //     in the UMMA interleaved K-major layout (tc_common.cuh); `tc_pack_weights_kernel` builds the images
-//   * warp roles: 4 epilogue warps per slot (thread = one sequence: TMEM -> registers -> sigma/tanh/cell
-//     -> h back to shared memory as the next step's A operand, h and c to the stash), 2 loader warps
-//     (x_t operand of the next step, coalesced, dropout applied), 1 MMA warp (one thread issues)
+//   * warp roles: 4 * EH epilogue warps per slot (thread = one sequence x 64 / EH units: TMEM -> registers -> sigma/tanh/cell
+//     -> h back to shared memory as the next step's A operand and to the global operand images, c to the stash);
+//     layer 0: 2 loader warps (fp32 x_t -> bf16 hi/lo image), layers > 0: ONE loader thread (x_t = the image the layer
+//     below stashed, one cp.async.bulk per tile and step); 1 MMA warp (one thread issues)
 //   * three mbarriers per slot: x_full (loader -> MMA), h_ready (epilogue -> MMA: h_t written, TMEM
 //     drained), acc_full (tcgen05.commit -> epilogue and loader: gates ready, operands consumed)
 //   * NSPLIT = 2 (precise): every product is hi*hi + lo*hi + hi*lo on bf16 halves of the fp32 operands,
@@ -183,63 +184,10 @@ tc_dropout_bits_kernel(uint64_t seed, int layer, int64_t N, int T, uint32_t thr,
     }
 }
 
-// A loader warp handles NRG consecutive row groups (8 rows each) of a [128 x 64] fp32 tile per batch, starting at
-// row group rg0; lane = (row in group rr, quarter q): element block (rgi, i) is the float4 at row (rg0 + rgi)*8 + rr,
-// columns 4q + 16i .. +3.  q = {0,1} live in lanes 0-15 and q = {2,3} in lanes 16-31, so that each half warp of an
-// 8-byte operand store covers one contiguous 128-byte core matrix (the lane / 4, lane % 4 split made every such store
-// a 2-way bank conflict: measured 2x the ideal wavefronts).  tile_load issues all loads of the batch first (one latency per batch), tile_store
-// converts and writes the operand image.
+// lane -> (row in an 8-row group, column quarter) of the layer-0 x staging: q = {0,1} live in lanes 0-15 and q = {2,3} in lanes
+// 16-31, so that each half warp of an 8-byte operand store covers one contiguous run of a core matrix (bank-conflict free)
 __device__ __forceinline__ int tile_rr(int lane) { return (lane >> 1) & 7; }
 __device__ __forceinline__ int tile_q(int lane) { return (lane & 1) | ((lane >> 3) & 2); }
-
-template <int NRG>
-__device__ __forceinline__ void tile_load(float4 (&v)[NRG][4], const float* __restrict__ tile_base, int64_t rows_live, int rg0, int lane) {
-    const int rr = tile_rr(lane), q = tile_q(lane);
-#pragma unroll
-    for (int rgi = 0; rgi < NRG; ++rgi) {
-        const int r = (rg0 + rgi) * 8 + rr;
-        const float* src = tile_base + (int64_t)r * TH + 4 * q;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) v[rgi][i] = r < rows_live ? *reinterpret_cast<const float4*>(src + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-}
-template <int NRG>
-__device__ __forceinline__ void tile_load_bits(uint64_t (&m)[NRG], const uint64_t* __restrict__ bits_base, int64_t rows_live, int rg0, int lane) {
-    const int rr = tile_rr(lane);
-#pragma unroll
-    for (int rgi = 0; rgi < NRG; ++rgi) {
-        const int r = (rg0 + rgi) * 8 + rr;
-        m[rgi] = r < rows_live ? bits_base[r] : 0ull;
-    }
-}
-template <int NSPLIT, int NRG>
-__device__ __forceinline__ void tile_store(const float4 (&v)[NRG][4], uint8_t* img_hi, uint8_t* img_lo, uint32_t sbo, int kcol0,
-                                           int rg0, int lane, bool drop, const uint64_t (&m)[NRG], float inv_keep) {
-    const int rr = tile_rr(lane), q = tile_q(lane);
-#pragma unroll
-    for (int rgi = 0; rgi < NRG; ++rgi) {
-        const int rg = rg0 + rgi;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int k = 4 * q + 16 * i;
-            float4 x = v[rgi][i];
-            if (drop) {
-                const uint32_t b = (uint32_t)(m[rgi] >> k) & 0xFu;
-                x.x = (b & 1u) ? x.x * inv_keep : 0.f;
-                x.y = (b & 2u) ? x.y * inv_keep : 0.f;
-                x.z = (b & 4u) ? x.z * inv_keep : 0.f;
-                x.w = (b & 8u) ? x.w * inv_keep : 0.f;
-            }
-            uint2 hi2, lo2;
-            split2(x.x, x.y, hi2.x, lo2.x);
-            split2(x.z, x.w, hi2.y, lo2.y);
-            const int kc = kcol0 + k;
-            const uint32_t o = (uint32_t)rg * sbo + (uint32_t)(kc >> 3) * LBO_BYTES + (uint32_t)rr * 16 + (uint32_t)(kc & 7) * 2;
-            *reinterpret_cast<uint2*>(img_hi + o) = hi2;
-            if (NSPLIT == 2) *reinterpret_cast<uint2*>(img_lo + o) = lo2;
-        }
-    }
-}
 
 // --------------------------------------------------------------------------------------------- forward
 template <int NSPLIT, int NTILE, bool LAYER0>
@@ -772,7 +720,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     constexpr int ND = LAYER0 ? TH : 2 * TH;                  // dgrad N
     // The [x_t | h_{t-1}] image is assembled by the TMA engine from the stashed operand images (1 KB per row group and part);
     // only layer 0's 16 x-columns (fp32 input, K = 3 plus the constant-one column) are staged by the loader warps.
-    constexpr bool EPI_LOADS = false;
     constexpr bool RB_EARLY = XB == 1;                     // see the top of the quarter loop
 #ifndef B200_ROLLQ_L0
 #define B200_ROLLQ_L0 false     // measured (B = 4096, image-stash kernels): layer 0 unrolled 13.55 ms, rolled 14.3 ms;
@@ -837,7 +784,6 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const uint32_t lane_addr = tmem_base + ((uint32_t)(wq * 32) << 16);
         const uint32_t row_off = (uint32_t)(r >> 3) * SBO_DA + (uint32_t)(r & 7) * 16;
         const bool drop = drop_bits != nullptr;
-        const float inv_keep = 1.0f / (1.0f - p);
         float dc[4][EU], dh[4][EU], db[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) db[q] = 0.f;
