@@ -1177,6 +1177,9 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 //      quarter 2 when its image is already staged (XB == 2)
                 if ((q == 0 || (q == 2 && XB == 2)) && qi + 2 < total_q) issue_recompute_pair(qi + 2);
                 trace_ev(2, 3, q, g, ntr);
+                // (Measured: issuing this recompute BEFORE the quarter's dgrad -- the epilogue waits ~2 k clk per step for these gates in
+                // layer 0 -- is slower, 15.8-16.4 vs 13.8 ms: the issuer then sits in the wait for the second gate slot while the da
+                // image arrives, and the late dgrad holds the da buffer.)
                 // (Measured: making issuer B wait until dgrad and the following gate recompute are queued -- so that the weight-gradient MMAs
                 // line up BEHIND them in the in-order tensor pipe -- is slower, 15.8 vs 13.6 ms in layer 0 and 20.5 vs 17.7 ms above: the
                 // wgrad MMAs release the da and image buffers the epilogue and the loader wait for, they are just as critical.)
