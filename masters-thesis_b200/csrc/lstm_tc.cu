@@ -569,6 +569,9 @@ constexpr int BW_LAUNCH_REGS = BW_EU == 8 ? 168 : 96;      // 65,536 / threads r
 constexpr int BW_EPI_REGS = BW_EU == 8 ? 200 : 104, BW_AUX_REGS = BW_EU == 8 ? 104 : 64;
 // kernels whose epilogue warps stage the operand image themselves (idle loader warps): 208 / 88 measured 0.6 ms faster in the
 // layer > 0 kernel (fewer epilogue spills) and 1.3 ms SLOWER in the layer-0 kernel (its loader warps then spill)
+#ifndef B200_ISSUER_C
+#define B200_ISSUER_C 1
+#endif
 #ifndef B200_EL_EPI
 #define B200_EL_EPI 208
 #define B200_EL_AUX 88
@@ -721,6 +724,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // The [x_t | h_{t-1}] image is assembled by the TMA engine from the stashed operand images (1 KB per row group and part);
     // only layer 0's 16 x-columns (fp32 input, K = 3 plus the constant-one column) are staged by the loader warps.
     constexpr bool RB_EARLY = XB == 1;                     // see the top of the quarter loop
+    constexpr bool ISSUER_C = B200_ISSUER_C && LAYER0 && XB == 2;   // see below (third MMA issuer thread)
 #ifndef B200_ROLLQ_L0
 #define B200_ROLLQ_L0 false     // measured (B = 4096, image-stash kernels): layer 0 unrolled 13.55 ms, rolled 14.3 ms;
 #define B200_ROLLQ_LN true      //          layer > 0 rolled 19.5 ms, unrolled 21.1 ms
@@ -750,9 +754,11 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         const float* bsrc = reinterpret_cast<const float*>(packed + 2 * S::WB);
         for (int i = threadIdx.x; i < TG; i += blockDim.x) bias_s[i] = bsrc[i];
         if (LAYER0) for (int i = threadIdx.x; i < 256; i += blockDim.x) reinterpret_cast<uint32_t*>(smem + S::off_pad)[i] = 0u;
+        // layer 0: the vectorised x staging writes only the first k-group of the 16 x columns; the second one must read as zero
+        if (LAYER0) for (uint32_t i = threadIdx.x; i < (XB * NSPLIT * S::XHB) / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem + S::off_xh)[i] = make_uint4(0, 0, 0, 0);
     }
     if (threadIdx.x == 0) {
-        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], LAYER0 ? LOADER_WARPS + 1 : 1); mbar_init(&xh_free[b], 2); }
+        for (int b = 0; b < XB; ++b) { mbar_init(&xh_full[b], LAYER0 ? (ISSUER_C ? 2 : LOADER_WARPS + 1) : 1); mbar_init(&xh_free[b], 2); }
         for (int b = 0; b < DB; ++b) { mbar_init(&da_full[b], BW_EPI_WARPS); mbar_init(&da_free[b], 2); }
         for (int b = 0; b < 2; ++b) { mbar_init(&a_full[b], 1); mbar_init(&a_free[b], BW_EPI_WARPS); }
         mbar_init(d_full, 1); mbar_init(d_free, BW_EPI_WARPS); mbar_init(done, 2);
@@ -770,6 +776,41 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     const int64_t total_steps = my_tiles * T;
     const int64_t total_q = 4 * total_steps;
 
+    // Gates of the quarter PAIR (nq, nq + 1), nq even -> TMEM slots 0 and 1 with ONE N = 128 MMA per product and k-step:
+    // a tcgen05.mma of this size costs ~60 clk of fixed overhead plus ~0.43 clk per column of N (measured), so two
+    // N = 64 quarters cost 174 clk and the pair 115.  Waits for both slots to be read out and for the image of its step.
+    constexpr uint32_t idesc_a2 = make_idesc_bf16(TM, 128, 0, 0);
+    auto issue_recompute_pair = [&](int64_t nq) {
+        const uint32_t s_base = smem_u32(smem);
+        const uint64_t wk_hi = make_desc(s_base + S::off_w, LBO_BYTES, SBO_W), wk_lo = wk_hi + (S::WB >> 4);
+        const int64_t ng = nq >> 2;
+        const int q = (int)(nq & 3);                                   // 0 or 2
+        if (q == 0) mbar_wait(&xh_full[ng % XB], (uint32_t)((ng / XB) & 1));
+        if (nq >= 2) {
+            mbar_wait(&a_free[0], (uint32_t)(((nq >> 1) - 1) & 1));
+            mbar_wait(&a_free[1], (uint32_t)(((nq >> 1) - 1) & 1));
+        }
+        tc_fence_after();
+        const uint64_t xh = make_desc(s_base + S::off_xh + ((uint32_t)(ng % XB) * NSPLIT) * S::XHB, LBO_BYTES, SBO_W), xl = xh + (S::XHB >> 4);
+        const uint32_t d = tmem_base + TMEM_A;
+        const uint64_t wrow = (uint64_t)(((uint32_t)(q * 64 / 8) * SBO_W) >> 4);
+        const uint64_t wh = wk_hi + wrow, wl = wk_lo + wrow;
+#pragma unroll
+        for (int ks = 0; ks < KC / 16; ++ks) {
+            const uint64_t ko = (uint64_t)((ks * 2 * LBO_BYTES) >> 4);
+            umma_bf16(d, xh + ko, wh + ko, idesc_a2, ks > 0 ? 1u : 0u);
+            if (NSPLIT == 2) {
+                umma_bf16(d, xl + ko, wh + ko, idesc_a2, 1);
+                umma_bf16(d, xh + ko, wl + ko, idesc_a2, 1);
+            }
+        }
+        umma_commit(&a_full[0]);
+        umma_commit(&a_full[1]);
+        if (q == 2) umma_commit(&xh_free[ng % XB]);     // this issuer's last read of the step's image
+    };
+    // Layer 0 (two image buffers): a THIRD issuer thread (the second loader warp, whose x staging the first one takes over) issues
+    // the gate recompute on its own, as soon as the gate slots are read out and the image is there, instead of issuer A doing
+    // it after a quarter's dgrad: A's wait for the da image no longer delays the gates the epilogue needs two quarters later.
     // register rebalancing between warpgroups: the loader/MMA group releases registers, the epilogue groups take them
     if (warp < BW_EPI_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(LAYER0 ? BW_EPI_REGS : BW_EPI_REGS_EL));
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(LAYER0 ? BW_AUX_REGS : BW_AUX_REGS_EL));
@@ -1016,10 +1057,17 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
         // their columns of the combined image; completion through complete_tx on xh_full.  Layer 0: both warps stage the
         // 16 x-columns from the fp32 input.
         const int lw = warp - BW_EPI_WARPS;
+        if (ISSUER_C && lw == 1) {
+            // ================================= MMA issuer C: gate recompute, pair after pair =================================
+            if (lane == 0)
+                for (int64_t nq = 0; nq < total_q; nq += 2) issue_recompute_pair(nq);
+            __syncwarp();
+        } else {
         const int rg_r = tile_rr(lane), qq = tile_q(lane);
         int64_t g = 0;
         int ntr = 0;
         const bool tracer = lw == 0 && lane == 0;
+        constexpr int STAGE_RG = ISSUER_C ? 16 : 8;             // row groups of the x columns this warp stages (layer 0)
         constexpr uint32_t XH_TX = NSPLIT * TM * TH * 2 * (LAYER0 ? 1 : 2);      // bytes the bulk copies deliver per image
         for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int64_t r0 = tile * TM;
@@ -1029,7 +1077,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
-                if (!LAYER0 && lw != 0) continue;
+                if ((!LAYER0 || ISSUER_C) && lw != 0) continue;
                 if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
                 if (tracer) trace_ev(1, 1, 0, g, ntr);
                 if (lw == 0) {
@@ -1048,10 +1096,31 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         }
                     }
                 }
-                if (LAYER0) {
+                if (LAYER0 && ISSUER_C && kin == 3 && rows_live >= TM && (N & 3) == 0) {
+                    // x part, whole tile, three features: the tile's 128 rows x 3 floats are 1,536 contiguous, 16-byte aligned bytes --
+                    // three 128-bit loads per lane bring rows 4 lane .. 4 lane + 3; each row becomes one 16-byte slot
+                    // [x0, x1, x2, 1, 0, 0, 0, 0] (hi and lo) of the first k-group.  The second k-group of the x columns stays zero
+                    // (zeroed once, never written).
+                    const float4* src4 = reinterpret_cast<const float4*>(xin + ((int64_t)t * N + r0) * 3) + 3 * lane;
+                    const float4 a = src4[0], b = src4[1], c = src4[2];
+                    const float xr[4][3] = {{a.x, a.y, a.z}, {a.w, b.x, b.y}, {b.z, b.w, c.x}, {c.y, c.z, c.w}};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int row = 4 * lane + j;
+                        uint4 hi4 = make_uint4(0, 0, 0, 0), lo4 = make_uint4(0, 0, 0, 0);
+                        split2(xr[j][0], xr[j][1], hi4.x, lo4.x);
+                        split2(xr[j][2], 1.0f, hi4.y, lo4.y);       // constant-one column: its weight-gradient row is the bias gradient
+                        const uint32_t o = (uint32_t)(row >> 3) * SBO_W + (uint32_t)(row & 7) * 16;
+                        *reinterpret_cast<uint4*>(xh_hi + o) = hi4;
+                        if (NSPLIT == 2) *reinterpret_cast<uint4*>(xh_lo + o) = lo4;
+                    }
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&xh_full[buf]);
+                } else if (LAYER0) {
                     // x part: 16 columns, lane quarter qq covers columns 4qq .. 4qq+3 of its row
 #pragma unroll
-                    for (int rgi = 0; rgi < 8; ++rgi) {
+                    for (int rgi = 0; rgi < STAGE_RG; ++rgi) {
                         const int rg = lw * 8 + rgi;
                         const int rr = rg * 8 + rg_r;
                         float x4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -1096,6 +1165,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 if (tracer) trace_ev(1, 2, 0, g, ntr);
             }
         }
+        }
     } else if (warp == BW_EPI_WARPS + LOADER_WARPS) {
         // ===================================== MMA issuer A: dgrad + gate recompute ===============================
         // Descriptors are built once; per MMA only a 64-bit add of a compile-time offset remains (the single issuing
@@ -1111,38 +1181,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             for (int b = 0; b < XB; ++b) xk_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, LBO_BYTES, SBO_W);
 #pragma unroll
             for (int b = 0; b < DB; ++b) dak_hi[b] = make_desc(s_base + S::off_da + b * DA_BUF, LBO_BYTES, SBO_DA);
-            // Gates of the quarter PAIR (nq, nq + 1), nq even -> TMEM slots 0 and 1 with ONE N = 128 MMA per product and k-step:
-            // a tcgen05.mma of this size costs ~60 clk of fixed overhead plus ~0.43 clk per column of N (measured), so two
-            // N = 64 quarters cost 174 clk and the pair 115.  Waits for both slots to be read out and for the image of its step.
-            constexpr uint32_t idesc_a2 = make_idesc_bf16(TM, 128, 0, 0);
-            auto issue_recompute_pair = [&](int64_t nq) {
-                const int64_t ng = nq >> 2;
-                const int q = (int)(nq & 3);                                   // 0 or 2
-                if (q == 0) mbar_wait(&xh_full[ng % XB], (uint32_t)((ng / XB) & 1));
-                if (nq >= 2) {
-                    mbar_wait(&a_free[0], (uint32_t)(((nq >> 1) - 1) & 1));
-                    mbar_wait(&a_free[1], (uint32_t)(((nq >> 1) - 1) & 1));
-                }
-                tc_fence_after();
-                const uint64_t xh = xk_hi[ng % XB], xl = xh + (S::XHB >> 4);
-                const uint32_t d = tmem_base + TMEM_A;
-                const uint64_t wrow = (uint64_t)(((uint32_t)(q * 64 / 8) * SBO_W) >> 4);
-                const uint64_t wh = wk_hi + wrow, wl = wk_lo + wrow;
-#pragma unroll
-                for (int ks = 0; ks < KC / 16; ++ks) {
-                    const uint64_t ko = (uint64_t)((ks * 2 * LBO_BYTES) >> 4);
-                    umma_bf16(d, xh + ko, wh + ko, idesc_a2, ks > 0 ? 1u : 0u);
-                    if (NSPLIT == 2) {
-                        umma_bf16(d, xl + ko, wh + ko, idesc_a2, 1);
-                        umma_bf16(d, xh + ko, wl + ko, idesc_a2, 1);
-                    }
-                }
-                umma_commit(&a_full[0]);
-                umma_commit(&a_full[1]);
-                if (q == 2) umma_commit(&xh_free[ng % XB]);     // this issuer's last read of the step's image
-            };
             int ntr = 0;
-            issue_recompute_pair(0);
+            if (!ISSUER_C) issue_recompute_pair(0);
             for (int64_t qi = 0; qi < total_q; ++qi) {
                 const int64_t g = qi >> 2;
                 const int q = (int)(qi & 3);
@@ -1175,7 +1215,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 trace_ev(2, 2, q, g, ntr);
                 // ---- next pair of gate quarters: (q2, q3) of this step after quarter 0, (q0, q1) of the next step after
                 //      quarter 2 when its image is already staged (XB == 2)
-                if ((q == 0 || (q == 2 && XB == 2)) && qi + 2 < total_q) issue_recompute_pair(qi + 2);
+                if (!ISSUER_C && (q == 0 || (q == 2 && XB == 2)) && qi + 2 < total_q) issue_recompute_pair(qi + 2);
                 trace_ev(2, 3, q, g, ntr);
                 // (Measured: issuing this recompute BEFORE the quarter's dgrad -- the epilogue waits ~2 k clk per step for these gates in
                 // layer 0 -- is slower, 15.8-16.4 vs 13.8 ms: the issuer then sits in the wait for the second gate slot while the da
