@@ -724,7 +724,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     // The [x_t | h_{t-1}] image is assembled by the TMA engine from the stashed operand images (1 KB per row group and part);
     // only layer 0's 16 x-columns (fp32 input, K = 3 plus the constant-one column) are staged by the loader warps.
     constexpr bool RB_EARLY = XB == 1;                     // see the top of the quarter loop
-    constexpr bool ISSUER_C = B200_ISSUER_C && LAYER0 && XB == 2;   // see below (third MMA issuer thread)
+    constexpr bool ISSUER_C = B200_ISSUER_C && LAYER0 && XB == 2;   // see below (third MMA issuer thread; layers > 0 measured 21.4 vs 17.7 ms with it)
 #ifndef B200_ROLLQ_L0
 #define B200_ROLLQ_L0 false     // measured (B = 4096, image-stash kernels): layer 0 unrolled 13.55 ms, rolled 14.3 ms;
 #define B200_ROLLQ_LN true      //          layer > 0 rolled 19.5 ms, unrolled 21.1 ms
@@ -1224,7 +1224,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 // line up BEHIND them in the in-order tensor pipe -- is slower, 15.8 vs 13.6 ms in layer 0 and 20.5 vs 17.7 ms above: the
                 // wgrad MMAs release the da and image buffers the epilogue and the loader wait for, they are just as critical.)
                 // single-buffered image: the next step's first pair can only be recomputed after the reload
-                if (XB == 1 && q == 3 && qi + 1 < total_q) {
+                if (!ISSUER_C && XB == 1 && q == 3 && qi + 1 < total_q) {
                     issue_recompute_pair(qi + 1);
                     trace_ev(2, 5, q, g, ntr);
                 }
