@@ -569,6 +569,9 @@ constexpr int BW_LAUNCH_REGS = BW_EU == 8 ? 168 : 96;      // 65,536 / threads r
 constexpr int BW_EPI_REGS = BW_EU == 8 ? 200 : 104, BW_AUX_REGS = BW_EU == 8 ? 104 : 64;
 // kernels whose epilogue warps stage the operand image themselves (idle loader warps): 208 / 88 measured 0.6 ms faster in the
 // layer > 0 kernel (fewer epilogue spills) and 1.3 ms SLOWER in the layer-0 kernel (its loader warps then spill)
+#ifndef B200_WGRAD_SINGLE
+#define B200_WGRAD_SINGLE 1
+#endif
 #ifndef B200_ISSUER_C
 #define B200_ISSUER_C 1
 #endif
@@ -1237,7 +1240,12 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
     } else {
         // ===================================== MMA issuer B: wgrad ==================================================
         if (lane == 0 && total_q > 0) {
-            constexpr int WN = 64 * DB;                                       // quarters per MMA: one (DB == 1) or a pair (DB == 2)
+            // Quarters per MMA.  A pair as ONE N = 128 MMA halves the instruction count (two da buffers), but then the first buffer of
+            // the pair is only released after the SECOND quarter's da image exists: with the gate recompute on its own issuer
+            // (ISSUER_C) the event trace showed the epilogue waiting ~1 k clk per quarter for a free da buffer, so there the weight
+            // gradient is issued quarter by quarter (N = 64), right behind each quarter's dgrad.
+            constexpr int WQ = (DB == 2 && !(ISSUER_C && B200_WGRAD_SINGLE)) ? 2 : 1;
+            constexpr int WN = 64 * WQ;
             constexpr uint32_t idesc_w = make_idesc_bf16(TM, WN, 1, 1);       // wgrad: both MN-major
             const uint32_t s_base = smem_u32(smem);
             uint64_t xm_hi[XB];
@@ -1245,18 +1253,19 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
             for (int b = 0; b < XB; ++b) xm_hi[b] = make_desc(s_base + S::off_xh + (b * NSPLIT) * S::XHB, SBO_W, LBO_BYTES);
             const uint64_t dam_hi = make_desc(s_base + S::off_da, SBO_DA, LBO_BYTES), dam_lo = dam_hi + (DA_LO >> 4);
             int ntr = 0;
-            for (int64_t qi = 0; qi < total_q; qi += DB) {
+            for (int64_t qi = 0; qi < total_q; qi += WQ) {
                 const int64_t g = qi >> 2;
                 const int q = (int)(qi & 3);
+                const int buf0 = (int)(qi % DB);
 #pragma unroll
-                for (int b = 0; b < DB; ++b) mbar_wait(&da_full[b], (uint32_t)((qi / DB) & 1));
+                for (int b = 0; b < WQ; ++b) mbar_wait(&da_full[(buf0 + b) % DB], (uint32_t)((qi / DB) & 1));
                 tc_fence_after();
                 // dWcat^T[:, quarter (pair) columns] += xh^T * da, K = the 128 rows of the tile
                 const uint32_t d = tmem_base + TMEM_DW + q * 64;
                 const uint64_t xh = xm_hi[g % XB], xl = xh + (S::XHB >> 4);
 #pragma unroll
                 for (int ks = 0; ks < TM / 16; ++ks) {
-                    const uint64_t xo = (uint64_t)((ks * 2 * SBO_W) >> 4), dao = (uint64_t)((ks * 2 * SBO_DA) >> 4);
+                    const uint64_t xo = (uint64_t)((ks * 2 * SBO_W) >> 4), dao = (uint64_t)((ks * 2 * SBO_DA + (uint32_t)buf0 * DA_BUF) >> 4);
                     umma_bf16(d, xh + xo, dam_hi + dao, idesc_w, (g > 0 || ks > 0) ? 1u : 0u);
                     if (NSPLIT == 2) {
                         // All three split products.  Measured (tools/grad_margin.py, per-tensor max error / max gradient): dropping
@@ -1268,8 +1277,8 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                     }
                 }
 #pragma unroll
-                for (int b = 0; b < DB; ++b) umma_commit(&da_free[b]);      // second arrival
-                if (q + DB == 4) umma_commit(&xh_free[g % XB]);
+                for (int b = 0; b < WQ; ++b) umma_commit(&da_free[(buf0 + b) % DB]);      // second arrival
+                if (q + WQ == 4) umma_commit(&xh_free[g % XB]);
                 trace_ev(3, 4, q, g, ntr);
             }
             umma_commit(done);
