@@ -1086,16 +1086,16 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 if (lw == 0) {
                     if (lane == 0) mbar_arrive_expect_tx(&xh_full[buf], XH_TX);
                     __syncwarp();
-                    if (lane < 16) {
-                        const uint8_t* hsrc = (t > 0 ? himg + img_off(t - 1, tile, ntiles) : zero_blk) + (uint32_t)lane * 1024u;
-                        uint8_t* dh_ = xh_hi + (uint32_t)lane * SBO_W + (uint32_t)(KX / 8) * LBO_BYTES;
+                    // lane = (image half: hi | lo, row group): every lane issues the h slice and (layers > 0) the x slice of its row group
+                    const int rg16 = lane & 15, part = lane >> 4;
+                    if (part < NSPLIT) {
+                        const uint32_t so = (uint32_t)part * IMG_HALF + (uint32_t)rg16 * 1024u;
+                        const uint8_t* hsrc = (t > 0 ? himg + img_off(t - 1, tile, ntiles) : zero_blk) + so;
+                        uint8_t* dh_ = xh_hi + (uint32_t)part * S::XHB + (uint32_t)rg16 * SBO_W + (uint32_t)(KX / 8) * LBO_BYTES;
                         bulk_copy_g2s(dh_, hsrc, 1024u, &xh_full[buf]);
-                        if (NSPLIT == 2) bulk_copy_g2s(dh_ + S::XHB, hsrc + IMG_HALF, 1024u, &xh_full[buf]);
                         if (!LAYER0) {
-                            const uint8_t* xsrc = ximg_in + img_off(t, tile, ntiles) + (uint32_t)lane * 1024u;
-                            uint8_t* dx_ = xh_hi + (uint32_t)lane * SBO_W;
-                            bulk_copy_g2s(dx_, xsrc, 1024u, &xh_full[buf]);
-                            if (NSPLIT == 2) bulk_copy_g2s(dx_ + S::XHB, xsrc + IMG_HALF, 1024u, &xh_full[buf]);
+                            const uint8_t* xsrc = ximg_in + img_off(t, tile, ntiles) + so;
+                            bulk_copy_g2s(xh_hi + (uint32_t)part * S::XHB + (uint32_t)rg16 * SBO_W, xsrc, 1024u, &xh_full[buf]);
                         }
                     }
                 }
