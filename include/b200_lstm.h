@@ -82,6 +82,8 @@ B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
 /* Tuning knobs for experiments (no counterpart in the reference); process-wide, read at launch time, defaults are
  * the measured best.  The library reads no environment variables.
  *   "tc_prefetch"  bit mask of L2 prefetches in the tcgen05 kernels (csrc/lstm_tc.cu, default 39)
+ *   "tc_fwd_eh"    bit 0 / bit 1: two epilogue threads per row in the forward kernel of layers > 0 / layer 0 (default 1)
+ *   "tc_wgrad"     products of the weight gradient in layers > 0, precise mode: 3 (default), 2, or 0 = two from 2^22 row-steps on
  *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM (default 0) */
 B200_API int b200_set_option(const char* name, int value);
 

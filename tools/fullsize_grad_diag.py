@@ -11,6 +11,9 @@ import lstm_oracle as O
 import masters_thesis_b200 as B
 from _budget import device_masks, S
 
+from masters_thesis_b200._lib import load
+if len(sys.argv) > 3:          # library option for the device engines, e.g. tc_wgrad=2
+    k, _, v = sys.argv[3].partition("="); load().b200_set_option(k.encode(), int(v))
 BW = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 P = float(sys.argv[2]) if len(sys.argv) > 2 else 0.2
 dev, seed = "cuda:0", 1234
@@ -57,8 +60,10 @@ def run(dtype, device, chunk, acc64):
         if acc64: acc += O.flat_grads(om).double().cpu().numpy()
     return (acc if acc64 else O.flat_grads(om).double().cpu().numpy()), loss
 
-refs = {"cpu32_acc32": run(torch.float32, "cpu", 256, False)[0], "cpu32_acc64": run(torch.float32, "cpu", 256, True)[0],
-        "gpu64": run(torch.float64, dev, 512, True)[0]}
+quick = len(sys.argv) > 3           # with an option: only the fp64 truth (the CPU oracle legs take a minute each at full size)
+refs = {"gpu64": run(torch.float64, dev, min(512, BW), True)[0]}
+if not quick:
+    refs.update({"cpu32_acc32": run(torch.float32, "cpu", 256, False)[0], "cpu32_acc64": run(torch.float32, "cpu", 256, True)[0]})
 names, shapes = model.names, B.model._param_shapes(3, 64, 2)
 def per_tensor(a, b):
     out, off = {}, 0
@@ -68,7 +73,10 @@ def per_tensor(a, b):
     return out
 res = {"windows": BW, "dropout": P}
 for a in ("tc_precise", "ffma", "cpu32_acc32", "cpu32_acc64"):
-    res[f"{a}_vs_gpu64"] = per_tensor(grads[a] if a in grads else refs[a], refs["gpu64"])
-res["tc_precise_vs_cpu32_acc32"] = per_tensor(grads["tc_precise"], refs["cpu32_acc32"])
-res["tc_precise_vs_cpu32_acc64"] = per_tensor(grads["tc_precise"], refs["cpu32_acc64"])
+    if a in grads or a in refs:
+        res[f"{a}_vs_gpu64"] = per_tensor(grads[a] if a in grads else refs[a], refs["gpu64"])
+if not quick:
+    res["tc_precise_vs_cpu32_acc32"] = per_tensor(grads["tc_precise"], refs["cpu32_acc32"])
+    res["tc_precise_vs_cpu32_acc64"] = per_tensor(grads["tc_precise"], refs["cpu32_acc64"])
+res["option"] = sys.argv[3] if quick else None
 print(json.dumps(res))
