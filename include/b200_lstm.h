@@ -84,6 +84,7 @@ B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
  *   "tc_prefetch"  bit mask of L2 prefetches in the tcgen05 kernels (csrc/lstm_tc.cu, default 39)
  *   "tc_fwd_eh"    bit 0 / bit 1: two epilogue threads per row in the forward kernel of layers > 0 / layer 0 (default 1)
  *   "tc_wgrad"     products of the weight gradient in layers > 0, precise mode: 3 (default), 2, or 0 = two from 2^22 row-steps on
+ *   "tc_dgrad"     products of the data gradient, precise mode: 3 (default) or 2
  *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM (default 0) */
 B200_API int b200_set_option(const char* name, int value);
 

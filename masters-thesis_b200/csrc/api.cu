@@ -74,6 +74,7 @@ bool tc_available();
 void tc_set_prefetch(int mask);
 void tc_set_fwd_eh(int eh);
 void tc_set_wgrad(int v);
+void tc_set_dgrad(int v);
 void wide_set_fuse(int on);
 size_t tc_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L);
 int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
@@ -116,10 +117,11 @@ extern "C" int b200_timing_enable(int on) {
 extern "C" int b200_set_option(const char* name, int value) {
     B200_CHECK_ARG(name != nullptr, "set_option: null name");
     if (strcmp(name, "tc_prefetch") == 0) { tc_set_prefetch(value); return B200_OK; }
+    if (strcmp(name, "tc_dgrad") == 0) { tc_set_dgrad(value); return B200_OK; }
     if (strcmp(name, "tc_wgrad") == 0) { tc_set_wgrad(value); return B200_OK; }
     if (strcmp(name, "tc_fwd_eh") == 0) { tc_set_fwd_eh(value); return B200_OK; }
     if (strcmp(name, "wide_fuse") == 0) { wide_set_fuse(value); return B200_OK; }
-    set_error("set_option: unknown option '%s' (known: tc_prefetch, tc_fwd_eh, tc_wgrad, wide_fuse)", name);
+    set_error("set_option: unknown option '%s' (known: tc_prefetch, tc_fwd_eh, tc_wgrad, tc_dgrad, wide_fuse)", name);
     return B200_ERR_INVALID;
 }
 

@@ -49,6 +49,8 @@ static int g_tc_prefetch = PF_DEFAULT;
 void tc_set_prefetch(int mask) { g_tc_prefetch = mask; }
 static int g_tc_wgrad = 3;           // option "tc_wgrad" (see tc_bwd_layer); default: always three products
 void tc_set_wgrad(int v) { g_tc_wgrad = v; }
+static int g_tc_dgrad = 3;
+void tc_set_dgrad(int v) { g_tc_dgrad = v; }
 static int g_tc_fwd_eh = 1;          // (default: layer > 0 only; measured 5.15 vs 5.72 ms there, neutral in layer 0) option "tc_fwd_eh": bit 0 = two epilogue threads per row in the layer > 0 forward kernel, bit 1 = in layer 0
 void tc_set_fwd_eh(int mask) { g_tc_fwd_eh = mask & 3; }
 #ifdef B200_ABLATE                    // timing experiments only (build with B200_ABLATE=1): env B200_TC_DBG is a bit mask of backward
@@ -709,7 +711,7 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                    const float* __restrict__ c_st, const float* __restrict__ d_out,
                    const float* __restrict__ dhT, float* __restrict__ d_in, float* __restrict__ wpart,
                    float* __restrict__ bpart, const uint64_t* __restrict__ drop_bits, float p, uint64_t drop_seed, int drop_layer,
-                   uint32_t drop_thr, int pf_mask, int wgrad3) {
+                   uint32_t drop_thr, int pf_mask, int wgrad3, int dgrad3) {
     // wgrad3 == 0: the weight gradient is accumulated from two products (x_hi da_hi + x_hi da_lo) instead of three; see tc_bwd_layer
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     if (!LAYER0 && drop_bits != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
@@ -1208,10 +1210,9 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                         const uint64_t ak = (uint64_t)((gate * 2 * LBO_BYTES) >> 4);
                         umma_bf16(d, dah + ak, wm_hi + wk, idesc_d, (q > 0 || gate > 0) ? 1u : 0u);
                         if (NSPLIT == 2) {
-#ifndef B200_DGRAD2          // experiment switch: without da_lo * W_hi the layer-0 kernel is 0.85 ms faster, but per-tensor gradient
-                             // errors reach 8.5e-4 of the 1e-3 gate (4-layer dropout case, tools/grad_margin.py) -> not the default
-                            umma_bf16(d, dal + ak, wm_hi + wk, idesc_d, 1);
-#endif
+                            // dgrad3 == 0 (option "tc_dgrad"): without da_lo * W_hi.  At 200 sequences the per-tensor gradient error then
+                            // reaches 8.5e-4 of the 1e-3 gate (4-layer dropout case, tools/grad_margin.py); see tc_bwd_layer
+                            if (dgrad3) umma_bf16(d, dal + ak, wm_hi + wk, idesc_d, 1);
                             umma_bf16(d, dah + ak, wm_lo + wk, idesc_d, 1);
                         }
                     }
@@ -1582,14 +1583,14 @@ int tc_fwd(int mode, const float* params, int F, int H, int L, const float* x, i
 template <int NSPLIT, bool LAYER0, int XB, int DB>
 static int launch_bwd(const uint8_t* packed, const float* xin, const uint8_t* ximg_in, int kin, int64_t N, int T, const uint8_t* himg,
                       const uint8_t* zero, const float* c_st, const float* d_out, const float* dhT, float* d_in, float* wpart,
-                      float* bpart, const uint64_t* drop_bits, float p, uint64_t seed, int layer, int grid, int wgrad3, cudaStream_t st) {
+                      float* bpart, const uint64_t* drop_bits, float p, uint64_t seed, int layer, int grid, int wgrad3, int dgrad3, cudaStream_t st) {
     using S = BwdSmem<NSPLIT, LAYER0, XB, DB>;
     auto kern = lstm_tc_bwd_kernel<NSPLIT, LAYER0, XB, DB>;
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     {
         TimedLaunch _t(LAYER0 ? "lstm_tc_bwd_kernel_l0" : "lstm_tc_bwd_kernel_lN", st);
         kern<<<grid, BW_THREADS, S::total, st>>>(packed, xin, ximg_in, kin, N, T, himg, zero, c_st, d_out, dhT, d_in, wpart, bpart, drop_bits,
-                                                 p, seed, layer, dropout_threshold(p), g_tc_prefetch, wgrad3);
+                                                 p, seed, layer, dropout_threshold(p), g_tc_prefetch, wgrad3, dgrad3);
     }
     B200_LAUNCH_CHECK("lstm_tc_bwd_kernel");
     return B200_OK;
@@ -1634,15 +1635,16 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
     // tools/fullsize_grad_diag.py); smaller batches and layer 0 (raw inputs, few features) keep all three products.
     // Option "tc_wgrad": 0 = this rule, 3 = always three products, 2 = always two in layers > 0.
     const int wgrad3 = (layer0 || g_tc_wgrad == 3) ? 1 : (g_tc_wgrad == 2 ? 0 : ((int64_t)N * T >= (1LL << 22) ? 0 : 1));
+    const int dgrad3 = g_tc_dgrad == 2 ? 0 : 1;           // option "tc_dgrad": 3 (default) or 2 products in the data gradient
     // keep bits of this layer's input were built by the forward pass of the same step (same workspace); the kernel checks
     // the tag behind them against (seed, layer, N, T, p) and aborts on a mismatch
     const uint64_t* bits = (!layer0 && drop) ? tail.bits + (size_t)(layer - 1) * (tc_bits_bytes(N, T) / 8) : nullptr;
     if (layer0)
-        rc = precise ? launch_bwd<2, true, 2, 2>(pk, x, nullptr, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, wgrad3, st)
-                     : launch_bwd<1, true, 2, 2>(pk, x, nullptr, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, wgrad3, st);
+        rc = precise ? launch_bwd<2, true, 2, 2>(pk, x, nullptr, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, wgrad3, dgrad3, st)
+                     : launch_bwd<1, true, 2, 2>(pk, x, nullptr, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, nullptr, p, seed, layer, grid, wgrad3, dgrad3, st);
     else
-        rc = precise ? launch_bwd<2, false, 1, 1>(pk, nullptr, ximg_in, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, wgrad3, st)
-                     : launch_bwd<1, false, 2, 2>(pk, nullptr, ximg_in, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, wgrad3, st);
+        rc = precise ? launch_bwd<2, false, 1, 1>(pk, nullptr, ximg_in, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, wgrad3, dgrad3, st)
+                     : launch_bwd<1, false, 2, 2>(pk, nullptr, ximg_in, kin, N, T, himg, tail.zero, c_st, d_out, dhT, d_in, wpart, bpart, bits, p, seed, layer, grid, wgrad3, dgrad3, st);
     if (rc) return rc;
     float* gbase = grads + b200_param_offset(F, TH, L, layer);
     float* gw_ih = gbase;
