@@ -84,7 +84,10 @@ int tc_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, 
                  int training, void* workspace, size_t ws_bytes, cudaStream_t st);
 int tc_hidden_states(int mode, int layer, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st);
 // wide engine (lstm_wide.cu): hidden sizes other than 64 in the tensor-core modes
-size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L);
+size_t wide_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L);
+void wide_set_images(int on);
+bool wide_uses_images(int mode, int H, int F);
+int wide2_hidden_states(int layer, int F, int H, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st);
 int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
              float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st);
 int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T,
@@ -121,7 +124,8 @@ extern "C" int b200_set_option(const char* name, int value) {
     if (strcmp(name, "tc_wgrad") == 0) { tc_set_wgrad(value); return B200_OK; }
     if (strcmp(name, "tc_fwd_eh") == 0) { tc_set_fwd_eh(value); return B200_OK; }
     if (strcmp(name, "wide_fuse") == 0) { wide_set_fuse(value); return B200_OK; }
-    set_error("set_option: unknown option '%s' (known: tc_prefetch, tc_fwd_eh, tc_wgrad, tc_dgrad, wide_fuse)", name);
+    if (strcmp(name, "wide_images") == 0) { wide_set_images(value); return B200_OK; }
+    set_error("set_option: unknown option '%s' (known: tc_prefetch, tc_fwd_eh, tc_wgrad, tc_dgrad, wide_fuse, wide_images)", name);
     return B200_ERR_INVALID;
 }
 
@@ -175,7 +179,7 @@ static int check_lstm_args(const char* who, int mode, const float* params, int F
 extern "C" size_t b200_lstm_workspace_bytes(int mode, int64_t n_seq, int T, int n_features, int hidden, int layers) {
     if (n_seq <= 0 || T <= 0 || layers <= 0) return 0;
     // generous default: room for a 64 Ki-sequence da chunk; callers may pass less (smaller chunks)
-    if (hidden != 64) return mode == B200_MODE_FFMA ? 0 : wide_workspace_bytes(n_seq, T, n_features, hidden, layers);
+    if (hidden != 64) return mode == B200_MODE_FFMA ? 0 : wide_workspace_bytes(mode, n_seq, T, n_features, hidden, layers);
     size_t ffma = ffma_workspace_bytes(n_seq, T, layers);
     if (mode == B200_MODE_FFMA) return ffma;
     size_t tc = tc_workspace_bytes(mode, n_seq, T, n_features, hidden, layers);
@@ -229,11 +233,14 @@ extern "C" int b200_lstm_bwd(int mode, const float* params, int n_features, int 
 
 extern "C" int b200_lstm_hidden_states(int mode, int layer, int n_features, int hidden, int layers, int64_t n_seq, int T,
                                        const float* stash_h, const void* workspace, size_t workspace_bytes, float* out, void* stream) {
-    (void)n_features;
     B200_CHECK_ARG(mode >= 0 && mode <= 2 && layer >= 0 && layer < layers && n_seq > 0 && T > 0 && out, "lstm_hidden_states: bad arguments");
     if (hidden == 64 && mode != B200_MODE_FFMA) {
         B200_CHECK_ARG(workspace != nullptr, "lstm_hidden_states: the tcgen05 engines keep the hidden states in the workspace");
         return tc_hidden_states(mode, layer, layers, n_seq, T, workspace, workspace_bytes, out, (cudaStream_t)stream);
+    }
+    if (hidden != 64 && wide_uses_images(mode, hidden, n_features)) {
+        B200_CHECK_ARG(workspace != nullptr, "lstm_hidden_states: the bf16 wide engine keeps the hidden states in the workspace");
+        return wide2_hidden_states(layer, n_features, hidden, layers, n_seq, T, workspace, workspace_bytes, out, (cudaStream_t)stream);
     }
     B200_CHECK_ARG(stash_h != nullptr, "lstm_hidden_states: null stash");
     const size_t lsz = (size_t)T * n_seq * hidden;

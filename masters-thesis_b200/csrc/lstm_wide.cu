@@ -621,7 +621,20 @@ LayerParams layer_params(const float* params, int F, int H, int l) {
 
 }  // namespace
 
-size_t wide_workspace_bytes(int64_t N, int T, int F, int H, int L) {
+// bf16 mode (B200_MODE_TC_FAST) at hidden 128 / 256: the operand-image engine of lstm_wide2.cu
+bool wide2_supported(int H, int F);
+size_t wide2_workspace_bytes(int64_t N, int T, int F, int H, int L);
+int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h, float* stash_c, float p,
+              uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st);
+int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T, const float* stash_h,
+                    const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed, int training, void* workspace,
+                    size_t ws_bytes, cudaStream_t st);
+static int g_wide_images = 1;         // option "wide_images": 0 = bf16 mode on the fp32-storage path below (comparison runs)
+void wide_set_images(int on) { g_wide_images = on; }
+bool wide_uses_images(int mode, int H, int F) { return mode == B200_MODE_TC_FAST && g_wide_images != 0 && wide2_supported(H, F); }
+
+size_t wide_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L) {
+    if (wide_uses_images(mode, H, F)) return wide2_workspace_bytes(N, T, F, H, L);
     const size_t lsz = (size_t)T * N * H * 4;
     return al256((size_t)L * lsz * 4) + 3 * al256(lsz) + 2 * al256((size_t)N * H * 4) + al256(wide_part_floats(H, F) * 4) +
            al256(wide_bsum_floats() * 4) + 4 * wide_pack_region(H) + 256;
@@ -640,9 +653,10 @@ int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x,
              float* stash_c, float p, uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
     int rc = wide_check("lstm_fwd", H, F);
     if (rc) return rc;
+    if (wide_uses_images(mode, H, F)) return wide2_fwd(params, F, H, L, x, N, T, stash_h, stash_c, p, seed, training, workspace, ws_bytes, st);
     WideWs w;
     B200_CHECK_ARG(wide_ws(workspace, ws_bytes, N, T, F, H, L, &w), "lstm_fwd (wide): workspace too small (%zu bytes, need %zu)", ws_bytes,
-                   wide_workspace_bytes(N, T, F, H, L));
+                   wide_workspace_bytes(mode, N, T, F, H, L));
     const int nsplit = mode == B200_MODE_TC_PRECISE ? 2 : 1;
     const bool drop = training && p > 0.f;
     const int64_t lsz = (int64_t)T * N * H, NH = N * H, G4 = 4LL * H;
@@ -702,6 +716,8 @@ int wide_bwd_layer(int mode, int layer, const float* params, int F, int H, int L
                    int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
     int rc = wide_check("lstm_bwd", H, F);
     if (rc) return rc;
+    if (wide_uses_images(mode, H, F))
+        return wide2_bwd_layer(layer, params, F, H, L, x, N, T, stash_h, stash_c, dhT, grads, p, seed, training, workspace, ws_bytes, st);
     WideWs w;
     B200_CHECK_ARG(wide_ws(workspace, ws_bytes, N, T, F, H, L, &w), "lstm_bwd (wide): workspace too small (%zu bytes)", ws_bytes);
     const int nsplit = mode == B200_MODE_TC_PRECISE ? 2 : 1;

@@ -1,0 +1,960 @@
+// Wide-model LSTM engine, bf16 mode (B200_MODE_TC_FAST, BASELINE.json configs[2]: hidden 256, 8 layers, bf16 GEMMs with fp32
+// accumulation).  Every operand of every GEMM lives in global memory as ready-made UMMA operand images, so the kernels move
+// them with bulk copies only (no thread touches an operand on its way to the tensor core), and the LSTM cell runs in the
+// epilogue of the forward GEMM.  lstm_wide.cu keeps the fp32-storage path of B200_MODE_TC_PRECISE.
+//
+// Chunk = the [128 rows x 64 columns] bf16 operand image in the interleaved (SWIZZLE_NONE) layout of tc_common.cuh, 16 KB:
+//     byte(r, c) = (r / 8) * 1024 + (c / 8) * 128 + (r % 8) * 16 + (c % 8) * 2
+// Read K-major it is a [128 x K = 64] operand; read MN-major the same bytes are a [K = 128 rows x 64] operand, and any 8-row
+// group of it is 1 KB of contiguous memory.  With NT = ceil(N / 128) row tiles, HC = H / 64, UG = H / 32, GC = 4H / 64:
+//   Himg[l]  [T][NT][HC] chunks   h_t of layer l (written by the forward epilogue); under dropout a second, masked set is the
+//                                 input of layer l + 1 (the 1/(1-p) lives in the packed W_ih, as in lstm_tc.cu)
+//   X0img    [T][NT][1]  chunk    the F input features of layer 0, columns >= F zero
+//   Gimg[l]  [T][NT][GC] chunks   activated gates (forward) -> pre-activation gradients dG (backward, in place); gate columns
+//                                 are permuted: g' = (u / 32) * 128 + gate * 32 + u % 32, so that the four gates of 32 hidden
+//                                 units are one 128-column block (one N tile of the forward GEMM, one M tile of the weight gradient)
+//   Wf[l]    [UG][KC] chunks      rows g' of [W_ih | W_hh], KC = (1 or HC) + HC K-chunks
+//   Wd[l]    per part (h, x): [GC][64 g' rows x (64 * HC) columns] MN-major images for dG . W
+//
+//   forward  step t: w2_fwd_kernel    gates = [x_t | h_{t-1}] . Wf^T, cell in the epilogue; persistent CTAs, each keeps the weights
+//                                     of one unit group (128 KB) in shared memory and streams the A chunks of its row tiles
+//   backward step t: w2_cell_bwd_kernel  (dh, dc, gates, c_{t-1}) -> dG, dc_{t-1}, bias-gradient partials
+//                    w2_dgrad_kernel      [dh_{t-1} | dx_t] = dG_t . Wd          two 128 x 256 accumulators per CTA
+//            layer:  w2_wgrad_kernel      d[W_ih | W_hh] = dG^T . [x | h_{t-1}]  over all steps, split-K, both operands MN-major
+//
+// Replaces, for hidden != 64 in bf16 mode: nn.LSTM forward / backward under autocast (src/model.py:88-109, train.py:172
+// precision), as lstm_tc.cu does for hidden 64.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace b200 {
+using namespace tc;
+
+namespace {
+
+constexpr int TM = 128;
+constexpr uint32_t CHUNK = 16384, RG_BYTES = 1024;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr int W2_THREADS = 320;                 // 8 epilogue warps, loader warp, MMA warp
+
+__host__ __device__ inline size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
+__host__ __device__ inline uint32_t chunk_off(int r, int c) {
+    return (uint32_t)(r >> 3) * 1024u + (uint32_t)(c >> 3) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(c & 7) * 2u;
+}
+
+struct Geom {
+    int F, H, L, T;
+    int64_t N;
+    int NT, HC, UG, GC;
+    __host__ __device__ int xc(int l) const { return l == 0 ? 1 : HC; }       // K-chunks of the layer input
+    __host__ __device__ int kc(int l) const { return xc(l) + HC; }
+};
+inline Geom make_geom(int64_t N, int T, int F, int H, int L) {
+    Geom g;
+    g.F = F; g.H = H; g.L = L; g.T = T; g.N = N;
+    g.NT = (int)((N + TM - 1) / TM);
+    g.HC = H / 64; g.UG = H / 32; g.GC = H / 16;
+    return g;
+}
+
+__device__ __forceinline__ uint32_t pack_bf2(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint4 pack_bf8(const float (&v)[8]) {
+    return make_uint4(pack_bf2(v[0], v[1]), pack_bf2(v[2], v[3]), pack_bf2(v[4], v[5]), pack_bf2(v[6], v[7]));
+}
+__device__ __forceinline__ void unpack_bf8(const uint4 q, float (&v)[8]) {
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+    }
+}
+__device__ __forceinline__ void ld8(const float* p, float (&v)[8]) {
+    const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void st8(float* p, const float (&v)[8]) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+// keep mask of 8 consecutive units (bit j = keep unit j) -> AND masks for the four bf16 pairs
+__device__ __forceinline__ uint4 and_mask8(uint4 q, uint32_t kb) {
+    uint32_t km[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) km[j] = (((kb >> (2 * j)) & 1u) ? 0x0000FFFFu : 0u) | (((kb >> (2 * j + 1)) & 1u) ? 0xFFFF0000u : 0u);
+    return make_uint4(q.x & km[0], q.y & km[1], q.z & km[2], q.w & km[3]);
+}
+
+// ------------------------------------------------------------------------------------------------ small kernels
+// Packed weights of one layer: Wf chunks, Wd images (h part, then x part), bias' [UG][4][32] (see w2_fwd_kernel).
+struct PackLayout {
+    size_t wf, wd_h, wd_x, bias, total;
+};
+inline PackLayout pack_layout(const Geom& g, int l) {
+    PackLayout p;
+    p.wf = 0;
+    p.wd_h = al256((size_t)g.UG * g.kc(l) * CHUNK);
+    p.wd_x = p.wd_h + al256((size_t)g.GC * 64 * g.H * 2);
+    p.bias = p.wd_x + (l > 0 ? al256((size_t)g.GC * 64 * g.H * 2) : 0);
+    p.total = p.bias + al256((size_t)4 * g.H * 4);
+    return p;
+}
+
+// in_scale: 1/(1-p) of the inter-layer dropout folded into W_ih (layers > 0)
+__global__ void __launch_bounds__(256)
+w2_pack_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, const float* __restrict__ b_ih, const float* __restrict__ b_hh,
+               int in, int H, int XC, float in_scale, uint8_t* __restrict__ wf, uint8_t* __restrict__ wd_h, uint8_t* __restrict__ wd_x,
+               float* __restrict__ biasp) {
+    const int HC = H / 64, KC = XC + HC, G4 = 4 * H;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    const int KW = KC * 64;
+    for (int64_t i = tid; i < (int64_t)G4 * KW; i += nthr) {
+        const int gp = (int)(i / KW), k = (int)(i - (int64_t)gp * KW);            // gp = permuted gate row
+        const int ug = gp >> 7, gate = (gp >> 5) & 3, u = ug * 32 + (gp & 31);
+        const int g = gate * H + u;
+        float v;
+        const bool xpart = k < XC * 64;
+        if (xpart) v = k < in ? w_ih[(int64_t)g * in + k] * in_scale : 0.f;
+        else v = w_hh[(int64_t)g * H + (k - XC * 64)];
+        const __nv_bfloat16 b = __float2bfloat16_rn(v);
+        // forward image: chunk (ug, k / 64), row gp % 128, column k % 64
+        *reinterpret_cast<__nv_bfloat16*>(wf + ((size_t)ug * KC + (k >> 6)) * CHUNK + chunk_off(gp & 127, k & 63)) = b;
+        // dgrad image: K-chunk gp / 64, k-row gp % 64, column n of the part: [8 row groups][ncols / 8 cores][128 B]
+        const int kcx = gp >> 6, kr = gp & 63;
+        if (xpart) {
+            if (wd_x != nullptr && k < H) {
+                const int n = k;
+                *reinterpret_cast<__nv_bfloat16*>(wd_x + (size_t)kcx * 64 * H * 2 + (size_t)(kr >> 3) * (H / 8) * 128 + (size_t)(n >> 3) * 128 + (kr & 7) * 16 + (n & 7) * 2) = b;
+            }
+        } else {
+            const int n = k - XC * 64;
+            *reinterpret_cast<__nv_bfloat16*>(wd_h + (size_t)kcx * 64 * H * 2 + (size_t)(kr >> 3) * (H / 8) * 128 + (size_t)(n >> 3) * 128 + (kr & 7) * 16 + (n & 7) * 2) = b;
+        }
+    }
+    for (int64_t gp = tid; gp < G4; gp += nthr) {
+        const int ug = (int)gp >> 7, gate = ((int)gp >> 5) & 3, u = ug * 32 + ((int)gp & 31);
+        const float b = b_ih[gate * H + u] + b_hh[gate * H + u];
+        biasp[gp] = gate == 2 ? 2.0f * LOG2E * b : -LOG2E * b;          // folded into the exponent argument
+    }
+}
+
+// layer-0 input as operand chunks: X0img[t][tile] (columns >= F and rows >= N zero); x is [T][N][F] fp32
+__global__ void __launch_bounds__(256)
+w2_x0_kernel(const float* __restrict__ x, int64_t N, int T, int F, int NT, uint8_t* __restrict__ out) {
+    // one thread per (t, tile, row, 8-column core)
+    const int64_t total = (int64_t)T * NT * TM * 8;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int core = (int)(i & 7), r = (int)((i >> 3) & 127);
+        const int64_t tt = i >> 10;                                   // t * NT + tile
+        const int64_t tile = tt % NT, t = tt / NT, row = tile * TM + r;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = core * 8 + j;
+            v[j] = (row < N && c < F) ? x[((int64_t)t * N + row) * F + c] : 0.f;
+        }
+        *reinterpret_cast<uint4*>(out + (size_t)tt * CHUNK + chunk_off(r, core * 8)) = pack_bf8(v);
+    }
+}
+
+// keep bits of the input of `layer`: bits[t][row][ug] (uint32: bit j = keep unit ug * 32 + j), Philox blocks of common.cuh
+__global__ void __launch_bounds__(256)
+w2_bits_kernel(uint64_t seed, int layer, int64_t N, int T, int UG, float p, uint32_t* __restrict__ bits) {
+    const uint32_t thr = dropout_threshold(p);
+    const int64_t total = (int64_t)T * N * UG;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int ug = (int)(i % UG);
+        const int64_t tr = i / UG, row = tr % N;
+        const int t = (int)(tr / N);
+        uint32_t w = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const U4 blk = dropout_block(seed, layer, row, t, ug * 4 + b);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w |= (dropout_lane16(blk, j) >= thr ? 1u : 0u) << (b * 8 + j);
+        }
+        bits[i] = w;
+    }
+}
+
+// hidden states of one layer as fp32 [T][N][H] (b200_lstm_hidden_states)
+__global__ void __launch_bounds__(256)
+w2_unpack_kernel(const uint8_t* __restrict__ himg, int64_t N, int T, int H, int NT, float* __restrict__ out) {
+    const int HC = H / 64;
+    const int64_t total = (int64_t)T * N * (H / 8);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % (H / 8));
+        const int64_t tr = i / (H / 8), row = tr % N, t = tr / N;
+        const int64_t tile = row / TM;
+        const int r = (int)(row % TM), col = c8 * 8;
+        const uint4 q = *reinterpret_cast<const uint4*>(himg + (((size_t)t * NT + tile) * HC + (col >> 6)) * CHUNK + chunk_off(r, col & 63));
+        float v[8];
+        unpack_bf8(q, v);
+        st8(out + (t * N + row) * H + col, v);
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------ forward step
+// One LSTM step of one layer for all rows.  CTA c owns unit group ug = c % UG (32 hidden units = 128 permuted gate columns, its
+// KC weight chunks stay in shared memory for the whole launch) and the row tiles m = c / UG, c / UG + gridDim.x / UG, ...
+// Per tile: KC bulk copies of 16 KB bring [x_t | h_{t-1}], 4 * KC MMAs (M 128, N 128, K 16) accumulate the gates into one of four
+// TMEM slots, and one of two epilogue warp groups (alternating tiles) applies the cell and writes c_t, the activated gates and its
+// 32 columns of the h_t image.  Activations as in lstm_tc.cu: the bias is folded into the exponent argument, one reciprocal
+// serves i, f and g, one serves o and tanh(c).
+struct FwdArgs {
+    const uint8_t* wf; const float* bias;
+    const uint8_t* xin; const uint8_t* hprev; uint8_t* hout; uint8_t* hmask; const uint32_t* keep;
+    const float* c_prev; float* c_out; uint8_t* gates; float* h_last;
+    int64_t N; int NT, XC, HC, UG, GC, H;
+};
+constexpr int FWD_NST = 6;
+constexpr uint32_t FWD_W_MAX = 8 * CHUNK;
+struct FwdSmem {
+    static constexpr uint32_t off_w = 0, off_ring = FWD_W_MAX, off_bias = off_ring + FWD_NST * CHUNK, off_bar = off_bias + 128 * 4;
+    // full[NST], empty[NST], acc_full[4], acc_free[4], w_ready
+    static constexpr uint32_t nbar = 2 * FWD_NST + 9, off_tmem = off_bar + nbar * 8, total = off_tmem + 16;
+};
+
+__global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
+    using S = FwdSmem;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    uint64_t* empty = full + FWD_NST;
+    uint64_t* acc_full = empty + FWD_NST;
+    uint64_t* acc_free = acc_full + 4;
+    uint64_t* w_ready = acc_free + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+    float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ug = (int)(blockIdx.x % a.UG), first = (int)(blockIdx.x / a.UG), stride = (int)(gridDim.x / a.UG);
+    const int KC = a.XC + a.HC;
+    const int nk = a.hprev ? KC : a.XC;                 // t = 0: h_{-1} = 0, the recurrent K-chunks are skipped
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < FWD_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 4; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 4); }
+        mbar_init(w_ready, 1);
+        fence_barrier_init();
+    }
+    if (threadIdx.x < 128) bias_s[threadIdx.x] = a.bias[ug * 128 + threadIdx.x];
+    if (warp == 9) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 8) {
+        // ================================ epilogue: LSTM cell of 32 units of one row ==========================
+        const int grp = warp >> 2, lq = warp & 3, r = lq * 32 + lane;
+        const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 16u;
+        const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16);
+        int i = 0;
+        for (int m = first; m < a.NT; m += stride, ++i) {
+            if ((i & 1) != grp) continue;
+            const int slot = i & 3;
+            const int64_t row = (int64_t)m * TM + r;
+            const bool live = row < a.N;
+            mbar_wait(&acc_full[slot], (uint32_t)((i >> 2) & 1));
+            tc_fence_after();
+            uint8_t* gbase = a.gates + ((size_t)m * a.GC + ug * 2) * CHUNK + row_off;
+            uint8_t* hdst = a.hout + ((size_t)m * a.HC + (ug >> 1)) * CHUNK + row_off + (uint32_t)((ug & 1) * 4) * 128u;
+            uint8_t* mdst = a.hmask ? a.hmask + ((size_t)m * a.HC + (ug >> 1)) * CHUNK + row_off + (uint32_t)((ug & 1) * 4) * 128u : nullptr;
+            uint32_t keep = 0u;
+            if (mdst != nullptr && live) keep = a.keep[row * a.UG + ug];
+#pragma unroll 1
+            for (int uc = 0; uc < 4; ++uc) {
+                float ai[8], af[8], ag[8], ao[8], cp[8];
+                const uint32_t col = tl + (uint32_t)(slot * 128 + uc * 8);
+                tmem_ld8(col + 0 * 32, ai);
+                tmem_ld8(col + 1 * 32, af);
+                tmem_ld8(col + 2 * 32, ag);
+                tmem_ld8(col + 3 * 32, ao);
+                if (a.c_prev != nullptr && live) ld8(a.c_prev + row * a.H + ug * 32 + uc * 8, cp);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cp[j] = 0.f;
+                }
+                tmem_ld_wait();
+                float cv[8], hv[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int u = uc * 8 + j;
+                    const float Ei = ex2a(fminf(fmaf(ai[j], -LOG2E, bias_s[0 * 32 + u]), EXP_CLAMP));
+                    const float Ef = ex2a(fminf(fmaf(af[j], -LOG2E, bias_s[1 * 32 + u]), EXP_CLAMP));
+                    const float Eg = ex2a(fminf(fmaf(ag[j], 2.f * LOG2E, bias_s[2 * 32 + u]), EXP_CLAMP));
+                    const float Eo = ex2a(fminf(fmaf(ao[j], -LOG2E, bias_s[3 * 32 + u]), EXP_CLAMP));
+                    const float Di = 1.f + Ei, Df = 1.f + Ef, Dg = 1.f + Eg, Do = 1.f + Eo;
+                    const float r1 = rcpa(Di * Df * Dg);
+                    const float gi = r1 * Df * Dg, gf = r1 * Di * Dg, gg = (Eg - 1.f) * (r1 * Di * Df);
+                    const float c = fmaf(gf, cp[j], gi * gg);
+                    const float Ec = ex2a(fminf(2.f * LOG2E * c, EXP_CLAMP));
+                    const float r2 = rcpa(Do * (Ec + 1.f));
+                    ai[j] = gi; af[j] = gf; ag[j] = gg; ao[j] = r2 * (Ec + 1.f);
+                    cv[j] = c;
+                    hv[j] = (Ec - 1.f) * r2;
+                }
+                // activated gates: chunk ug * 2 + gate / 2, 16-byte slot (gate % 2) * 4 + uc of this row
+                *reinterpret_cast<uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u) = pack_bf8(ai);
+                *reinterpret_cast<uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u) = pack_bf8(af);
+                *reinterpret_cast<uint4*>(gbase + CHUNK + (uint32_t)(0 * 4 + uc) * 128u) = pack_bf8(ag);
+                *reinterpret_cast<uint4*>(gbase + CHUNK + (uint32_t)(1 * 4 + uc) * 128u) = pack_bf8(ao);
+                const uint4 h8 = pack_bf8(hv);
+                *reinterpret_cast<uint4*>(hdst + (uint32_t)uc * 128u) = h8;
+                if (mdst != nullptr) *reinterpret_cast<uint4*>(mdst + (uint32_t)uc * 128u) = and_mask8(h8, (keep >> (uc * 8)) & 0xFFu);
+                if (live) {
+                    st8(a.c_out + row * a.H + ug * 32 + uc * 8, cv);
+                    if (a.h_last != nullptr) st8(a.h_last + row * a.H + ug * 32 + uc * 8, hv);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_free[slot]);
+        }
+    } else if (warp == 8) {
+        // ================================ loader ================================================================
+        if (lane == 0) {
+            mbar_arrive_expect_tx(w_ready, (uint32_t)KC * CHUNK);
+            for (int kc = 0; kc < KC; ++kc) bulk_copy_g2s(smem + S::off_w + kc * CHUNK, a.wf + ((size_t)ug * KC + kc) * CHUNK, CHUNK, w_ready);
+            uint32_t q = 0;
+            for (int m = first; m < a.NT; m += stride) {
+                for (int kc = 0; kc < nk; ++kc, ++q) {
+                    const uint32_t st = q % FWD_NST;
+                    if (q >= FWD_NST) mbar_wait(&empty[st], ((q / FWD_NST) - 1) & 1);
+                    const uint8_t* src = kc < a.XC ? a.xin + ((size_t)m * a.XC + kc) * CHUNK : a.hprev + ((size_t)m * a.HC + (kc - a.XC)) * CHUNK;
+                    mbar_arrive_expect_tx(&full[st], CHUNK);
+                    bulk_copy_g2s(smem + S::off_ring + st * CHUNK, src, CHUNK, &full[st]);
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ================================ MMA issuer ============================================================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(TM, 128);
+            const uint32_t s_base = smem_u32(smem);
+            mbar_wait(w_ready, 0u);
+            uint32_t q = 0;
+            int i = 0;
+            for (int m = first; m < a.NT; m += stride, ++i) {
+                const int slot = i & 3;
+                if (i >= 4) mbar_wait(&acc_free[slot], (uint32_t)(((i >> 2) - 1) & 1));
+                tc_fence_after();
+                const uint32_t d = tmem_base + (uint32_t)(slot * 128);
+                for (int kc = 0; kc < nk; ++kc, ++q) {
+                    const uint32_t st = q % FWD_NST;
+                    mbar_wait(&full[st], (q / FWD_NST) & 1);
+                    tc_fence_after();
+                    const uint32_t aa = s_base + S::off_ring + st * CHUNK, bb = s_base + S::off_w + (uint32_t)kc * CHUNK;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks)
+                        umma_bf16(d, make_desc(aa + ks * 256, LBO_BYTES, RG_BYTES), make_desc(bb + ks * 256, LBO_BYTES, RG_BYTES), idesc,
+                                  (kc > 0 || ks > 0) ? 1u : 0u);
+                    umma_commit(&empty[st]);
+                }
+                umma_commit(&acc_full[slot]);
+            }
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(tmem_base, 512);
+}
+
+
+// ------------------------------------------------------------------------------------------------ backward cell
+// One block = the 128 rows of (row tile m, unit group ug), one thread = 32 hidden units of one row.  Reads the activated gates
+// (in place), c_{t-1}, the incoming dh (recurrent + from the layer above + from the heads) and dc; writes dG (pre-activation
+// gradients, bf16, rows >= N zero), dc_{t-1}, and adds the tile's column sums of dG (the bias gradient) to its own slot of bsum.
+struct CellArgs {
+    uint8_t* G; const float* c_prev; const float* dh_rec; const float* d_out; const float* dhT; float* dc; float* bsum;
+    int first; int64_t N; int UG, GC, H;
+};
+
+__global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
+    __shared__ float red[4][4][32];
+    const int m = (int)(blockIdx.x / a.UG), ug = (int)(blockIdx.x % a.UG);
+    const int r = threadIdx.x, warp = r >> 5, lane = r & 31;
+    const int64_t row = (int64_t)m * TM + r;
+    const bool live = row < a.N;
+    uint8_t* gbase = a.G + ((size_t)m * a.GC + ug * 2) * CHUNK + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 16u;
+#pragma unroll 1
+    for (int uc = 0; uc < 4; ++uc) {
+        const int64_t e = row * a.H + ug * 32 + uc * 8;
+        float gi[8], gf[8], gg[8], go[8], cp[8], dh[8], dc[8], v[32];
+        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u), gi);
+        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u), gf);
+        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + CHUNK + (uint32_t)(0 * 4 + uc) * 128u), gg);
+        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + CHUNK + (uint32_t)(1 * 4 + uc) * 128u), go);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { cp[j] = 0.f; dh[j] = 0.f; dc[j] = 0.f; }
+        if (live) {
+            float t8[8];
+            if (a.c_prev) ld8(a.c_prev + e, cp);
+            if (a.dh_rec) ld8(a.dh_rec + e, dh);
+            if (a.d_out) {
+                ld8(a.d_out + e, t8);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) dh[j] += t8[j];
+            }
+            if (a.dhT) {
+                ld8(a.dhT + e, t8);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) dh[j] += t8[j];
+            }
+            if (!a.first) ld8(a.dc + e, dc);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float c = fmaf(gf[j], cp[j], gi[j] * gg[j]);
+            const float Ec = ex2a(fminf(2.f * LOG2E * c, EXP_CLAMP));
+            const float tc = 1.f - 2.f * rcpa(Ec + 1.f);
+            const float dct = fmaf(dh[j] * go[j], 1.f - tc * tc, dc[j]);
+            const float d_o = dh[j] * tc;
+            v[0 * 8 + j] = live ? dct * gg[j] * gi[j] * (1.f - gi[j]) : 0.f;
+            v[1 * 8 + j] = live ? dct * cp[j] * gf[j] * (1.f - gf[j]) : 0.f;
+            v[2 * 8 + j] = live ? dct * gi[j] * (1.f - gg[j] * gg[j]) : 0.f;
+            v[3 * 8 + j] = live ? d_o * go[j] * (1.f - go[j]) : 0.f;
+            dc[j] = dct * gf[j];
+        }
+        if (live) st8(a.dc + e, dc);
+        {
+            float t8[8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) t8[j] = v[k * 8 + j];
+                *reinterpret_cast<uint4*>(gbase + (uint32_t)(k >> 1) * CHUNK + (uint32_t)((k & 1) * 4 + uc) * 128u) = pack_bf8(t8);
+            }
+        }
+        // bias gradient: the warp's 32 rows of the 32 values, lane i ends up with the sum of value i
+#pragma unroll
+        for (int S = 16; S >= 1; S >>= 1) {
+            const bool up = (lane & S) != 0;
+#pragma unroll
+            for (int k = 0; k < S; ++k) {
+                const float lo = v[k], hi = v[k + S];
+                v[k] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, S);
+            }
+        }
+        red[warp][uc][lane] = v[0];
+    }
+    __syncthreads();
+    {
+        const int uc = r >> 5, idx = r & 31, gate = idx >> 3, j = idx & 7;
+        const float sum = (red[0][uc][idx] + red[1][uc][idx]) + (red[2][uc][idx] + red[3][uc][idx]);
+        a.bsum[(size_t)blockIdx.x * 128 + gate * 32 + uc * 8 + j] += sum;
+    }
+}
+
+// gb_ih = gb_hh = column sums over the row tiles (fixed order)
+__global__ void __launch_bounds__(256)
+w2_bsum_reduce_kernel(const float* __restrict__ bsum, int NT, int UG, int H, float* __restrict__ gb_ih, float* __restrict__ gb_hh) {
+    const int gp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gp >= 4 * H) return;
+    const int ug = gp >> 7, gate = (gp >> 5) & 3, u = ug * 32 + (gp & 31);
+    float s = 0.f;
+    for (int m = 0; m < NT; ++m) s += bsum[((size_t)m * UG + ug) * 128 + (gp & 127)];
+    gb_ih[gate * H + u] = s;
+    gb_hh[gate * H + u] = s;
+}
+
+// ------------------------------------------------------------------------------------------------ data gradient
+// out[p] = dG_t . Wd[p]  (p = 0: dh_{t-1} = dG . W_hh, p = 1: dx_t = dG . W_ih, masked with the keep bits of this layer's input;
+// the 1/(1-p) is in the packed W_ih).  A task = two row tiles x one part: per K-chunk of 64 gate columns two A chunks and one
+// [64 x H] B image arrive by bulk copy, 8 MMAs (M 128, N = H, B read MN-major) feed two TMEM accumulators; 3 stages of 64 KB.
+struct DgradArgs {
+    const uint8_t* dG; const uint8_t* wd[2]; float* out[2]; const uint32_t* keep;
+    int np; int part[2];
+    int64_t N; int NT, GC, H, UG;
+};
+constexpr int DG_NST = 3;
+constexpr uint32_t DG_STAGE = 4 * CHUNK;
+struct DgSmem {
+    static constexpr uint32_t off_bar = DG_NST * DG_STAGE;          // full[NST], empty[NST], acc_full, acc_free
+    static constexpr uint32_t off_tmem = off_bar + (2 * DG_NST + 2) * 8, total = off_tmem + 16;
+};
+
+__global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
+    using S = DgSmem;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    uint64_t* empty = full + DG_NST;
+    uint64_t* acc_full = empty + DG_NST;
+    uint64_t* acc_free = acc_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ntask = ((a.NT + 1) / 2) * a.np;
+    const uint32_t b_bytes = (uint32_t)(64 * a.H * 2), rgs = (uint32_t)(a.H / 8) * 128u;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < DG_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        mbar_init(acc_full, 1);
+        mbar_init(acc_free, 8);
+        fence_barrier_init();
+    }
+    if (warp == 9) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 8) {
+        const int j = warp >> 2, lq = warp & 3, r = lq * 32 + lane;
+        const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)(j * 256);
+        int i = 0;
+        for (int task = blockIdx.x; task < ntask; task += gridDim.x, ++i) {
+            const int p = a.part[task % a.np], m = 2 * (task / a.np) + j;
+            const int64_t row = (int64_t)m * TM + r;
+            mbar_wait(acc_full, (uint32_t)(i & 1));
+            tc_fence_after();
+            if (m < a.NT) {
+                const bool live = row < a.N;
+                float* dst = a.out[p] + row * a.H;
+                const bool masked = p == 1 && a.keep != nullptr;
+                for (int c0 = 0; c0 < a.H; c0 += 32) {
+                    float v[4][8];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) tmem_ld8(tl + (uint32_t)(c0 + k * 8), v[k]);
+                    tmem_ld_wait();
+                    if (live) {
+                        uint32_t kw = 0xFFFFFFFFu;
+                        if (masked) kw = a.keep[row * a.UG + (c0 >> 5)];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) if (!((kw >> (k * 8 + q)) & 1u)) v[k][q] = 0.f;
+                            st8(dst + c0 + k * 8, v[k]);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_free);
+        }
+    } else if (warp == 8) {
+        if (lane == 0) {
+            uint32_t q = 0;
+            for (int task = blockIdx.x; task < ntask; task += gridDim.x) {
+                const int p = a.part[task % a.np], m0 = 2 * (task / a.np);
+                const bool two = m0 + 1 < a.NT;
+                for (int kc = 0; kc < a.GC; ++kc, ++q) {
+                    const uint32_t st = q % DG_NST;
+                    if (q >= DG_NST) mbar_wait(&empty[st], ((q / DG_NST) - 1) & 1);
+                    uint8_t* sa = smem + st * DG_STAGE;
+                    mbar_arrive_expect_tx(&full[st], (two ? 2u : 1u) * CHUNK + b_bytes);
+                    bulk_copy_g2s(sa, a.dG + ((size_t)m0 * a.GC + kc) * CHUNK, CHUNK, &full[st]);
+                    if (two) bulk_copy_g2s(sa + CHUNK, a.dG + ((size_t)(m0 + 1) * a.GC + kc) * CHUNK, CHUNK, &full[st]);
+                    bulk_copy_g2s(sa + 2 * CHUNK, a.wd[p] + (size_t)kc * b_bytes, b_bytes, &full[st]);
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(TM, a.H, 0, 1);
+            const uint32_t s_base = smem_u32(smem);
+            uint32_t q = 0;
+            int i = 0;
+            for (int task = blockIdx.x; task < ntask; task += gridDim.x, ++i) {
+                const bool two = 2 * (task / a.np) + 1 < a.NT;
+                if (i > 0) mbar_wait(acc_free, (uint32_t)((i - 1) & 1));
+                tc_fence_after();
+                for (int kc = 0; kc < a.GC; ++kc, ++q) {
+                    const uint32_t st = q % DG_NST;
+                    mbar_wait(&full[st], (q / DG_NST) & 1);
+                    tc_fence_after();
+                    const uint32_t sa = s_base + st * DG_STAGE, sb = sa + 2 * CHUNK;
+#pragma unroll
+                    for (int t2 = 0; t2 < 2; ++t2) {
+                        if (t2 == 1 && !two) break;
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks)
+                            umma_bf16(tmem_base + (uint32_t)(t2 * 256), make_desc(sa + t2 * CHUNK + ks * 256, LBO_BYTES, RG_BYTES),
+                                      make_desc(sb + ks * 2 * rgs, rgs, LBO_BYTES), idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty[st]);
+                }
+                umma_commit(acc_full);
+            }
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------ weight gradient
+// part[z] = dG^T . [x | h_{t-1}] over the K-chunks (64 rows of one (t, row tile)) of split z; both operands are read MN-major, so
+// a stage is assembled from 1 KB row-group pieces of the chunks: A [64 rows x 128 gate columns] for two M tiles (two unit groups),
+// B [64 rows x N] with N = the x part (nt = 0) or the h part (nt = 1) of the K-concatenated weight matrix.
+struct WgradArgs {
+    const uint8_t* dG; const uint8_t* xsrc; const uint8_t* hsrc; const uint8_t* zero; float* part;
+    int T, NT, GC, XC, HC, H;
+    int splits; int64_t kps;
+};
+constexpr int WG_NST = 3;
+constexpr uint32_t WG_STAGE = 4 * CHUNK;
+struct WgSmem {
+    static constexpr uint32_t off_bar = WG_NST * WG_STAGE;          // full[NST], empty[NST], acc_full
+    static constexpr uint32_t off_tmem = off_bar + (2 * WG_NST + 1) * 8, total = off_tmem + 16;
+};
+
+__global__ void __launch_bounds__(W2_THREADS, 1) w2_wgrad_kernel(WgradArgs a) {
+    using S = WgSmem;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    uint64_t* empty = full + WG_NST;
+    uint64_t* acc_full = empty + WG_NST;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ntask = (a.H / 64) * 2;                          // (M pair, N tile)
+    const int z = (int)(blockIdx.x / ntask), task = (int)(blockIdx.x % ntask);
+    const int mp = task >> 1, nt = task & 1;
+    const int nch = nt == 0 ? a.XC : a.HC;
+    const int KW = (a.XC + a.HC) * 64, G4 = 4 * a.H;
+    const int64_t ktot = (int64_t)a.T * a.NT * 2;
+    const int64_t k_beg = (int64_t)z * a.kps, k_end = k_beg + a.kps < ktot ? k_beg + a.kps : ktot;
+    const uint32_t brg = (uint32_t)nch * 1024u;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < WG_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        mbar_init(acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 9) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 8) {
+        const int mt = warp >> 2, lq = warp & 3, r = lq * 32 + lane;
+        const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)(mt * 256);
+        const bool any = k_end > k_beg;
+        if (any) {
+            mbar_wait(acc_full, 0u);
+            tc_fence_after();
+        }
+        float* dst = a.part + ((size_t)z * G4 + (size_t)(2 * mp + mt) * 128 + r) * KW + (nt == 0 ? 0 : a.XC * 64);
+        for (int c0 = 0; c0 < nch * 64; c0 += 32) {
+            float v[4][8];
+            if (any) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) tmem_ld8(tl + (uint32_t)(c0 + k * 8), v[k]);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) v[k][q] = 0.f;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) st8(dst + c0 + k * 8, v[k]);
+        }
+    } else if (warp == 8) {
+        uint32_t q = 0;
+        for (int64_t kq = k_beg; kq < k_end; ++kq, ++q) {
+            const uint32_t st = q % WG_NST;
+            const int64_t tm = kq >> 1;                        // t * NT + m
+            const int half = (int)(kq & 1), t = (int)(tm / a.NT);
+            if (q >= WG_NST) mbar_wait(&empty[st], ((q / WG_NST) - 1) & 1);
+            uint8_t* sa = smem + st * WG_STAGE;
+            uint8_t* sb = sa + 2 * CHUNK;
+            if (lane == 0) mbar_arrive_expect_tx(&full[st], 2 * CHUNK + 8u * brg);
+            __syncwarp();
+            {   // A: (M tile, row group, chunk of the tile) = 32 pieces of 1 KB
+                const int mt = lane >> 4, rg = (lane >> 1) & 7, ci = lane & 1;
+                const uint8_t* src = a.dG + ((size_t)tm * a.GC + (size_t)(2 * mp + mt) * 2 + ci) * CHUNK + (size_t)(half * 8 + rg) * 1024;
+                bulk_copy_g2s(sa + mt * CHUNK + rg * 2048 + ci * 1024, src, 1024, &full[st]);
+            }
+            {   // B: (row group, chunk) = 8 * nch pieces
+                const int rg = lane >> 2, ci = lane & 3;
+                if (ci < nch) {
+                    const uint8_t* ch = nt == 0 ? a.xsrc + ((size_t)tm * a.XC + ci) * CHUNK
+                                                : (t > 0 ? a.hsrc + ((size_t)(tm - a.NT) * a.HC + ci) * CHUNK : a.zero);
+                    bulk_copy_g2s(sb + rg * brg + ci * 1024, ch + (size_t)(half * 8 + rg) * 1024, 1024, &full[st]);
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(TM, nch * 64, 1, 1);
+            const uint32_t s_base = smem_u32(smem);
+            uint32_t q = 0;
+            for (int64_t kq = k_beg; kq < k_end; ++kq, ++q) {
+                const uint32_t st = q % WG_NST;
+                mbar_wait(&full[st], (q / WG_NST) & 1);
+                tc_fence_after();
+                const uint32_t sa = s_base + st * WG_STAGE, sb = sa + 2 * CHUNK;
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks)
+                        umma_bf16(tmem_base + (uint32_t)(mt * 256), make_desc(sa + mt * CHUNK + ks * 2 * 2048, 2048, LBO_BYTES),
+                                  make_desc(sb + ks * 2 * brg, brg, LBO_BYTES), idesc, (q > 0 || ks > 0) ? 1u : 0u);
+                umma_commit(&empty[st]);
+            }
+            if (k_end > k_beg) umma_commit(acc_full);
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(tmem_base, 512);
+}
+
+// grads of W_ih [4H][in] and W_hh [4H][H] in torch order = sum over the splits (fixed order), x part scaled by 1/(1-p)
+__global__ void __launch_bounds__(256)
+w2_wgrad_reduce_kernel(const float* __restrict__ part, int splits, int H, int XC, int in, float x_scale, float* __restrict__ gw_ih,
+                       float* __restrict__ gw_hh) {
+    const int G4 = 4 * H, KW = (XC + H / 64) * 64;
+    const int64_t total = (int64_t)G4 * (in + H);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int g = (int)(i / (in + H)), k = (int)(i % (in + H));
+        const int gate = g / H, u = g % H;
+        const int gp = (u >> 5) * 128 + gate * 32 + (u & 31);
+        const int col = k < in ? k : XC * 64 + (k - in);
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += part[((size_t)z * G4 + gp) * KW + col];
+        if (k < in) gw_ih[(int64_t)g * in + k] = s * x_scale;
+        else gw_hh[(int64_t)g * H + (k - in)] = s;
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------ host side
+struct W2Ws {
+    uint8_t *himg, *xmask, *x0img, *gimg, *zero, *pack;
+    uint32_t* bits;
+    float *dx[2], *dh_rec, *dc, *part, *bsum;
+    size_t himg_bytes, gimg_bytes, bits_words, pack_stride, total;
+    int splits;
+};
+
+int wgrad_splits(const Geom& g) {
+    const int ntask = (g.H / 64) * 2;
+    int s = num_sms() / ntask;
+    const int64_t ktot = (int64_t)g.T * g.NT * 2;
+    if (s > ktot) s = (int)ktot;
+    return s < 1 ? 1 : s;
+}
+
+void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { uint8_t* q = p ? p + off : nullptr; off += al256(bytes); return q; };
+    const size_t lsz = (size_t)g.T * g.N * g.H * 4;
+    w->himg_bytes = (size_t)g.T * g.NT * g.HC * CHUNK;
+    w->gimg_bytes = (size_t)g.T * g.NT * g.GC * CHUNK;
+    w->bits_words = (size_t)g.T * g.N * g.UG;
+    w->pack_stride = pack_layout(g, g.L > 1 ? 1 : 0).total;
+    w->splits = wgrad_splits(g);
+    w->himg = take(w->himg_bytes * g.L);
+    w->xmask = take(w->himg_bytes * (g.L > 1 ? g.L - 1 : 0));
+    w->x0img = take((size_t)g.T * g.NT * CHUNK);
+    w->gimg = take(w->gimg_bytes * g.L);
+    w->bits = (uint32_t*)take(w->bits_words * 4 * (g.L > 1 ? g.L - 1 : 0));
+    w->dx[0] = (float*)take(g.L > 1 ? lsz : 0);
+    w->dx[1] = (float*)take(g.L > 2 ? lsz : 0);
+    w->dh_rec = (float*)take((size_t)g.N * g.H * 4);
+    w->dc = (float*)take((size_t)g.N * g.H * 4);
+    w->part = (float*)take((size_t)w->splits * 4 * g.H * (2 * g.H) * 4);
+    w->bsum = (float*)take((size_t)g.NT * g.UG * 128 * 4);
+    w->zero = take(CHUNK);
+    w->pack = take(w->pack_stride * g.L);
+    w->total = off;
+}
+
+unsigned ew_grid2(int64_t n) {
+    const int64_t b = (n + 255) / 256, cap = (int64_t)num_sms() * 16;
+    return (unsigned)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+struct LayerP { const float *w_ih, *w_hh, *b_ih, *b_hh; int in; };
+LayerP layer_p(const float* params, int F, int H, int l) {
+    int64_t off = 0;
+    for (int i = 0; i < l; ++i) off += 4LL * H * (i == 0 ? F : H) + 4LL * H * H + 8LL * H;
+    LayerP lp;
+    lp.in = l == 0 ? F : H;
+    lp.w_ih = params + off;
+    lp.w_hh = lp.w_ih + 4LL * H * lp.in;
+    lp.b_ih = lp.w_hh + 4LL * H * H;
+    lp.b_hh = lp.b_ih + 4LL * H;
+    return lp;
+}
+
+template <typename K>
+int opt_in_smem(K kernel, uint32_t bytes, const char* who) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return cuda_fail(e, who);
+    return B200_OK;
+}
+
+}  // namespace
+
+bool wide2_supported(int H, int F) { return (H == 128 || H == 256) && F >= 1 && F <= 63; }
+
+size_t wide2_workspace_bytes(int64_t N, int T, int F, int H, int L) {
+    const Geom g = make_geom(N, T, F, H, L);
+    W2Ws w;
+    w2_layout(g, nullptr, &w);
+    return w.total + 256;
+}
+
+int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h, float* stash_c, float p,
+              uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
+    const Geom g = make_geom(N, T, F, H, L);
+    W2Ws w;
+    w2_layout(g, (uint8_t*)workspace, &w);
+    B200_CHECK_ARG(workspace != nullptr && w.total <= ws_bytes, "lstm_fwd (wide, bf16): workspace too small (%zu bytes, need %zu)", ws_bytes, w.total);
+    const bool drop = training && p > 0.f && L > 1;
+    const int64_t NH = N * H, lsz = (int64_t)T * NH;
+    int rc = opt_in_smem(w2_fwd_kernel, FwdSmem::total, "w2_fwd_kernel smem");
+    if (rc) return rc;
+    B200_CUDA(cudaMemsetAsync(w.zero, 0, CHUNK, st));
+    { TimedLaunch _t("w2_x0_kernel", st); w2_x0_kernel<<<ew_grid2((int64_t)T * g.NT * TM * 8), 256, 0, st>>>(x, N, T, F, g.NT, w.x0img); }
+    B200_LAUNCH_CHECK("w2_x0_kernel");
+    for (int l = 0; l < L; ++l) {
+        const LayerP lp = layer_p(params, F, H, l);
+        const PackLayout pl = pack_layout(g, l);
+        uint8_t* pk = w.pack + (size_t)l * w.pack_stride;
+        const float in_scale = (l > 0 && drop) ? 1.0f / (1.0f - p) : 1.0f;
+        { TimedLaunch _t("w2_pack_kernel", st);
+          w2_pack_kernel<<<128, 256, 0, st>>>(lp.w_ih, lp.w_hh, lp.b_ih, lp.b_hh, lp.in, H, g.xc(l), in_scale, pk + pl.wf, pk + pl.wd_h,
+                                              l > 0 ? pk + pl.wd_x : nullptr, (float*)(pk + pl.bias)); }
+        B200_LAUNCH_CHECK("w2_pack_kernel");
+        if (drop && l > 0) {
+            { TimedLaunch _t("w2_bits_kernel", st); w2_bits_kernel<<<ew_grid2((int64_t)T * N * g.UG), 256, 0, st>>>(seed, l, N, T, g.UG, p, w.bits + (size_t)(l - 1) * w.bits_words); }
+            B200_LAUNCH_CHECK("w2_bits_kernel");
+        }
+    }
+    int lanes = num_sms() / g.UG;
+    if (lanes > g.NT) lanes = g.NT;
+    if (lanes < 1) lanes = 1;
+    for (int l = 0; l < L; ++l) {
+        const PackLayout pl = pack_layout(g, l);
+        const uint8_t* pk = w.pack + (size_t)l * w.pack_stride;
+        uint8_t* himg = w.himg + (size_t)l * w.himg_bytes;
+        const bool mask_out = drop && l < L - 1;
+        const uint8_t* xin = l == 0 ? w.x0img : (drop ? w.xmask + (size_t)(l - 1) * w.himg_bytes : w.himg + (size_t)(l - 1) * w.himg_bytes);
+        const size_t xstep = (size_t)g.NT * g.xc(l) * CHUNK, hstep = (size_t)g.NT * g.HC * CHUNK, gstep = (size_t)g.NT * g.GC * CHUNK;
+        for (int t = 0; t < T; ++t) {
+            FwdArgs a;
+            a.wf = pk + pl.wf; a.bias = (const float*)(pk + pl.bias);
+            a.xin = xin + (size_t)t * xstep;
+            a.hprev = t > 0 ? himg + (size_t)(t - 1) * hstep : nullptr;
+            a.hout = himg + (size_t)t * hstep;
+            a.hmask = mask_out ? w.xmask + (size_t)l * w.himg_bytes + (size_t)t * hstep : nullptr;
+            a.keep = mask_out ? w.bits + (size_t)l * w.bits_words + (size_t)t * N * g.UG : nullptr;
+            a.c_prev = t > 0 ? stash_c + (int64_t)l * lsz + (int64_t)(t - 1) * NH : nullptr;
+            a.c_out = stash_c + (int64_t)l * lsz + (int64_t)t * NH;
+            a.gates = w.gimg + (size_t)l * w.gimg_bytes + (size_t)t * gstep;
+            a.h_last = (l == L - 1 && t == T - 1) ? stash_h + (int64_t)l * lsz + (int64_t)t * NH : nullptr;
+            a.N = N; a.NT = g.NT; a.XC = g.xc(l); a.HC = g.HC; a.UG = g.UG; a.GC = g.GC; a.H = H;
+            { TimedLaunch _t("w2_fwd_kernel", st); w2_fwd_kernel<<<(unsigned)(lanes * g.UG), W2_THREADS, FwdSmem::total, st>>>(a); }
+            B200_LAUNCH_CHECK("w2_fwd_kernel");
+        }
+    }
+    return B200_OK;
+}
+
+int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T, const float* stash_h,
+                    const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed, int training, void* workspace,
+                    size_t ws_bytes, cudaStream_t st) {
+    (void)x; (void)stash_h; (void)seed;
+    const Geom g = make_geom(N, T, F, H, L);
+    W2Ws w;
+    w2_layout(g, (uint8_t*)workspace, &w);
+    B200_CHECK_ARG(workspace != nullptr && w.total <= ws_bytes, "lstm_bwd (wide, bf16): workspace too small (%zu bytes, need %zu)", ws_bytes, w.total);
+    const bool drop = training && p > 0.f && L > 1;
+    const int l = layer;
+    const int64_t NH = N * H, lsz = (int64_t)T * NH;
+    int rc = opt_in_smem(w2_dgrad_kernel, DgSmem::total, "w2_dgrad_kernel smem");
+    if (rc) return rc;
+    rc = opt_in_smem(w2_wgrad_kernel, WgSmem::total, "w2_wgrad_kernel smem");
+    if (rc) return rc;
+    const LayerP lp = layer_p(params, F, H, l);
+    const int64_t poff = lp.w_ih - params;
+    float* gw_ih = grads + poff;
+    float* gw_hh = gw_ih + 4LL * H * lp.in;
+    float* gb_ih = gw_hh + 4LL * H * H;
+    float* gb_hh = gb_ih + 4LL * H;
+    const PackLayout pl = pack_layout(g, l);
+    const uint8_t* pk = w.pack + (size_t)l * w.pack_stride;
+    uint8_t* gimg = w.gimg + (size_t)l * w.gimg_bytes;
+    const float* cs = stash_c + (int64_t)l * lsz;
+    const bool top = l == L - 1;
+    const float* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
+    float* d_in = w.dx[(L - 1 - l) & 1];
+    const size_t gstep = (size_t)g.NT * g.GC * CHUNK;
+    const float in_scale = (l > 0 && drop) ? 1.0f / (1.0f - p) : 1.0f;
+
+    B200_CUDA(cudaMemsetAsync(w.bsum, 0, (size_t)g.NT * g.UG * 128 * 4, st));
+    const int dg_tasks_max = ((g.NT + 1) / 2) * 2;
+    for (int t = T - 1; t >= 0; --t) {
+        CellArgs c;
+        c.G = gimg + (size_t)t * gstep;
+        c.c_prev = t > 0 ? cs + (int64_t)(t - 1) * NH : nullptr;
+        c.dh_rec = t < T - 1 ? w.dh_rec : nullptr;
+        c.d_out = d_out ? d_out + (int64_t)t * NH : nullptr;
+        c.dhT = (top && t == T - 1) ? dhT : nullptr;
+        c.dc = w.dc; c.bsum = w.bsum; c.first = t == T - 1 ? 1 : 0;
+        c.N = N; c.UG = g.UG; c.GC = g.GC; c.H = H;
+        { TimedLaunch _t("w2_cell_bwd_kernel", st); w2_cell_bwd_kernel<<<(unsigned)(g.NT * g.UG), 128, 0, st>>>(c); }
+        B200_LAUNCH_CHECK("w2_cell_bwd_kernel");
+        DgradArgs d;
+        d.dG = c.G; d.wd[0] = pk + pl.wd_h; d.wd[1] = l > 0 ? pk + pl.wd_x : nullptr;
+        d.out[0] = w.dh_rec; d.out[1] = l > 0 ? d_in + (int64_t)t * NH : nullptr;
+        d.keep = (drop && l > 0) ? w.bits + (size_t)(l - 1) * w.bits_words + (size_t)t * N * g.UG : nullptr;
+        d.np = 0;
+        if (t > 0) d.part[d.np++] = 0;
+        if (l > 0) d.part[d.np++] = 1;
+        if (d.np == 1) d.part[1] = d.part[0];
+        d.N = N; d.NT = g.NT; d.GC = g.GC; d.H = H; d.UG = g.UG;
+        if (d.np > 0) {
+            int grid = ((g.NT + 1) / 2) * d.np;
+            if (grid > num_sms()) grid = num_sms();
+            (void)dg_tasks_max;
+            { TimedLaunch _t("w2_dgrad_kernel", st); w2_dgrad_kernel<<<(unsigned)grid, W2_THREADS, DgSmem::total, st>>>(d); }
+            B200_LAUNCH_CHECK("w2_dgrad_kernel");
+        }
+    }
+    WgradArgs wa;
+    wa.dG = gimg;
+    wa.xsrc = l == 0 ? w.x0img : (drop ? w.xmask + (size_t)(l - 1) * w.himg_bytes : w.himg + (size_t)(l - 1) * w.himg_bytes);
+    wa.hsrc = w.himg + (size_t)l * w.himg_bytes;
+    wa.zero = w.zero; wa.part = w.part;
+    wa.T = T; wa.NT = g.NT; wa.GC = g.GC; wa.XC = g.xc(l); wa.HC = g.HC; wa.H = H;
+    wa.splits = w.splits;
+    const int64_t ktot = (int64_t)T * g.NT * 2;
+    wa.kps = (ktot + w.splits - 1) / w.splits;
+    { TimedLaunch _t("w2_wgrad_kernel", st); w2_wgrad_kernel<<<(unsigned)((H / 64) * 2 * w.splits), W2_THREADS, WgSmem::total, st>>>(wa); }
+    B200_LAUNCH_CHECK("w2_wgrad_kernel");
+    { TimedLaunch _t("w2_wgrad_reduce_kernel", st);
+      w2_wgrad_reduce_kernel<<<ew_grid2(4LL * H * (lp.in + H)), 256, 0, st>>>(w.part, w.splits, H, g.xc(l), lp.in, in_scale, gw_ih, gw_hh); }
+    B200_LAUNCH_CHECK("w2_wgrad_reduce_kernel");
+    { TimedLaunch _t("w2_bsum_reduce_kernel", st); w2_bsum_reduce_kernel<<<(unsigned)((4 * H + 255) / 256), 256, 0, st>>>(w.bsum, g.NT, g.UG, H, gb_ih, gb_hh); }
+    B200_LAUNCH_CHECK("w2_bsum_reduce_kernel");
+    return B200_OK;
+}
+
+int wide2_hidden_states(int layer, int F, int H, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st) {
+    const Geom g = make_geom(N, T, F, H, L);
+    W2Ws w;
+    w2_layout(g, (uint8_t*)workspace, &w);
+    B200_CHECK_ARG(workspace != nullptr && w.total <= ws_bytes, "lstm_hidden_states (wide, bf16): workspace too small");
+    { TimedLaunch _t("w2_unpack_kernel", st); w2_unpack_kernel<<<ew_grid2((int64_t)T * N * (H / 8)), 256, 0, st>>>(w.himg + (size_t)layer * w.himg_bytes, N, T, H, g.NT, out); }
+    B200_LAUNCH_CHECK("w2_unpack_kernel");
+    return B200_OK;
+}
+
+}  // namespace b200
