@@ -239,10 +239,10 @@ def lstm_roofline(kt, steps, seqs, H, L, tf_sus, src):
     F_seq = flops_per_sequence(3, H, L)
     mine = {k: v for k, v in kt.items() if not k.startswith("nccl")}
     dom = max(mine.items(), key=lambda kv: kv[1][1]) if mine else (None, (0, 0.0))
-    lstm_ms = sum(v[1] for k, v in mine.items() if k.startswith(("lstm_", "wide_")))
+    lstm_ms = sum(v[1] for k, v in mine.items() if k.startswith(("lstm_", "wide_", "w2_")))
     per_step = lstm_ms / steps if steps else 0.0
     achieved = seqs * F_seq / (per_step * 1e-3) / 1e12 if per_step else 0.0
-    return {"bound": "tensor", "kernel": "LSTM forward+backward kernels (" + ", ".join(sorted(k for k in mine if k.startswith(("lstm_", "wide_")))) + ")",
+    return {"bound": "tensor", "kernel": "LSTM forward+backward kernels (" + ", ".join(sorted(k for k in mine if k.startswith(("lstm_", "wide_", "w2_")))) + ")",
             "dominant_kernel": dom[0], "achieved": achieved, "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
             "peak_source": f"{src} bf16 sustained (MEASURED_PEAKS.json)", "algorithmic_flops_per_step": seqs * F_seq,
             "lstm_ms_per_step": per_step,

@@ -34,6 +34,9 @@
  *        The tcgen05 engines at hidden 64 (B200_MODE_TC_*) write ONLY hT into stash_h: they keep the hidden states of all
  *        steps inside `workspace` as bf16 hi/lo operand images that later kernels fetch with bulk copies (csrc/lstm_tc.cu);
  *        b200_lstm_hidden_states() returns any layer's states as fp32 for every engine.  stash_c is always fp32.
+ *        The wide engine in bf16 mode (hidden 128 / 256 with B200_MODE_TC_FAST, csrc/lstm_wide2.cu) also writes ONLY hT into
+ *        stash_h and does not touch stash_c: hidden states, activated gates (bf16 operand images) and the fp32 cell state
+ *        live in `workspace`.
  */
 #ifndef B200_LSTM_H
 #define B200_LSTM_H
@@ -85,7 +88,9 @@ B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
  *   "tc_fwd_eh"    bit 0 / bit 1: two epilogue threads per row in the forward kernel of layers > 0 / layer 0 (default 1)
  *   "tc_wgrad"     products of the weight gradient in layers > 0, precise mode: 3 (default), 2, or 0 = two from 2^22 row-steps on
  *   "tc_dgrad"     products of the data gradient, precise mode: 3 (default) or 2
- *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM (default 0) */
+ *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM, fp32-storage path (default 0)
+ *   "wide_images"  0 = run bf16 mode of the wide engine on the fp32-storage path of csrc/lstm_wide.cu instead of the
+ *                  operand-image engine of csrc/lstm_wide2.cu (default 1); changes b200_lstm_workspace_bytes */
 B200_API int b200_set_option(const char* name, int value);
 
 /* number of fp32 parameters of the model (src/model.py:88-97): 51,074 for F=3,H=64,L=2 */

@@ -28,7 +28,7 @@ int cuda_fail(cudaError_t e, const char* what) {
 // safe; while it is off, timing_begin/timing_end are one relaxed flag test.
 struct TimingSlot {
     const char* name;
-    cudaEvent_t ev[2 * 4096];
+    cudaEvent_t ev[2 * 16384];
     int used;       // events recorded (pairs * 2)
     int allocated;  // events created
 };
@@ -49,7 +49,7 @@ void timing_begin(const char* name, cudaStream_t st) {
         s = &g_slots[g_nslots++];
         s->name = name; s->used = 0; s->allocated = 0;
     }
-    if (s->used + 2 > 2 * 4096) return;
+    if (s->used + 2 > 2 * 16384) return;
     while (s->allocated < s->used + 2) cudaEventCreate(&s->ev[s->allocated++]);
     cudaEventRecord(s->ev[s->used], st);
     g_open = s;

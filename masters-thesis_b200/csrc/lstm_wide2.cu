@@ -13,6 +13,8 @@
 //   Gimg[l]  [T][NT][GC] chunks   activated gates (forward) -> pre-activation gradients dG (backward, in place); gate columns
 //                                 are permuted: g' = (u / 32) * 128 + gate * 32 + u % 32, so that the four gates of 32 hidden
 //                                 units are one 128-column block (one N tile of the forward GEMM, one M tile of the weight gradient)
+//   c, dc, dh, dx                  fp32 in the "row-slot" layout [tile][u / 8][128 rows][8]: the thread that owns a row (TMEM lane) moves
+//                                 32 bytes and a warp 1 KB of contiguous memory (row-major [N][H] costs 32 cache lines per warp access)
 //   Wf[l]    [UG][KC] chunks      rows g' of [W_ih | W_hh], KC = (1 or HC) + HC K-chunks
 //   Wd[l]    per part (h, x): [GC][64 g' rows x (64 * HC) columns] MN-major images for dG . W
 //
@@ -43,6 +45,9 @@ __host__ __device__ inline size_t al256(size_t b) { return (b + 255) & ~(size_t)
 __host__ __device__ inline uint32_t chunk_off(int r, int c) {
     return (uint32_t)(r >> 3) * 1024u + (uint32_t)(c >> 3) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(c & 7) * 2u;
 }
+
+// fp32 row-slot layout: float index of (row, unit) and of the 8-float slot (tile, octet, r)
+__host__ __device__ inline size_t slot_off(int64_t tile, int octet, int r, int H) { return (((size_t)tile * (H >> 3) + octet) * 128 + r) * 8; }
 
 struct Geom {
     int F, H, L, T;
@@ -260,6 +265,15 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             const int slot = i & 3;
             const int64_t row = (int64_t)m * TM + r;
             const bool live = row < a.N;
+            float cpv[4][8];                      // c_{t-1} of the row's 32 units, fetched while the MMAs of the tile run
+#pragma unroll
+            for (int uc = 0; uc < 4; ++uc) {
+                if (a.c_prev != nullptr) ld8(a.c_prev + slot_off(m, ug * 4 + uc, r, a.H), cpv[uc]);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cpv[uc][j] = 0.f;
+                }
+            }
             mbar_wait(&acc_full[slot], (uint32_t)((i >> 2) & 1));
             tc_fence_after();
             uint8_t* gbase = a.gates + ((size_t)m * a.GC + ug * 2) * CHUNK + row_off;
@@ -267,19 +281,15 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             uint8_t* mdst = a.hmask ? a.hmask + ((size_t)m * a.HC + (ug >> 1)) * CHUNK + row_off + (uint32_t)((ug & 1) * 4) * 128u : nullptr;
             uint32_t keep = 0u;
             if (mdst != nullptr && live) keep = a.keep[row * a.UG + ug];
-#pragma unroll 1
+#pragma unroll
             for (int uc = 0; uc < 4; ++uc) {
-                float ai[8], af[8], ag[8], ao[8], cp[8];
+                float ai[8], af[8], ag[8], ao[8];
+                const float (&cp)[8] = cpv[uc];
                 const uint32_t col = tl + (uint32_t)(slot * 128 + uc * 8);
                 tmem_ld8(col + 0 * 32, ai);
                 tmem_ld8(col + 1 * 32, af);
                 tmem_ld8(col + 2 * 32, ag);
                 tmem_ld8(col + 3 * 32, ao);
-                if (a.c_prev != nullptr && live) ld8(a.c_prev + row * a.H + ug * 32 + uc * 8, cp);
-                else {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) cp[j] = 0.f;
-                }
                 tmem_ld_wait();
                 float cv[8], hv[8];
 #pragma unroll
@@ -307,10 +317,8 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                 const uint4 h8 = pack_bf8(hv);
                 *reinterpret_cast<uint4*>(hdst + (uint32_t)uc * 128u) = h8;
                 if (mdst != nullptr) *reinterpret_cast<uint4*>(mdst + (uint32_t)uc * 128u) = and_mask8(h8, (keep >> (uc * 8)) & 0xFFu);
-                if (live) {
-                    st8(a.c_out + row * a.H + ug * 32 + uc * 8, cv);
-                    if (a.h_last != nullptr) st8(a.h_last + row * a.H + ug * 32 + uc * 8, hv);
-                }
+                st8(a.c_out + slot_off(m, ug * 4 + uc, r, a.H), cv);
+                if (live && a.h_last != nullptr) st8(a.h_last + row * a.H + ug * 32 + uc * 8, hv);
             }
             tc_fence_before();
             __syncwarp();
@@ -380,13 +388,20 @@ struct CellArgs {
 __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
     __shared__ float red[4][4][32];
     const int m = (int)(blockIdx.x / a.UG), ug = (int)(blockIdx.x % a.UG);
-    const int r = threadIdx.x, warp = r >> 5, lane = r & 31;
-    const int64_t row = (int64_t)m * TM + r;
-    const bool live = row < a.N;
-    uint8_t* gbase = a.G + ((size_t)m * a.GC + ug * 2) * CHUNK + (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 16u;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // a warp step = one 8-row group x the four unit octets of the group: lane = (row in group, octet), so that the fp32 slots of a
+    // lane quartet and the 16-byte image slots of the warp are contiguous memory
+    const int rr = lane >> 2, uc = lane & 3;
+    float acc[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) acc[k] = 0.f;
 #pragma unroll 1
-    for (int uc = 0; uc < 4; ++uc) {
-        const int64_t e = row * a.H + ug * 32 + uc * 8;
+    for (int it = 0; it < 4; ++it) {
+        const int rg = warp * 4 + it, r = rg * 8 + rr;
+        const int64_t row = (int64_t)m * TM + r;
+        const bool live = row < a.N;
+        uint8_t* gbase = a.G + ((size_t)m * a.GC + ug * 2) * CHUNK + (uint32_t)rg * 1024u + (uint32_t)rr * 16u;
+        const size_t e = slot_off(m, ug * 4 + uc, r, a.H);
         float gi[8], gf[8], gg[8], go[8], cp[8], dh[8], dc[8], v[32];
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u), gi);
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u), gf);
@@ -394,7 +409,7 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + CHUNK + (uint32_t)(1 * 4 + uc) * 128u), go);
 #pragma unroll
         for (int j = 0; j < 8; ++j) { cp[j] = 0.f; dh[j] = 0.f; dc[j] = 0.f; }
-        if (live) {
+        {
             float t8[8];
             if (a.c_prev) ld8(a.c_prev + e, cp);
             if (a.dh_rec) ld8(a.dh_rec + e, dh);
@@ -403,8 +418,8 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) dh[j] += t8[j];
             }
-            if (a.dhT) {
-                ld8(a.dhT + e, t8);
+            if (a.dhT && live) {
+                ld8(a.dhT + row * a.H + ug * 32 + uc * 8, t8);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) dh[j] += t8[j];
             }
@@ -415,15 +430,15 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
             const float c = fmaf(gf[j], cp[j], gi[j] * gg[j]);
             const float Ec = ex2a(fminf(2.f * LOG2E * c, EXP_CLAMP));
             const float tc = 1.f - 2.f * rcpa(Ec + 1.f);
-            const float dct = fmaf(dh[j] * go[j], 1.f - tc * tc, dc[j]);
-            const float d_o = dh[j] * tc;
-            v[0 * 8 + j] = live ? dct * gg[j] * gi[j] * (1.f - gi[j]) : 0.f;
-            v[1 * 8 + j] = live ? dct * cp[j] * gf[j] * (1.f - gf[j]) : 0.f;
-            v[2 * 8 + j] = live ? dct * gi[j] * (1.f - gg[j] * gg[j]) : 0.f;
-            v[3 * 8 + j] = live ? d_o * go[j] * (1.f - go[j]) : 0.f;
+            const float dct = live ? fmaf(dh[j] * go[j], 1.f - tc * tc, dc[j]) : 0.f;
+            const float d_o = live ? dh[j] * tc : 0.f;
+            v[0 * 8 + j] = dct * gg[j] * gi[j] * (1.f - gi[j]);
+            v[1 * 8 + j] = dct * cp[j] * gf[j] * (1.f - gf[j]);
+            v[2 * 8 + j] = dct * gi[j] * (1.f - gg[j] * gg[j]);
+            v[3 * 8 + j] = d_o * go[j] * (1.f - go[j]);
             dc[j] = dct * gf[j];
         }
-        if (live) st8(a.dc + e, dc);
+        st8(a.dc + e, dc);
         {
             float t8[8];
 #pragma unroll
@@ -433,23 +448,27 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
                 *reinterpret_cast<uint4*>(gbase + (uint32_t)(k >> 1) * CHUNK + (uint32_t)((k & 1) * 4 + uc) * 128u) = pack_bf8(t8);
             }
         }
-        // bias gradient: the warp's 32 rows of the 32 values, lane i ends up with the sum of value i
 #pragma unroll
-        for (int S = 16; S >= 1; S >>= 1) {
-            const bool up = (lane & S) != 0;
-#pragma unroll
-            for (int k = 0; k < S; ++k) {
-                const float lo = v[k], hi = v[k + S];
-                v[k] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, S);
-            }
-        }
-        red[warp][uc][lane] = v[0];
+        for (int k = 0; k < 32; ++k) acc[k] += v[k];
     }
+    // bias gradient: sum the 32 values (4 gates x 8 units of the lane's octet) over the 8 rows of the warp step; lane (rr, uc) ends up
+    // with values rr * 4 .. rr * 4 + 3
+#pragma unroll
+    for (int S = 16; S >= 4; S >>= 1) {
+        const bool up = (lane & S) != 0;
+#pragma unroll
+        for (int k = 0; k < S; ++k) {
+            const float lo = acc[k], hi = acc[k + S];
+            acc[k] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, S);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) red[warp][uc][rr * 4 + k] = acc[k];
     __syncthreads();
     {
-        const int uc = r >> 5, idx = r & 31, gate = idx >> 3, j = idx & 7;
-        const float sum = (red[0][uc][idx] + red[1][uc][idx]) + (red[2][uc][idx] + red[3][uc][idx]);
-        a.bsum[(size_t)blockIdx.x * 128 + gate * 32 + uc * 8 + j] += sum;
+        const int o = threadIdx.x >> 5, idx = threadIdx.x & 31, gate = idx >> 3, j = idx & 7;
+        const float sum = (red[0][o][idx] + red[1][o][idx]) + (red[2][o][idx] + red[3][o][idx]);
+        a.bsum[(size_t)blockIdx.x * 128 + gate * 32 + o * 8 + j] += sum;
     }
 }
 
@@ -515,23 +534,19 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
             mbar_wait(acc_full, (uint32_t)(i & 1));
             tc_fence_after();
             if (m < a.NT) {
-                const bool live = row < a.N;
-                float* dst = a.out[p] + row * a.H;
-                const bool masked = p == 1 && a.keep != nullptr;
+                const bool masked = p == 1 && a.keep != nullptr && row < a.N;
                 for (int c0 = 0; c0 < a.H; c0 += 32) {
                     float v[4][8];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) tmem_ld8(tl + (uint32_t)(c0 + k * 8), v[k]);
+                    uint32_t kw = 0xFFFFFFFFu;
+                    if (masked) kw = a.keep[row * a.UG + (c0 >> 5)];
                     tmem_ld_wait();
-                    if (live) {
-                        uint32_t kw = 0xFFFFFFFFu;
-                        if (masked) kw = a.keep[row * a.UG + (c0 >> 5)];
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
+                    for (int k = 0; k < 4; ++k) {
 #pragma unroll
-                            for (int q = 0; q < 8; ++q) if (!((kw >> (k * 8 + q)) & 1u)) v[k][q] = 0.f;
-                            st8(dst + c0 + k * 8, v[k]);
-                        }
+                        for (int q = 0; q < 8; ++q) if (!((kw >> (k * 8 + q)) & 1u)) v[k][q] = 0.f;
+                        st8(a.out[p] + slot_off(m, (c0 >> 3) + k, r, a.H), v[k]);
                     }
                 }
             }
@@ -736,8 +751,8 @@ w2_wgrad_reduce_kernel(const float* __restrict__ part, int splits, int H, int XC
 struct W2Ws {
     uint8_t *himg, *xmask, *x0img, *gimg, *zero, *pack;
     uint32_t* bits;
-    float *dx[2], *dh_rec, *dc, *part, *bsum;
-    size_t himg_bytes, gimg_bytes, bits_words, pack_stride, total;
+    float *cst, *dx[2], *dh_rec, *dc, *part, *bsum;
+    size_t himg_bytes, gimg_bytes, bits_words, pack_stride, slot_floats, total;
     int splits;
 };
 
@@ -752,7 +767,8 @@ int wgrad_splits(const Geom& g) {
 void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
     size_t off = 0;
     auto take = [&](size_t bytes) { uint8_t* q = p ? p + off : nullptr; off += al256(bytes); return q; };
-    const size_t lsz = (size_t)g.T * g.N * g.H * 4;
+    w->slot_floats = (size_t)g.NT * TM * g.H;                       // one [rows x H] fp32 array in the row-slot layout
+    const size_t lsz = (size_t)g.T * w->slot_floats * 4;
     w->himg_bytes = (size_t)g.T * g.NT * g.HC * CHUNK;
     w->gimg_bytes = (size_t)g.T * g.NT * g.GC * CHUNK;
     w->bits_words = (size_t)g.T * g.N * g.UG;
@@ -763,10 +779,11 @@ void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
     w->x0img = take((size_t)g.T * g.NT * CHUNK);
     w->gimg = take(w->gimg_bytes * g.L);
     w->bits = (uint32_t*)take(w->bits_words * 4 * (g.L > 1 ? g.L - 1 : 0));
+    w->cst = (float*)take(lsz * g.L);
     w->dx[0] = (float*)take(g.L > 1 ? lsz : 0);
     w->dx[1] = (float*)take(g.L > 2 ? lsz : 0);
-    w->dh_rec = (float*)take((size_t)g.N * g.H * 4);
-    w->dc = (float*)take((size_t)g.N * g.H * 4);
+    w->dh_rec = (float*)take(w->slot_floats * 4);
+    w->dc = (float*)take(w->slot_floats * 4);
     w->part = (float*)take((size_t)w->splits * 4 * g.H * (2 * g.H) * 4);
     w->bsum = (float*)take((size_t)g.NT * g.UG * 128 * 4);
     w->zero = take(CHUNK);
@@ -812,6 +829,7 @@ size_t wide2_workspace_bytes(int64_t N, int T, int F, int H, int L) {
 
 int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h, float* stash_c, float p,
               uint64_t seed, int training, void* workspace, size_t ws_bytes, cudaStream_t st) {
+    (void)stash_c;                   // the cell state lives in the workspace (row-slot layout); stash_h receives h_T of the top layer only
     const Geom g = make_geom(N, T, F, H, L);
     W2Ws w;
     w2_layout(g, (uint8_t*)workspace, &w);
@@ -855,8 +873,8 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
             a.hout = himg + (size_t)t * hstep;
             a.hmask = mask_out ? w.xmask + (size_t)l * w.himg_bytes + (size_t)t * hstep : nullptr;
             a.keep = mask_out ? w.bits + (size_t)l * w.bits_words + (size_t)t * N * g.UG : nullptr;
-            a.c_prev = t > 0 ? stash_c + (int64_t)l * lsz + (int64_t)(t - 1) * NH : nullptr;
-            a.c_out = stash_c + (int64_t)l * lsz + (int64_t)t * NH;
+            a.c_prev = t > 0 ? w.cst + ((size_t)l * T + (t - 1)) * w.slot_floats : nullptr;
+            a.c_out = w.cst + ((size_t)l * T + t) * w.slot_floats;
             a.gates = w.gimg + (size_t)l * w.gimg_bytes + (size_t)t * gstep;
             a.h_last = (l == L - 1 && t == T - 1) ? stash_h + (int64_t)l * lsz + (int64_t)t * NH : nullptr;
             a.N = N; a.NT = g.NT; a.XC = g.xc(l); a.HC = g.HC; a.UG = g.UG; a.GC = g.GC; a.H = H;
@@ -870,7 +888,7 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
 int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T, const float* stash_h,
                     const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed, int training, void* workspace,
                     size_t ws_bytes, cudaStream_t st) {
-    (void)x; (void)stash_h; (void)seed;
+    (void)x; (void)stash_h; (void)stash_c; (void)seed;
     const Geom g = make_geom(N, T, F, H, L);
     W2Ws w;
     w2_layout(g, (uint8_t*)workspace, &w);
@@ -891,7 +909,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
     const PackLayout pl = pack_layout(g, l);
     const uint8_t* pk = w.pack + (size_t)l * w.pack_stride;
     uint8_t* gimg = w.gimg + (size_t)l * w.gimg_bytes;
-    const float* cs = stash_c + (int64_t)l * lsz;
+    const float* cs = w.cst + (size_t)l * T * w.slot_floats;
     const bool top = l == L - 1;
     const float* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
     float* d_in = w.dx[(L - 1 - l) & 1];
@@ -903,9 +921,9 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
     for (int t = T - 1; t >= 0; --t) {
         CellArgs c;
         c.G = gimg + (size_t)t * gstep;
-        c.c_prev = t > 0 ? cs + (int64_t)(t - 1) * NH : nullptr;
+        c.c_prev = t > 0 ? cs + (size_t)(t - 1) * w.slot_floats : nullptr;
         c.dh_rec = t < T - 1 ? w.dh_rec : nullptr;
-        c.d_out = d_out ? d_out + (int64_t)t * NH : nullptr;
+        c.d_out = d_out ? d_out + (size_t)t * w.slot_floats : nullptr;
         c.dhT = (top && t == T - 1) ? dhT : nullptr;
         c.dc = w.dc; c.bsum = w.bsum; c.first = t == T - 1 ? 1 : 0;
         c.N = N; c.UG = g.UG; c.GC = g.GC; c.H = H;
@@ -913,7 +931,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
         B200_LAUNCH_CHECK("w2_cell_bwd_kernel");
         DgradArgs d;
         d.dG = c.G; d.wd[0] = pk + pl.wd_h; d.wd[1] = l > 0 ? pk + pl.wd_x : nullptr;
-        d.out[0] = w.dh_rec; d.out[1] = l > 0 ? d_in + (int64_t)t * NH : nullptr;
+        d.out[0] = w.dh_rec; d.out[1] = l > 0 ? d_in + (size_t)t * w.slot_floats : nullptr;
         d.keep = (drop && l > 0) ? w.bits + (size_t)(l - 1) * w.bits_words + (size_t)t * N * g.UG : nullptr;
         d.np = 0;
         if (t > 0) d.part[d.np++] = 0;

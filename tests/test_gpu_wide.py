@@ -180,3 +180,94 @@ def test_wide_fused_cell_path_matches_unfused(data):
     assert float((outs[0][0] - outs[1][0]).abs().max()) < 2e-6
     assert float(outs[0][1][2]) == pytest.approx(float(outs[1][1][2]), rel=1e-6)
     assert rel_err(outs[1][2].cpu().numpy(), outs[0][2].cpu().numpy()) < 1e-5
+
+
+# ------------------------------------------------------------------------------------ bf16 operand-image engine (lstm_wide2.cu)
+def _oracle_step(m, ref, kind, masks=None):
+    em = O.ExplicitMaskLstm(m)
+    ls = O.batch_losses(m, ref, kind, 100.0, forward=(lambda x: em(x, masks)) if masks is not None else None)
+    m.zero_grad()
+    ls["total"].backward()
+    with torch.no_grad():
+        seqs = em(ref[0].flatten(0, 1), masks, return_all=True)[2]
+    return float(ls["total"].detach()), O.flat_grads(m).numpy().copy(), [s.permute(1, 0, 2).numpy() for s in seqs]
+
+
+@pytest.mark.parametrize("H,layers,p,nwin,kind", [(256, 2, 0.0, 2, "mse"), (128, 3, 0.0, 3, "combined"), (256, 3, 0.3, 3, "mse"),
+                                                  (256, 8, 0.3, 2, "mse")])
+def test_wide_bf16_engine_vs_oracle(H, layers, p, nwin, kind, data):
+    """B200_MODE_TC_FAST at hidden 128 / 256 (bf16 operands and bf16 activation stash, fp32 accumulation and cell state), including
+    the configs[2] shape hidden 256 x 8 layers with dropout 0.3: every layer's hidden states within 1e-2 absolute of the fp32
+    oracle (bf16 has 8 mantissa bits), loss within 1e-3 relative, every parameter tensor's gradient within 2e-2 of the tensor's
+    largest gradient, direction of the whole gradient cosine > 0.9999.  Dropout through the shared Philox masks."""
+    seed = 0xB16B00
+    torch.manual_seed(31 + layers)
+    m = O.OracleLstm(3, H, layers, 0.0)
+    flat = O.flat_params(m).clone()
+    ref = ref_batch(data, 0, nwin)
+    masks = None
+    if p > 0:
+        masks = [torch.from_numpy(O.dropout_mask(seed, l + 1, nwin * 100, 60, H, p)).permute(1, 0, 2) for l in range(layers - 1)]
+    total, want, seqs = _oracle_step(m, ref, kind, masks)
+    e = make_engine(flat, layers, p, "tc_fast", 3, H)
+    batch = B.DeviceBatch.from_reference(ref, DEV)
+    e.forward(batch, training=True, dropout_seed=seed)
+    hs = [e.hidden_states(l, nwin).cpu().numpy() for l in range(layers)]
+    losses = e.heads(batch, kind, 100.0, None, 1.0, True).clone()
+    e.backward(batch, True, dropout_seed=seed)
+    got = e.grads[: e.P].cpu().numpy()
+    for l in range(layers):
+        np.testing.assert_allclose(hs[l], seqs[l], rtol=0, atol=1e-2, err_msg=f"layer {l}")
+    assert float(losses[2]) == pytest.approx(total, rel=1e-3)
+    cos = float(np.dot(got, want) / (np.linalg.norm(got) * np.linalg.norm(want)))
+    assert cos > 0.9999
+    off = 0
+    for name, p_ in m.named_parameters():
+        n = p_.numel()
+        assert rel_err(got[off:off + n], want[off:off + n]) < 2e-2, name
+        off += n
+
+
+def test_wide_bf16_engine_is_deterministic_and_micro_batches_add_up(data):
+    """Two runs give bit-identical gradients; a 4-window step equals the sum of its two 2-window halves to fp32 summation order
+    (what ChunkedBatch + b200_grad_accumulate rely on)."""
+    H, layers = 256, 2
+    torch.manual_seed(77)
+    flat = O.flat_params(O.OracleLstm(3, H, layers, 0.0)).clone()
+    e = make_engine(flat, layers, 0.0, "tc_fast", 3, H)
+
+    def run(lo, hi, scale):
+        batch = B.DeviceBatch.from_reference(ref_batch(data, lo, hi), DEV)
+        e.forward(batch, training=True)
+        e.heads(batch, "mse", 100.0, None, scale, True)
+        e.backward(batch, True)
+        return e.grads[: e.P].clone()
+
+    whole = run(0, 4, 1.0)
+    again = run(0, 4, 1.0)
+    assert torch.equal(whole, again)
+    halves = run(0, 2, 0.5) + run(2, 4, 0.5)
+    assert rel_err(halves.cpu().numpy(), whole.cpu().numpy()) < 2e-4
+
+
+def test_wide_images_option_selects_the_fp32_storage_path(data):
+    """b200_set_option("wide_images", 0) sends bf16 mode through lstm_wide.cu (fp32 activations in global memory): same loss to
+    bf16 accuracy, so the two implementations check each other."""
+    H, layers = 256, 2
+    torch.manual_seed(3)
+    flat = O.flat_params(O.OracleLstm(3, H, layers, 0.0)).clone()
+    batch = B.DeviceBatch.from_reference(ref_batch(data, 0, 2), DEV)
+    lib = B._lib.load()
+    out = []
+    try:
+        for images in (1, 0):
+            assert lib.b200_set_option(b"wide_images", images) == 0
+            e = make_engine(flat, layers, 0.0, "tc_fast", 3, H)
+            e.forward(batch, training=True)
+            losses = e.heads(batch, "mse", 100.0, None, 1.0, True).clone()
+            e.backward(batch, True)
+            out.append((float(losses[2]), e.grads[: e.P].cpu().numpy().copy()))
+    finally:
+        lib.b200_set_option(b"wide_images", 1)
+    assert out[0][0] == pytest.approx(out[1][0], rel=1e-3)
+    assert rel_err(out[0][1], out[1][1]) < 2e-2
