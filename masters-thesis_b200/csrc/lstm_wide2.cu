@@ -3,20 +3,23 @@
 // them with bulk copies only (no thread touches an operand on its way to the tensor core), and the LSTM cell runs in the
 // epilogue of the forward GEMM.  lstm_wide.cu keeps the fp32-storage path of B200_MODE_TC_PRECISE.
 //
-// Chunk = the [128 rows x 64 columns] bf16 operand image in the interleaved (SWIZZLE_NONE) layout of tc_common.cuh, 16 KB:
-//     byte(r, c) = (r / 8) * 1024 + (c / 8) * 128 + (r % 8) * 16 + (c % 8) * 2
-// Read K-major it is a [128 x K = 64] operand; read MN-major the same bytes are a [K = 128 rows x 64] operand, and any 8-row
-// group of it is 1 KB of contiguous memory.  With NT = ceil(N / 128) row tiles, HC = H / 64, UG = H / 32, GC = 4H / 64:
+// Activation chunk = a [128 rows x 128 columns] bf16 operand image in the interleaved (SWIZZLE_NONE) layout of tc_common.cuh, 32 KB:
+//     byte(r, c) = (r / 8) * 2048 + (c / 8) * 128 + (r % 8) * 16 + (c % 8) * 2
+// Read K-major it is a [128 x K = 128] operand (two K = 64 halves at +0 / +1024, SBO 2048); read MN-major the same bytes are a
+// [K = 128 rows x 128] operand whose 64-row halves are 16 KB of contiguous memory -- so every kernel stages its operands with a
+// few large bulk copies.  (A first version with [128 x 64] chunks had to assemble the MN-major stages of the weight gradient from
+// 64 copies of 1 KB; ncu showed the loader warp serialising them, 4.0 k clk per stage against 1.0 k clk of MMAs.)
+// With NT = ceil(N / 128) row tiles, HC = H / 128, UG = H / 32:
 //   Himg[l]  [T][NT][HC] chunks   h_t of layer l (written by the forward epilogue); under dropout a second, masked set is the
 //                                 input of layer l + 1 (the 1/(1-p) lives in the packed W_ih, as in lstm_tc.cu)
 //   X0img    [T][NT][1]  chunk    the F input features of layer 0, columns >= F zero
-//   Gimg[l]  [T][NT][GC] chunks   activated gates (forward) -> pre-activation gradients dG (backward, in place); gate columns
+//   Gimg[l]  [T][NT][UG] chunks   activated gates (forward) -> pre-activation gradients dG (backward, in place); gate columns
 //                                 are permuted: g' = (u / 32) * 128 + gate * 32 + u % 32, so that the four gates of 32 hidden
-//                                 units are one 128-column block (one N tile of the forward GEMM, one M tile of the weight gradient)
+//                                 units are one chunk (one N tile of the forward GEMM, one M tile of the weight gradient)
 //   c, dc, dh, dx                  fp32 in the "row-slot" layout [tile][u / 8][128 rows][8]: the thread that owns a row (TMEM lane) moves
 //                                 32 bytes and a warp 1 KB of contiguous memory (row-major [N][H] costs 32 cache lines per warp access)
-//   Wf[l]    [UG][KC] chunks      rows g' of [W_ih | W_hh], KC = (1 or HC) + HC K-chunks
-//   Wd[l]    per part (h, x): [GC][64 g' rows x (64 * HC) columns] MN-major images for dG . W
+//   Wf[l]    [UG][KC] images      [128 rows g' x 64] K-major (16 KB each) of [W_ih | W_hh], KC = 2 * ((1 or HC) + HC) K-chunks of 64
+//   Wd[l]    per part (h, x): [4H / 64][64 g' rows x H columns] MN-major images for dG . W
 //
 //   forward  step t: w2_fwd_kernel    gates = [x_t | h_{t-1}] . Wf^T, cell in the epilogue; persistent CTAs, each keeps the weights
 //                                     of one unit group (128 KB) in shared memory and streams the A chunks of its row tiles
@@ -37,13 +40,17 @@ using namespace tc;
 namespace {
 
 constexpr int TM = 128;
-constexpr uint32_t CHUNK = 16384, RG_BYTES = 1024;
+constexpr uint32_t CHUNK = 16384, RG_BYTES = 1024;          // weight image [128 x 64]
+constexpr uint32_t WCHUNK = 32768, WRG_BYTES = 2048;         // activation chunk [128 x 128]
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr int W2_THREADS = 320;                 // 8 epilogue warps, loader warp, MMA warp
 
 __host__ __device__ inline size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
 __host__ __device__ inline uint32_t chunk_off(int r, int c) {
     return (uint32_t)(r >> 3) * 1024u + (uint32_t)(c >> 3) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(c & 7) * 2u;
+}
+__host__ __device__ inline uint32_t wchunk_off(int r, int c) {
+    return (uint32_t)(r >> 3) * 2048u + (uint32_t)(c >> 3) * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)(c & 7) * 2u;
 }
 
 // fp32 row-slot layout: float index of (row, unit) and of the 8-float slot (tile, octet, r)
@@ -52,15 +59,15 @@ __host__ __device__ inline size_t slot_off(int64_t tile, int octet, int r, int H
 struct Geom {
     int F, H, L, T;
     int64_t N;
-    int NT, HC, UG, GC;
-    __host__ __device__ int xc(int l) const { return l == 0 ? 1 : HC; }       // K-chunks of the layer input
-    __host__ __device__ int kc(int l) const { return xc(l) + HC; }
+    int NT, HC, UG, GC;                                                       // GC = 4H / 64 K-chunks of the data gradient
+    __host__ __device__ int xc(int l) const { return l == 0 ? 1 : HC; }       // activation chunks of the layer input
+    __host__ __device__ int kc(int l) const { return 2 * (xc(l) + HC); }      // K = 64 weight images per unit group
 };
 inline Geom make_geom(int64_t N, int T, int F, int H, int L) {
     Geom g;
     g.F = F; g.H = H; g.L = L; g.T = T; g.N = N;
     g.NT = (int)((N + TM - 1) / TM);
-    g.HC = H / 64; g.UG = H / 32; g.GC = H / 16;
+    g.HC = H / 128; g.UG = H / 32; g.GC = H / 16;
     return g;
 }
 
@@ -113,9 +120,9 @@ inline PackLayout pack_layout(const Geom& g, int l) {
 // in_scale: 1/(1-p) of the inter-layer dropout folded into W_ih (layers > 0)
 __global__ void __launch_bounds__(256)
 w2_pack_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, const float* __restrict__ b_ih, const float* __restrict__ b_hh,
-               int in, int H, int XC, float in_scale, uint8_t* __restrict__ wf, uint8_t* __restrict__ wd_h, uint8_t* __restrict__ wd_x,
+               int in, int H, int XC /* K = 64 images of the x part */, float in_scale, uint8_t* __restrict__ wf, uint8_t* __restrict__ wd_h, uint8_t* __restrict__ wd_x,
                float* __restrict__ biasp) {
-    const int HC = H / 64, KC = XC + HC, G4 = 4 * H;
+    const int KC = XC + H / 64, G4 = 4 * H;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
     const int KW = KC * 64;
     for (int64_t i = tid; i < (int64_t)G4 * KW; i += nthr) {
@@ -148,14 +155,14 @@ w2_pack_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, c
     }
 }
 
-// layer-0 input as operand chunks: X0img[t][tile] (columns >= F and rows >= N zero); x is [T][N][F] fp32
+// layer-0 input as activation chunks: X0img[t][tile] (columns >= F and rows >= N zero); x is [T][N][F] fp32
 __global__ void __launch_bounds__(256)
 w2_x0_kernel(const float* __restrict__ x, int64_t N, int T, int F, int NT, uint8_t* __restrict__ out) {
     // one thread per (t, tile, row, 8-column core)
-    const int64_t total = (int64_t)T * NT * TM * 8;
+    const int64_t total = (int64_t)T * NT * TM * 16;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int core = (int)(i & 7), r = (int)((i >> 3) & 127);
-        const int64_t tt = i >> 10;                                   // t * NT + tile
+        const int core = (int)(i & 15), r = (int)((i >> 4) & 127);
+        const int64_t tt = i >> 11;                                   // t * NT + tile
         const int64_t tile = tt % NT, t = tt / NT, row = tile * TM + r;
         float v[8];
 #pragma unroll
@@ -163,7 +170,7 @@ w2_x0_kernel(const float* __restrict__ x, int64_t N, int T, int F, int NT, uint8
             const int c = core * 8 + j;
             v[j] = (row < N && c < F) ? x[((int64_t)t * N + row) * F + c] : 0.f;
         }
-        *reinterpret_cast<uint4*>(out + (size_t)tt * CHUNK + chunk_off(r, core * 8)) = pack_bf8(v);
+        *reinterpret_cast<uint4*>(out + (size_t)tt * WCHUNK + wchunk_off(r, core * 8)) = pack_bf8(v);
     }
 }
 
@@ -190,14 +197,14 @@ w2_bits_kernel(uint64_t seed, int layer, int64_t N, int T, int UG, float p, uint
 // hidden states of one layer as fp32 [T][N][H] (b200_lstm_hidden_states)
 __global__ void __launch_bounds__(256)
 w2_unpack_kernel(const uint8_t* __restrict__ himg, int64_t N, int T, int H, int NT, float* __restrict__ out) {
-    const int HC = H / 64;
+    const int HC = H / 128;
     const int64_t total = (int64_t)T * N * (H / 8);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int c8 = (int)(i % (H / 8));
         const int64_t tr = i / (H / 8), row = tr % N, t = tr / N;
         const int64_t tile = row / TM;
         const int r = (int)(row % TM), col = c8 * 8;
-        const uint4 q = *reinterpret_cast<const uint4*>(himg + (((size_t)t * NT + tile) * HC + (col >> 6)) * CHUNK + chunk_off(r, col & 63));
+        const uint4 q = *reinterpret_cast<const uint4*>(himg + (((size_t)t * NT + tile) * HC + (col >> 7)) * WCHUNK + wchunk_off(r, col & 127));
         float v[8];
         unpack_bf8(q, v);
         st8(out + (t * N + row) * H + col, v);
@@ -208,7 +215,7 @@ w2_unpack_kernel(const uint8_t* __restrict__ himg, int64_t N, int T, int H, int 
 // ------------------------------------------------------------------------------------------------ forward step
 // One LSTM step of one layer for all rows.  CTA c owns unit group ug = c % UG (32 hidden units = 128 permuted gate columns, its
 // KC weight chunks stay in shared memory for the whole launch) and the row tiles m = c / UG, c / UG + gridDim.x / UG, ...
-// Per tile: KC bulk copies of 16 KB bring [x_t | h_{t-1}], 4 * KC MMAs (M 128, N 128, K 16) accumulate the gates into one of four
+// Per tile: XC + HC bulk copies of 32 KB bring [x_t | h_{t-1}], 8 MMAs each (M 128, N 128, K 16) accumulate the gates into one of four
 // TMEM slots, and one of two epilogue warp groups (alternating tiles) applies the cell and writes c_t, the activated gates and its
 // 32 columns of the h_t image.  Activations as in lstm_tc.cu: the bias is folded into the exponent argument, one reciprocal
 // serves i, f and g, one serves o and tanh(c).
@@ -218,10 +225,10 @@ struct FwdArgs {
     const float* c_prev; float* c_out; uint8_t* gates; float* h_last;
     int64_t N; int NT, XC, HC, UG, GC, H;
 };
-constexpr int FWD_NST = 6;
+constexpr int FWD_NST = 3;
 constexpr uint32_t FWD_W_MAX = 8 * CHUNK;
 struct FwdSmem {
-    static constexpr uint32_t off_w = 0, off_ring = FWD_W_MAX, off_bias = off_ring + FWD_NST * CHUNK, off_bar = off_bias + 128 * 4;
+    static constexpr uint32_t off_w = 0, off_ring = FWD_W_MAX, off_bias = off_ring + FWD_NST * WCHUNK, off_bar = off_bias + 128 * 4;
     // full[NST], empty[NST], acc_full[4], acc_free[4], w_ready
     static constexpr uint32_t nbar = 2 * FWD_NST + 9, off_tmem = off_bar + nbar * 8, total = off_tmem + 16;
 };
@@ -238,8 +245,8 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     float* bias_s = reinterpret_cast<float*>(smem + S::off_bias);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ug = (int)(blockIdx.x % a.UG), first = (int)(blockIdx.x / a.UG), stride = (int)(gridDim.x / a.UG);
-    const int KC = a.XC + a.HC;
-    const int nk = a.hprev ? KC : a.XC;                 // t = 0: h_{-1} = 0, the recurrent K-chunks are skipped
+    const int KC = 2 * (a.XC + a.HC);                   // weight images of this unit group
+    const int nk = a.hprev ? a.XC + a.HC : a.XC;        // activation chunks per tile; t = 0: h_{-1} = 0, the recurrent ones are skipped
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < FWD_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -257,7 +264,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     if (warp < 8) {
         // ================================ epilogue: LSTM cell of 32 units of one row ==========================
         const int grp = warp >> 2, lq = warp & 3, r = lq * 32 + lane;
-        const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 16u;
+        const uint32_t row_off = (uint32_t)(r >> 3) * WRG_BYTES + (uint32_t)(r & 7) * 16u;
         const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16);
         int i = 0;
         for (int m = first; m < a.NT; m += stride, ++i) {
@@ -276,9 +283,10 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             }
             mbar_wait(&acc_full[slot], (uint32_t)((i >> 2) & 1));
             tc_fence_after();
-            uint8_t* gbase = a.gates + ((size_t)m * a.GC + ug * 2) * CHUNK + row_off;
-            uint8_t* hdst = a.hout + ((size_t)m * a.HC + (ug >> 1)) * CHUNK + row_off + (uint32_t)((ug & 1) * 4) * 128u;
-            uint8_t* mdst = a.hmask ? a.hmask + ((size_t)m * a.HC + (ug >> 1)) * CHUNK + row_off + (uint32_t)((ug & 1) * 4) * 128u : nullptr;
+            uint8_t* gbase = a.gates + ((size_t)m * a.UG + ug) * WCHUNK + row_off;
+            const size_t hoff = ((size_t)m * a.HC + (ug >> 2)) * WCHUNK + row_off + (uint32_t)((ug & 3) * 4) * 128u;
+            uint8_t* hdst = a.hout + hoff;
+            uint8_t* mdst = a.hmask ? a.hmask + hoff : nullptr;
             uint32_t keep = 0u;
             if (mdst != nullptr && live) keep = a.keep[row * a.UG + ug];
 #pragma unroll
@@ -309,11 +317,11 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     cv[j] = c;
                     hv[j] = (Ec - 1.f) * r2;
                 }
-                // activated gates: chunk ug * 2 + gate / 2, 16-byte slot (gate % 2) * 4 + uc of this row
+                // activated gates: chunk ug, 16-byte slot gate * 4 + uc of this row
                 *reinterpret_cast<uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u) = pack_bf8(ai);
                 *reinterpret_cast<uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u) = pack_bf8(af);
-                *reinterpret_cast<uint4*>(gbase + CHUNK + (uint32_t)(0 * 4 + uc) * 128u) = pack_bf8(ag);
-                *reinterpret_cast<uint4*>(gbase + CHUNK + (uint32_t)(1 * 4 + uc) * 128u) = pack_bf8(ao);
+                *reinterpret_cast<uint4*>(gbase + (uint32_t)(2 * 4 + uc) * 128u) = pack_bf8(ag);
+                *reinterpret_cast<uint4*>(gbase + (uint32_t)(3 * 4 + uc) * 128u) = pack_bf8(ao);
                 const uint4 h8 = pack_bf8(hv);
                 *reinterpret_cast<uint4*>(hdst + (uint32_t)uc * 128u) = h8;
                 if (mdst != nullptr) *reinterpret_cast<uint4*>(mdst + (uint32_t)uc * 128u) = and_mask8(h8, (keep >> (uc * 8)) & 0xFFu);
@@ -334,9 +342,9 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                 for (int kc = 0; kc < nk; ++kc, ++q) {
                     const uint32_t st = q % FWD_NST;
                     if (q >= FWD_NST) mbar_wait(&empty[st], ((q / FWD_NST) - 1) & 1);
-                    const uint8_t* src = kc < a.XC ? a.xin + ((size_t)m * a.XC + kc) * CHUNK : a.hprev + ((size_t)m * a.HC + (kc - a.XC)) * CHUNK;
-                    mbar_arrive_expect_tx(&full[st], CHUNK);
-                    bulk_copy_g2s(smem + S::off_ring + st * CHUNK, src, CHUNK, &full[st]);
+                    const uint8_t* src = kc < a.XC ? a.xin + ((size_t)m * a.XC + kc) * WCHUNK : a.hprev + ((size_t)m * a.HC + (kc - a.XC)) * WCHUNK;
+                    mbar_arrive_expect_tx(&full[st], WCHUNK);
+                    bulk_copy_g2s(smem + S::off_ring + st * WCHUNK, src, WCHUNK, &full[st]);
                 }
             }
         }
@@ -358,11 +366,11 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     const uint32_t st = q % FWD_NST;
                     mbar_wait(&full[st], (q / FWD_NST) & 1);
                     tc_fence_after();
-                    const uint32_t aa = s_base + S::off_ring + st * CHUNK, bb = s_base + S::off_w + (uint32_t)kc * CHUNK;
+                    const uint32_t aa = s_base + S::off_ring + st * WCHUNK, bb = s_base + S::off_w + (uint32_t)(2 * kc) * CHUNK;
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks)
-                        umma_bf16(d, make_desc(aa + ks * 256, LBO_BYTES, RG_BYTES), make_desc(bb + ks * 256, LBO_BYTES, RG_BYTES), idesc,
-                                  (kc > 0 || ks > 0) ? 1u : 0u);
+                    for (int ks = 0; ks < 8; ++ks)          // two K = 64 halves of the activation chunk, one weight image each
+                        umma_bf16(d, make_desc(aa + (ks >> 2) * 1024 + (ks & 3) * 256, LBO_BYTES, WRG_BYTES),
+                                  make_desc(bb + (ks >> 2) * CHUNK + (ks & 3) * 256, LBO_BYTES, RG_BYTES), idesc, (kc > 0 || ks > 0) ? 1u : 0u);
                     umma_commit(&empty[st]);
                 }
                 umma_commit(&acc_full[slot]);
@@ -400,13 +408,13 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
         const int rg = warp * 4 + it, r = rg * 8 + rr;
         const int64_t row = (int64_t)m * TM + r;
         const bool live = row < a.N;
-        uint8_t* gbase = a.G + ((size_t)m * a.GC + ug * 2) * CHUNK + (uint32_t)rg * 1024u + (uint32_t)rr * 16u;
+        uint8_t* gbase = a.G + ((size_t)m * a.UG + ug) * WCHUNK + (uint32_t)rg * WRG_BYTES + (uint32_t)rr * 16u;
         const size_t e = slot_off(m, ug * 4 + uc, r, a.H);
         float gi[8], gf[8], gg[8], go[8], cp[8], dh[8], dc[8], v[32];
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u), gi);
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u), gf);
-        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + CHUNK + (uint32_t)(0 * 4 + uc) * 128u), gg);
-        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + CHUNK + (uint32_t)(1 * 4 + uc) * 128u), go);
+        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(2 * 4 + uc) * 128u), gg);
+        unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(3 * 4 + uc) * 128u), go);
 #pragma unroll
         for (int j = 0; j < 8; ++j) { cp[j] = 0.f; dh[j] = 0.f; dc[j] = 0.f; }
         {
@@ -445,7 +453,7 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
             for (int k = 0; k < 4; ++k) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) t8[j] = v[k * 8 + j];
-                *reinterpret_cast<uint4*>(gbase + (uint32_t)(k >> 1) * CHUNK + (uint32_t)((k & 1) * 4 + uc) * 128u) = pack_bf8(t8);
+                *reinterpret_cast<uint4*>(gbase + (uint32_t)(k * 4 + uc) * 128u) = pack_bf8(t8);
             }
         }
 #pragma unroll
@@ -486,26 +494,29 @@ w2_bsum_reduce_kernel(const float* __restrict__ bsum, int NT, int UG, int H, flo
 
 // ------------------------------------------------------------------------------------------------ data gradient
 // out[p] = dG_t . Wd[p]  (p = 0: dh_{t-1} = dG . W_hh, p = 1: dx_t = dG . W_ih, masked with the keep bits of this layer's input;
-// the 1/(1-p) is in the packed W_ih).  A task = two row tiles x one part: per K-chunk of 64 gate columns two A chunks and one
-// [64 x H] B image arrive by bulk copy, 8 MMAs (M 128, N = H, B read MN-major) feed two TMEM accumulators; 3 stages of 64 KB.
+// the 1/(1-p) is in the packed W_ih).  A task = two row tiles x one part.  Per unit group (K = 128 gate columns) the two dG chunks
+// of the tiles arrive with one 32 KB bulk copy each (A ring, 2 slots of 64 KB); the matching [64 x H] halves of the weight image
+// arrive separately (B ring, 3 slots of 32 KB); 8 MMAs per half (M 128, N = H, B read MN-major) feed two TMEM accumulators.
 struct DgradArgs {
     const uint8_t* dG; const uint8_t* wd[2]; float* out[2]; const uint32_t* keep;
     int np; int part[2];
-    int64_t N; int NT, GC, H, UG;
+    int64_t N; int NT, H, UG;
 };
-constexpr int DG_NST = 3;
-constexpr uint32_t DG_STAGE = 4 * CHUNK;
+constexpr int DG_NSA = 2, DG_NSB = 3;
 struct DgSmem {
-    static constexpr uint32_t off_bar = DG_NST * DG_STAGE;          // full[NST], empty[NST], acc_full, acc_free
-    static constexpr uint32_t off_tmem = off_bar + (2 * DG_NST + 2) * 8, total = off_tmem + 16;
+    static constexpr uint32_t off_b = DG_NSA * 2 * WCHUNK, off_bar = off_b + DG_NSB * WCHUNK;
+    // fullA[2], emptyA[2], fullB[3], emptyB[3], acc_full, acc_free
+    static constexpr uint32_t off_tmem = off_bar + (2 * DG_NSA + 2 * DG_NSB + 2) * 8, total = off_tmem + 16;
 };
 
 __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
     using S = DgSmem;
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::off_bar);
-    uint64_t* empty = full + DG_NST;
-    uint64_t* acc_full = empty + DG_NST;
+    uint64_t* fullA = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    uint64_t* emptyA = fullA + DG_NSA;
+    uint64_t* fullB = emptyA + DG_NSA;
+    uint64_t* emptyB = fullB + DG_NSB;
+    uint64_t* acc_full = emptyB + DG_NSB;
     uint64_t* acc_free = acc_full + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -513,7 +524,8 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
     const uint32_t b_bytes = (uint32_t)(64 * a.H * 2), rgs = (uint32_t)(a.H / 8) * 128u;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < DG_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < DG_NSA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+        for (int i = 0; i < DG_NSB; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
         mbar_init(acc_full, 1);
         mbar_init(acc_free, 8);
         fence_barrier_init();
@@ -556,18 +568,23 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
         }
     } else if (warp == 8) {
         if (lane == 0) {
-            uint32_t q = 0;
+            uint32_t qa = 0, qb = 0;
             for (int task = blockIdx.x; task < ntask; task += gridDim.x) {
                 const int p = a.part[task % a.np], m0 = 2 * (task / a.np);
                 const bool two = m0 + 1 < a.NT;
-                for (int kc = 0; kc < a.GC; ++kc, ++q) {
-                    const uint32_t st = q % DG_NST;
-                    if (q >= DG_NST) mbar_wait(&empty[st], ((q / DG_NST) - 1) & 1);
-                    uint8_t* sa = smem + st * DG_STAGE;
-                    mbar_arrive_expect_tx(&full[st], (two ? 2u : 1u) * CHUNK + b_bytes);
-                    bulk_copy_g2s(sa, a.dG + ((size_t)m0 * a.GC + kc) * CHUNK, CHUNK, &full[st]);
-                    if (two) bulk_copy_g2s(sa + CHUNK, a.dG + ((size_t)(m0 + 1) * a.GC + kc) * CHUNK, CHUNK, &full[st]);
-                    bulk_copy_g2s(sa + 2 * CHUNK, a.wd[p] + (size_t)kc * b_bytes, b_bytes, &full[st]);
+                for (int ug = 0; ug < a.UG; ++ug, ++qa) {
+                    const uint32_t sa = qa % DG_NSA;
+                    if (qa >= DG_NSA) mbar_wait(&emptyA[sa], ((qa / DG_NSA) - 1) & 1);
+                    uint8_t* da = smem + sa * 2 * WCHUNK;
+                    mbar_arrive_expect_tx(&fullA[sa], (two ? 2u : 1u) * WCHUNK);
+                    bulk_copy_g2s(da, a.dG + ((size_t)m0 * a.UG + ug) * WCHUNK, WCHUNK, &fullA[sa]);
+                    if (two) bulk_copy_g2s(da + WCHUNK, a.dG + ((size_t)(m0 + 1) * a.UG + ug) * WCHUNK, WCHUNK, &fullA[sa]);
+                    for (int half = 0; half < 2; ++half, ++qb) {
+                        const uint32_t sb = qb % DG_NSB;
+                        if (qb >= DG_NSB) mbar_wait(&emptyB[sb], ((qb / DG_NSB) - 1) & 1);
+                        mbar_arrive_expect_tx(&fullB[sb], b_bytes);
+                        bulk_copy_g2s(smem + S::off_b + sb * WCHUNK, a.wd[p] + (size_t)(ug * 2 + half) * b_bytes, b_bytes, &fullB[sb]);
+                    }
                 }
             }
         }
@@ -576,26 +593,31 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
         if (lane == 0) {
             const uint32_t idesc = make_idesc_bf16(TM, a.H, 0, 1);
             const uint32_t s_base = smem_u32(smem);
-            uint32_t q = 0;
+            uint32_t qa = 0, qb = 0;
             int i = 0;
             for (int task = blockIdx.x; task < ntask; task += gridDim.x, ++i) {
                 const bool two = 2 * (task / a.np) + 1 < a.NT;
                 if (i > 0) mbar_wait(acc_free, (uint32_t)((i - 1) & 1));
                 tc_fence_after();
-                for (int kc = 0; kc < a.GC; ++kc, ++q) {
-                    const uint32_t st = q % DG_NST;
-                    mbar_wait(&full[st], (q / DG_NST) & 1);
-                    tc_fence_after();
-                    const uint32_t sa = s_base + st * DG_STAGE, sb = sa + 2 * CHUNK;
+                for (int ug = 0; ug < a.UG; ++ug, ++qa) {
+                    const uint32_t sa = qa % DG_NSA;
+                    mbar_wait(&fullA[sa], (qa / DG_NSA) & 1);
+                    for (int half = 0; half < 2; ++half, ++qb) {
+                        const uint32_t sb = qb % DG_NSB;
+                        mbar_wait(&fullB[sb], (qb / DG_NSB) & 1);
+                        tc_fence_after();
+                        const uint32_t da = s_base + sa * 2 * WCHUNK + half * 1024, db = s_base + S::off_b + sb * WCHUNK;
 #pragma unroll
-                    for (int t2 = 0; t2 < 2; ++t2) {
-                        if (t2 == 1 && !two) break;
+                        for (int t2 = 0; t2 < 2; ++t2) {
+                            if (t2 == 1 && !two) break;
 #pragma unroll
-                        for (int ks = 0; ks < 4; ++ks)
-                            umma_bf16(tmem_base + (uint32_t)(t2 * 256), make_desc(sa + t2 * CHUNK + ks * 256, LBO_BYTES, RG_BYTES),
-                                      make_desc(sb + ks * 2 * rgs, rgs, LBO_BYTES), idesc, (kc > 0 || ks > 0) ? 1u : 0u);
+                            for (int ks = 0; ks < 4; ++ks)
+                                umma_bf16(tmem_base + (uint32_t)(t2 * 256), make_desc(da + t2 * WCHUNK + ks * 256, LBO_BYTES, WRG_BYTES),
+                                          make_desc(db + ks * 2 * rgs, rgs, LBO_BYTES), idesc, (ug > 0 || half > 0 || ks > 0) ? 1u : 0u);
+                        }
+                        umma_commit(&emptyB[sb]);
                     }
-                    umma_commit(&empty[st]);
+                    umma_commit(&emptyA[sa]);
                 }
                 umma_commit(acc_full);
             }
@@ -608,16 +630,16 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------ weight gradient
-// part[z] = dG^T . [x | h_{t-1}] over the K-chunks (64 rows of one (t, row tile)) of split z; both operands are read MN-major, so
-// a stage is assembled from 1 KB row-group pieces of the chunks: A [64 rows x 128 gate columns] for two M tiles (two unit groups),
-// B [64 rows x N] with N = the x part (nt = 0) or the h part (nt = 1) of the K-concatenated weight matrix.
+// part[z] = dG^T . [x | h_{t-1}] over the K-chunks (64 rows of one (t, row tile)) of split z; both operands are read MN-major: a
+// stage is the 64-row halves (16 KB, contiguous) of two dG chunks (two unit groups = two M tiles) and of the XC or HC activation
+// chunks of the x part (nt = 0) or the h part (nt = 1); 4 MMAs (M 128, N 128, K 16) per (M tile, activation chunk).
 struct WgradArgs {
     const uint8_t* dG; const uint8_t* xsrc; const uint8_t* hsrc; const uint8_t* zero; float* part;
-    int T, NT, GC, XC, HC, H;
+    int T, NT, UG, XC, HC, H;
     int splits; int64_t kps;
 };
 constexpr int WG_NST = 3;
-constexpr uint32_t WG_STAGE = 4 * CHUNK;
+constexpr uint32_t WG_STAGE = 2 * WCHUNK, WG_HALF = WCHUNK / 2;
 struct WgSmem {
     static constexpr uint32_t off_bar = WG_NST * WG_STAGE;          // full[NST], empty[NST], acc_full
     static constexpr uint32_t off_tmem = off_bar + (2 * WG_NST + 1) * 8, total = off_tmem + 16;
@@ -634,11 +656,10 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_wgrad_kernel(WgradArgs a) {
     const int ntask = (a.H / 64) * 2;                          // (M pair, N tile)
     const int z = (int)(blockIdx.x / ntask), task = (int)(blockIdx.x % ntask);
     const int mp = task >> 1, nt = task & 1;
-    const int nch = nt == 0 ? a.XC : a.HC;
-    const int KW = (a.XC + a.HC) * 64, G4 = 4 * a.H;
+    const int nch = nt == 0 ? a.XC : a.HC;                     // activation chunks (128 columns each) of this N tile
+    const int KW = (a.XC + a.HC) * 128, G4 = 4 * a.H;
     const int64_t ktot = (int64_t)a.T * a.NT * 2;
     const int64_t k_beg = (int64_t)z * a.kps, k_end = k_beg + a.kps < ktot ? k_beg + a.kps : ktot;
-    const uint32_t brg = (uint32_t)nch * 1024u;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < WG_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -659,8 +680,8 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_wgrad_kernel(WgradArgs a) {
             mbar_wait(acc_full, 0u);
             tc_fence_after();
         }
-        float* dst = a.part + ((size_t)z * G4 + (size_t)(2 * mp + mt) * 128 + r) * KW + (nt == 0 ? 0 : a.XC * 64);
-        for (int c0 = 0; c0 < nch * 64; c0 += 32) {
+        float* dst = a.part + ((size_t)z * G4 + (size_t)(2 * mp + mt) * 128 + r) * KW + (nt == 0 ? 0 : a.XC * 128);
+        for (int c0 = 0; c0 < nch * 128; c0 += 32) {
             float v[4][8];
             if (any) {
 #pragma unroll
@@ -676,47 +697,43 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_wgrad_kernel(WgradArgs a) {
             for (int k = 0; k < 4; ++k) st8(dst + c0 + k * 8, v[k]);
         }
     } else if (warp == 8) {
-        uint32_t q = 0;
-        for (int64_t kq = k_beg; kq < k_end; ++kq, ++q) {
-            const uint32_t st = q % WG_NST;
-            const int64_t tm = kq >> 1;                        // t * NT + m
-            const int half = (int)(kq & 1), t = (int)(tm / a.NT);
-            if (q >= WG_NST) mbar_wait(&empty[st], ((q / WG_NST) - 1) & 1);
-            uint8_t* sa = smem + st * WG_STAGE;
-            uint8_t* sb = sa + 2 * CHUNK;
-            if (lane == 0) mbar_arrive_expect_tx(&full[st], 2 * CHUNK + 8u * brg);
-            __syncwarp();
-            {   // A: (M tile, row group, chunk of the tile) = 32 pieces of 1 KB
-                const int mt = lane >> 4, rg = (lane >> 1) & 7, ci = lane & 1;
-                const uint8_t* src = a.dG + ((size_t)tm * a.GC + (size_t)(2 * mp + mt) * 2 + ci) * CHUNK + (size_t)(half * 8 + rg) * 1024;
-                bulk_copy_g2s(sa + mt * CHUNK + rg * 2048 + ci * 1024, src, 1024, &full[st]);
-            }
-            {   // B: (row group, chunk) = 8 * nch pieces
-                const int rg = lane >> 2, ci = lane & 3;
-                if (ci < nch) {
-                    const uint8_t* ch = nt == 0 ? a.xsrc + ((size_t)tm * a.XC + ci) * CHUNK
-                                                : (t > 0 ? a.hsrc + ((size_t)(tm - a.NT) * a.HC + ci) * CHUNK : a.zero);
-                    bulk_copy_g2s(sb + rg * brg + ci * 1024, ch + (size_t)(half * 8 + rg) * 1024, 1024, &full[st]);
+        if (lane == 0) {
+            uint32_t q = 0;
+            for (int64_t kq = k_beg; kq < k_end; ++kq, ++q) {
+                const uint32_t st = q % WG_NST;
+                const int64_t tm = kq >> 1;                        // t * NT + m
+                const int half = (int)(kq & 1), t = (int)(tm / a.NT);
+                if (q >= WG_NST) mbar_wait(&empty[st], ((q / WG_NST) - 1) & 1);
+                uint8_t* sa = smem + st * WG_STAGE;
+                uint8_t* sb = sa + WCHUNK;
+                mbar_arrive_expect_tx(&full[st], (uint32_t)(2 + nch) * WG_HALF);
+                for (int mt = 0; mt < 2; ++mt)
+                    bulk_copy_g2s(sa + mt * WG_HALF, a.dG + ((size_t)tm * a.UG + (2 * mp + mt)) * WCHUNK + (size_t)half * WG_HALF, WG_HALF, &full[st]);
+                for (int ci = 0; ci < nch; ++ci) {
+                    const uint8_t* ch = nt == 0 ? a.xsrc + ((size_t)tm * a.XC + ci) * WCHUNK + (size_t)half * WG_HALF
+                                                : (t > 0 ? a.hsrc + ((size_t)(tm - a.NT) * a.HC + ci) * WCHUNK + (size_t)half * WG_HALF : a.zero);
+                    bulk_copy_g2s(sb + ci * WG_HALF, ch, WG_HALF, &full[st]);
                 }
             }
         }
         __syncwarp();
     } else {
         if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(TM, nch * 64, 1, 1);
+            constexpr uint32_t idesc = make_idesc_bf16(TM, 128, 1, 1);
             const uint32_t s_base = smem_u32(smem);
             uint32_t q = 0;
             for (int64_t kq = k_beg; kq < k_end; ++kq, ++q) {
                 const uint32_t st = q % WG_NST;
                 mbar_wait(&full[st], (q / WG_NST) & 1);
                 tc_fence_after();
-                const uint32_t sa = s_base + st * WG_STAGE, sb = sa + 2 * CHUNK;
+                const uint32_t sa = s_base + st * WG_STAGE, sb = sa + WCHUNK;
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt)
+                    for (int ci = 0; ci < nch; ++ci)
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks)
-                        umma_bf16(tmem_base + (uint32_t)(mt * 256), make_desc(sa + mt * CHUNK + ks * 2 * 2048, 2048, LBO_BYTES),
-                                  make_desc(sb + ks * 2 * brg, brg, LBO_BYTES), idesc, (q > 0 || ks > 0) ? 1u : 0u);
+                        for (int ks = 0; ks < 4; ++ks)
+                            umma_bf16(tmem_base + (uint32_t)(mt * 256 + ci * 128), make_desc(sa + mt * WG_HALF + ks * 2 * WRG_BYTES, WRG_BYTES, LBO_BYTES),
+                                      make_desc(sb + ci * WG_HALF + ks * 2 * WRG_BYTES, WRG_BYTES, LBO_BYTES), idesc, (q > 0 || ks > 0) ? 1u : 0u);
                 umma_commit(&empty[st]);
             }
             if (k_end > k_beg) umma_commit(acc_full);
@@ -730,7 +747,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_wgrad_kernel(WgradArgs a) {
 
 // grads of W_ih [4H][in] and W_hh [4H][H] in torch order = sum over the splits (fixed order), x part scaled by 1/(1-p)
 __global__ void __launch_bounds__(256)
-w2_wgrad_reduce_kernel(const float* __restrict__ part, int splits, int H, int XC, int in, float x_scale, float* __restrict__ gw_ih,
+w2_wgrad_reduce_kernel(const float* __restrict__ part, int splits, int H, int XC /* K = 64 images of the x part */, int in, float x_scale, float* __restrict__ gw_ih,
                        float* __restrict__ gw_hh) {
     const int G4 = 4 * H, KW = (XC + H / 64) * 64;
     const int64_t total = (int64_t)G4 * (in + H);
@@ -769,14 +786,14 @@ void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
     auto take = [&](size_t bytes) { uint8_t* q = p ? p + off : nullptr; off += al256(bytes); return q; };
     w->slot_floats = (size_t)g.NT * TM * g.H;                       // one [rows x H] fp32 array in the row-slot layout
     const size_t lsz = (size_t)g.T * w->slot_floats * 4;
-    w->himg_bytes = (size_t)g.T * g.NT * g.HC * CHUNK;
-    w->gimg_bytes = (size_t)g.T * g.NT * g.GC * CHUNK;
+    w->himg_bytes = (size_t)g.T * g.NT * g.HC * WCHUNK;
+    w->gimg_bytes = (size_t)g.T * g.NT * g.UG * WCHUNK;
     w->bits_words = (size_t)g.T * g.N * g.UG;
     w->pack_stride = pack_layout(g, g.L > 1 ? 1 : 0).total;
     w->splits = wgrad_splits(g);
     w->himg = take(w->himg_bytes * g.L);
     w->xmask = take(w->himg_bytes * (g.L > 1 ? g.L - 1 : 0));
-    w->x0img = take((size_t)g.T * g.NT * CHUNK);
+    w->x0img = take((size_t)g.T * g.NT * WCHUNK);
     w->gimg = take(w->gimg_bytes * g.L);
     w->bits = (uint32_t*)take(w->bits_words * 4 * (g.L > 1 ? g.L - 1 : 0));
     w->cst = (float*)take(lsz * g.L);
@@ -786,7 +803,7 @@ void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
     w->dc = (float*)take(w->slot_floats * 4);
     w->part = (float*)take((size_t)w->splits * 4 * g.H * (2 * g.H) * 4);
     w->bsum = (float*)take((size_t)g.NT * g.UG * 128 * 4);
-    w->zero = take(CHUNK);
+    w->zero = take(WCHUNK);
     w->pack = take(w->pack_stride * g.L);
     w->total = off;
 }
@@ -838,8 +855,8 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
     const int64_t NH = N * H, lsz = (int64_t)T * NH;
     int rc = opt_in_smem(w2_fwd_kernel, FwdSmem::total, "w2_fwd_kernel smem");
     if (rc) return rc;
-    B200_CUDA(cudaMemsetAsync(w.zero, 0, CHUNK, st));
-    { TimedLaunch _t("w2_x0_kernel", st); w2_x0_kernel<<<ew_grid2((int64_t)T * g.NT * TM * 8), 256, 0, st>>>(x, N, T, F, g.NT, w.x0img); }
+    B200_CUDA(cudaMemsetAsync(w.zero, 0, WCHUNK, st));
+    { TimedLaunch _t("w2_x0_kernel", st); w2_x0_kernel<<<ew_grid2((int64_t)T * g.NT * TM * 16), 256, 0, st>>>(x, N, T, F, g.NT, w.x0img); }
     B200_LAUNCH_CHECK("w2_x0_kernel");
     for (int l = 0; l < L; ++l) {
         const LayerP lp = layer_p(params, F, H, l);
@@ -847,7 +864,7 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
         uint8_t* pk = w.pack + (size_t)l * w.pack_stride;
         const float in_scale = (l > 0 && drop) ? 1.0f / (1.0f - p) : 1.0f;
         { TimedLaunch _t("w2_pack_kernel", st);
-          w2_pack_kernel<<<128, 256, 0, st>>>(lp.w_ih, lp.w_hh, lp.b_ih, lp.b_hh, lp.in, H, g.xc(l), in_scale, pk + pl.wf, pk + pl.wd_h,
+          w2_pack_kernel<<<128, 256, 0, st>>>(lp.w_ih, lp.w_hh, lp.b_ih, lp.b_hh, lp.in, H, 2 * g.xc(l), in_scale, pk + pl.wf, pk + pl.wd_h,
                                               l > 0 ? pk + pl.wd_x : nullptr, (float*)(pk + pl.bias)); }
         B200_LAUNCH_CHECK("w2_pack_kernel");
         if (drop && l > 0) {
@@ -864,7 +881,7 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
         uint8_t* himg = w.himg + (size_t)l * w.himg_bytes;
         const bool mask_out = drop && l < L - 1;
         const uint8_t* xin = l == 0 ? w.x0img : (drop ? w.xmask + (size_t)(l - 1) * w.himg_bytes : w.himg + (size_t)(l - 1) * w.himg_bytes);
-        const size_t xstep = (size_t)g.NT * g.xc(l) * CHUNK, hstep = (size_t)g.NT * g.HC * CHUNK, gstep = (size_t)g.NT * g.GC * CHUNK;
+        const size_t xstep = (size_t)g.NT * g.xc(l) * WCHUNK, hstep = (size_t)g.NT * g.HC * WCHUNK, gstep = (size_t)g.NT * g.UG * WCHUNK;
         for (int t = 0; t < T; ++t) {
             FwdArgs a;
             a.wf = pk + pl.wf; a.bias = (const float*)(pk + pl.bias);
@@ -913,7 +930,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
     const bool top = l == L - 1;
     const float* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
     float* d_in = w.dx[(L - 1 - l) & 1];
-    const size_t gstep = (size_t)g.NT * g.GC * CHUNK;
+    const size_t gstep = (size_t)g.NT * g.UG * WCHUNK;
     const float in_scale = (l > 0 && drop) ? 1.0f / (1.0f - p) : 1.0f;
 
     B200_CUDA(cudaMemsetAsync(w.bsum, 0, (size_t)g.NT * g.UG * 128 * 4, st));
@@ -937,7 +954,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
         if (t > 0) d.part[d.np++] = 0;
         if (l > 0) d.part[d.np++] = 1;
         if (d.np == 1) d.part[1] = d.part[0];
-        d.N = N; d.NT = g.NT; d.GC = g.GC; d.H = H; d.UG = g.UG;
+        d.N = N; d.NT = g.NT; d.H = H; d.UG = g.UG;
         if (d.np > 0) {
             int grid = ((g.NT + 1) / 2) * d.np;
             if (grid > num_sms()) grid = num_sms();
@@ -951,14 +968,14 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
     wa.xsrc = l == 0 ? w.x0img : (drop ? w.xmask + (size_t)(l - 1) * w.himg_bytes : w.himg + (size_t)(l - 1) * w.himg_bytes);
     wa.hsrc = w.himg + (size_t)l * w.himg_bytes;
     wa.zero = w.zero; wa.part = w.part;
-    wa.T = T; wa.NT = g.NT; wa.GC = g.GC; wa.XC = g.xc(l); wa.HC = g.HC; wa.H = H;
+    wa.T = T; wa.NT = g.NT; wa.UG = g.UG; wa.XC = g.xc(l); wa.HC = g.HC; wa.H = H;
     wa.splits = w.splits;
     const int64_t ktot = (int64_t)T * g.NT * 2;
     wa.kps = (ktot + w.splits - 1) / w.splits;
     { TimedLaunch _t("w2_wgrad_kernel", st); w2_wgrad_kernel<<<(unsigned)((H / 64) * 2 * w.splits), W2_THREADS, WgSmem::total, st>>>(wa); }
     B200_LAUNCH_CHECK("w2_wgrad_kernel");
     { TimedLaunch _t("w2_wgrad_reduce_kernel", st);
-      w2_wgrad_reduce_kernel<<<ew_grid2(4LL * H * (lp.in + H)), 256, 0, st>>>(w.part, w.splits, H, g.xc(l), lp.in, in_scale, gw_ih, gw_hh); }
+      w2_wgrad_reduce_kernel<<<ew_grid2(4LL * H * (lp.in + H)), 256, 0, st>>>(w.part, w.splits, H, 2 * g.xc(l), lp.in, in_scale, gw_ih, gw_hh); }
     B200_LAUNCH_CHECK("w2_wgrad_reduce_kernel");
     { TimedLaunch _t("w2_bsum_reduce_kernel", st); w2_bsum_reduce_kernel<<<(unsigned)((4 * H + 255) / 256), 256, 0, st>>>(w.bsum, g.NT, g.UG, H, gb_ih, gb_hh); }
     B200_LAUNCH_CHECK("w2_bsum_reduce_kernel");
