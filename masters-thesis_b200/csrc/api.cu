@@ -86,6 +86,7 @@ int tc_hidden_states(int mode, int layer, int L, int64_t N, int T, const void* w
 // wide engine (lstm_wide.cu): hidden sizes other than 64 in the tensor-core modes
 size_t wide_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L);
 void wide_set_images(int on);
+void wide2_set_dbg(int v);
 bool wide_uses_images(int mode, int H, int F);
 int wide2_hidden_states(int layer, int F, int H, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st);
 int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
@@ -125,6 +126,7 @@ extern "C" int b200_set_option(const char* name, int value) {
     if (strcmp(name, "tc_fwd_eh") == 0) { tc_set_fwd_eh(value); return B200_OK; }
     if (strcmp(name, "wide_fuse") == 0) { wide_set_fuse(value); return B200_OK; }
     if (strcmp(name, "wide_images") == 0) { wide_set_images(value); return B200_OK; }
+    if (strcmp(name, "wide_dbg") == 0) { wide2_set_dbg(value); return B200_OK; }
     set_error("set_option: unknown option '%s' (known: tc_prefetch, tc_fwd_eh, tc_wgrad, tc_dgrad, wide_fuse, wide_images)", name);
     return B200_ERR_INVALID;
 }

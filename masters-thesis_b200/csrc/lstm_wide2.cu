@@ -16,8 +16,9 @@
 //   Gimg[l]  [T][NT][UG] chunks   activated gates (forward) -> pre-activation gradients dG (backward, in place); gate columns
 //                                 are permuted: g' = (u / 32) * 128 + gate * 32 + u % 32, so that the four gates of 32 hidden
 //                                 units are one chunk (one N tile of the forward GEMM, one M tile of the weight gradient)
-//   c, dc, dh, dx                  fp32 in the "row-slot" layout [tile][u / 8][128 rows][8]: the thread that owns a row (TMEM lane) moves
-//                                 32 bytes and a warp 1 KB of contiguous memory (row-major [N][H] costs 32 cache lines per warp access)
+//   c, dc (fp32), dh, dx (bf16)    in the "row-slot" layout [tile][u / 8][128 rows][8]: the thread that owns a row (TMEM lane) moves
+//                                 32 or 16 bytes and a warp 1 KB / 512 B of contiguous memory (row-major [N][H] costs 32 cache lines per
+//                                 warp access)
 //   Wf[l]    [UG][KC] images      [128 rows g' x 64] K-major (16 KB each) of [W_ih | W_hh], KC = 2 * ((1 or HC) + HC) K-chunks of 64
 //   Wd[l]    per part (h, x): [4H / 64][64 g' rows x H columns] MN-major images for dG . W
 //
@@ -42,7 +43,6 @@ namespace {
 constexpr int TM = 128;
 constexpr uint32_t CHUNK = 16384, RG_BYTES = 1024;          // weight image [128 x 64]
 constexpr uint32_t WCHUNK = 32768, WRG_BYTES = 2048;         // activation chunk [128 x 128]
-constexpr float LOG2E = 1.4426950408889634f;
 constexpr int W2_THREADS = 320;                 // 8 epilogue warps, loader warp, MMA warp
 
 __host__ __device__ inline size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
@@ -70,6 +70,11 @@ inline Geom make_geom(int64_t N, int T, int F, int H, int L) {
     g.HC = H / 128; g.UG = H / 32; g.GC = H / 16;
     return g;
 }
+
+// tanh on the XU pipe, one MUFU (relative error 2^-11: an eighth of the bf16 rounding the activations get when they are stored).
+// The bf16 mode computes sigma(x) = 0.5 + 0.5 tanh(x / 2) with it: 5 MUFU and ~11 FP32 operations per cell instead of the 7 and ~30 of
+// the exp2 / reciprocal form the fp32-accurate engines use -- the forward epilogue is XU-bound (ncu: XU 53 % busy, tensor pipe 31 %).
+__device__ __forceinline__ float tanha(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 __device__ __forceinline__ uint32_t pack_bf2(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
@@ -151,7 +156,7 @@ w2_pack_kernel(const float* __restrict__ w_ih, const float* __restrict__ w_hh, c
     for (int64_t gp = tid; gp < G4; gp += nthr) {
         const int ug = (int)gp >> 7, gate = ((int)gp >> 5) & 3, u = ug * 32 + ((int)gp & 31);
         const float b = b_ih[gate * H + u] + b_hh[gate * H + u];
-        biasp[gp] = gate == 2 ? 2.0f * LOG2E * b : -LOG2E * b;          // folded into the exponent argument
+        biasp[gp] = gate == 2 ? b : 0.5f * b;                           // sigma(a + b) = 0.5 + 0.5 tanh(0.5 a + 0.5 b)
     }
 }
 
@@ -216,16 +221,21 @@ w2_unpack_kernel(const uint8_t* __restrict__ himg, int64_t N, int T, int H, int 
 // One LSTM step of one layer for all rows.  CTA c owns unit group ug = c % UG (32 hidden units = 128 permuted gate columns, its
 // KC weight chunks stay in shared memory for the whole launch) and the row tiles m = c / UG, c / UG + gridDim.x / UG, ...
 // Per tile: XC + HC bulk copies of 32 KB bring [x_t | h_{t-1}], 8 MMAs each (M 128, N 128, K 16) accumulate the gates into one of four
-// TMEM slots, and one of two epilogue warp groups (alternating tiles) applies the cell and writes c_t, the activated gates and its
-// 32 columns of the h_t image.  Activations as in lstm_tc.cu: the bias is folded into the exponent argument, one reciprocal
-// serves i, f and g, one serves o and tanh(c).
+// TMEM slots, and one of three epilogue warp groups (taking tiles in turn) applies the cell and writes c_t, the activated gates and its
+// 32 columns of the h_t image.  Activations through tanh.approx (see tanha).
 struct FwdArgs {
     const uint8_t* wf; const float* bias;
     const uint8_t* xin; const uint8_t* hprev; uint8_t* hout; uint8_t* hmask; const uint32_t* keep;
     const float* c_prev; float* c_out; uint8_t* gates; float* h_last;
     int64_t N; int NT, XC, HC, UG, GC, H;
+    int dbg;       // timing experiments (option "wide_dbg", results are wrong when set): 1 = no cell math / stores, 2 = no operand loads
 };
 constexpr int FWD_NST = 3;
+constexpr int FWD_GROUPS = 3;                            // epilogue warp groups (4 warps each) taking the tiles of a CTA in turn
+constexpr int FWD_THREADS = (FWD_GROUPS * 4 + 2) * 32;
+#ifndef W2_PF_DIST
+#define W2_PF_DIST 2
+#endif
 constexpr uint32_t FWD_W_MAX = 8 * CHUNK;
 struct FwdSmem {
     static constexpr uint32_t off_w = 0, off_ring = FWD_W_MAX, off_bias = off_ring + FWD_NST * WCHUNK, off_bar = off_bias + 128 * 4;
@@ -233,7 +243,7 @@ struct FwdSmem {
     static constexpr uint32_t nbar = 2 * FWD_NST + 9, off_tmem = off_bar + nbar * 8, total = off_tmem + 16;
 };
 
-__global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
+__global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     using S = FwdSmem;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::off_bar);
@@ -254,28 +264,29 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
         mbar_init(w_ready, 1);
         fence_barrier_init();
     }
+    constexpr int LD_WARP = FWD_GROUPS * 4, MMA_WARP = LD_WARP + 1;
     if (threadIdx.x < 128) bias_s[threadIdx.x] = a.bias[ug * 128 + threadIdx.x];
-    if (warp == 9) tmem_alloc(tmem_slot, 512);
+    if (warp == MMA_WARP) tmem_alloc(tmem_slot, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 8) {
+    if (warp < LD_WARP) {
         // ================================ epilogue: LSTM cell of 32 units of one row ==========================
         const int grp = warp >> 2, lq = warp & 3, r = lq * 32 + lane;
         const uint32_t row_off = (uint32_t)(r >> 3) * WRG_BYTES + (uint32_t)(r & 7) * 16u;
         const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16);
         int i = 0;
         for (int m = first; m < a.NT; m += stride, ++i) {
-            if ((i & 1) != grp) continue;
+            if (i % FWD_GROUPS != grp) continue;
             const int slot = i & 3;
             const int64_t row = (int64_t)m * TM + r;
             const bool live = row < a.N;
             float cpv[4][8];                      // c_{t-1} of the row's 32 units, fetched while the MMAs of the tile run
 #pragma unroll
             for (int uc = 0; uc < 4; ++uc) {
-                if (a.c_prev != nullptr) ld8(a.c_prev + slot_off(m, ug * 4 + uc, r, a.H), cpv[uc]);
+                if (a.c_prev != nullptr && !(a.dbg & 1)) ld8(a.c_prev + slot_off(m, ug * 4 + uc, r, a.H), cpv[uc]);
                 else {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) cpv[uc][j] = 0.f;
@@ -291,6 +302,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             if (mdst != nullptr && live) keep = a.keep[row * a.UG + ug];
 #pragma unroll
             for (int uc = 0; uc < 4; ++uc) {
+                if (a.dbg & 1) break;
                 float ai[8], af[8], ag[8], ao[8];
                 const float (&cp)[8] = cpv[uc];
                 const uint32_t col = tl + (uint32_t)(slot * 128 + uc * 8);
@@ -303,19 +315,14 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int u = uc * 8 + j;
-                    const float Ei = ex2a(fminf(fmaf(ai[j], -LOG2E, bias_s[0 * 32 + u]), EXP_CLAMP));
-                    const float Ef = ex2a(fminf(fmaf(af[j], -LOG2E, bias_s[1 * 32 + u]), EXP_CLAMP));
-                    const float Eg = ex2a(fminf(fmaf(ag[j], 2.f * LOG2E, bias_s[2 * 32 + u]), EXP_CLAMP));
-                    const float Eo = ex2a(fminf(fmaf(ao[j], -LOG2E, bias_s[3 * 32 + u]), EXP_CLAMP));
-                    const float Di = 1.f + Ei, Df = 1.f + Ef, Dg = 1.f + Eg, Do = 1.f + Eo;
-                    const float r1 = rcpa(Di * Df * Dg);
-                    const float gi = r1 * Df * Dg, gf = r1 * Di * Dg, gg = (Eg - 1.f) * (r1 * Di * Df);
+                    const float gi = fmaf(tanha(fmaf(ai[j], 0.5f, bias_s[0 * 32 + u])), 0.5f, 0.5f);
+                    const float gf = fmaf(tanha(fmaf(af[j], 0.5f, bias_s[1 * 32 + u])), 0.5f, 0.5f);
+                    const float gg = tanha(ag[j] + bias_s[2 * 32 + u]);
+                    const float go = fmaf(tanha(fmaf(ao[j], 0.5f, bias_s[3 * 32 + u])), 0.5f, 0.5f);
                     const float c = fmaf(gf, cp[j], gi * gg);
-                    const float Ec = ex2a(fminf(2.f * LOG2E * c, EXP_CLAMP));
-                    const float r2 = rcpa(Do * (Ec + 1.f));
-                    ai[j] = gi; af[j] = gf; ag[j] = gg; ao[j] = r2 * (Ec + 1.f);
+                    ai[j] = gi; af[j] = gf; ag[j] = gg; ao[j] = go;
                     cv[j] = c;
-                    hv[j] = (Ec - 1.f) * r2;
+                    hv[j] = go * tanha(c);
                 }
                 // activated gates: chunk ug, 16-byte slot gate * 4 + uc of this row
                 *reinterpret_cast<uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u) = pack_bf8(ai);
@@ -332,17 +339,23 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_free[slot]);
         }
-    } else if (warp == 8) {
+    } else if (warp == LD_WARP) {
         // ================================ loader ================================================================
         if (lane == 0) {
             mbar_arrive_expect_tx(w_ready, (uint32_t)KC * CHUNK);
             for (int kc = 0; kc < KC; ++kc) bulk_copy_g2s(smem + S::off_w + kc * CHUNK, a.wf + ((size_t)ug * KC + kc) * CHUNK, CHUNK, w_ready);
             uint32_t q = 0;
             for (int m = first; m < a.NT; m += stride) {
+                const int mp = m + W2_PF_DIST * stride;          // L2 prefetch: the layer input of a later tile comes from HBM
+                if (W2_PF_DIST > 0 && mp < a.NT) {
+                    if (ug < 2 * a.XC) prefetch_l2(a.xin + ((size_t)mp * a.XC + (ug >> 1)) * WCHUNK + (size_t)(ug & 1) * (WCHUNK / 2), WCHUNK / 2);
+                    if (a.c_prev != nullptr) prefetch_l2(a.c_prev + slot_off(mp, ug * 4, 0, a.H), 16384);
+                }
                 for (int kc = 0; kc < nk; ++kc, ++q) {
                     const uint32_t st = q % FWD_NST;
                     if (q >= FWD_NST) mbar_wait(&empty[st], ((q / FWD_NST) - 1) & 1);
                     const uint8_t* src = kc < a.XC ? a.xin + ((size_t)m * a.XC + kc) * WCHUNK : a.hprev + ((size_t)m * a.HC + (kc - a.XC)) * WCHUNK;
+                    if (a.dbg & 2) { mbar_arrive(&full[st]); continue; }
                     mbar_arrive_expect_tx(&full[st], WCHUNK);
                     bulk_copy_g2s(smem + S::off_ring + st * WCHUNK, src, WCHUNK, &full[st]);
                 }
@@ -380,7 +393,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) tmem_dealloc(tmem_base, 512);
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 512);
 }
 
 
@@ -389,7 +402,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
 // (in place), c_{t-1}, the incoming dh (recurrent + from the layer above + from the heads) and dc; writes dG (pre-activation
 // gradients, bf16, rows >= N zero), dc_{t-1}, and adds the tile's column sums of dG (the bias gradient) to its own slot of bsum.
 struct CellArgs {
-    uint8_t* G; const float* c_prev; const float* dh_rec; const float* d_out; const float* dhT; float* dc; float* bsum;
+    uint8_t* G; const float* c_prev; const uint4* dh_rec; const uint4* d_out; const float* dhT; float* dc; float* bsum;
     int first; int64_t N; int UG, GC, H;
 };
 
@@ -420,9 +433,9 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
         {
             float t8[8];
             if (a.c_prev) ld8(a.c_prev + e, cp);
-            if (a.dh_rec) ld8(a.dh_rec + e, dh);
+            if (a.dh_rec) unpack_bf8(a.dh_rec[e >> 3], dh);
             if (a.d_out) {
-                ld8(a.d_out + e, t8);
+                unpack_bf8(a.d_out[e >> 3], t8);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) dh[j] += t8[j];
             }
@@ -436,8 +449,7 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float c = fmaf(gf[j], cp[j], gi[j] * gg[j]);
-            const float Ec = ex2a(fminf(2.f * LOG2E * c, EXP_CLAMP));
-            const float tc = 1.f - 2.f * rcpa(Ec + 1.f);
+            const float tc = tanha(c);
             const float dct = live ? fmaf(dh[j] * go[j], 1.f - tc * tc, dc[j]) : 0.f;
             const float d_o = live ? dh[j] * tc : 0.f;
             v[0 * 8 + j] = dct * gg[j] * gi[j] * (1.f - gi[j]);
@@ -498,9 +510,10 @@ w2_bsum_reduce_kernel(const float* __restrict__ bsum, int NT, int UG, int H, flo
 // of the tiles arrive with one 32 KB bulk copy each (A ring, 2 slots of 64 KB); the matching [64 x H] halves of the weight image
 // arrive separately (B ring, 3 slots of 32 KB); 8 MMAs per half (M 128, N = H, B read MN-major) feed two TMEM accumulators.
 struct DgradArgs {
-    const uint8_t* dG; const uint8_t* wd[2]; float* out[2]; const uint32_t* keep;
+    const uint8_t* dG; const uint8_t* wd[2]; uint4* out[2]; const uint32_t* keep;
     int np; int part[2];
     int64_t N; int NT, H, UG;
+    int dbg;       // 1 = no epilogue stores, 2 = no operand loads, 4 = no weight loads only
 };
 constexpr int DG_NSA = 2, DG_NSB = 3;
 struct DgSmem {
@@ -545,7 +558,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
             const int64_t row = (int64_t)m * TM + r;
             mbar_wait(acc_full, (uint32_t)(i & 1));
             tc_fence_after();
-            if (m < a.NT) {
+            if (m < a.NT && !(a.dbg & 1)) {
                 const bool masked = p == 1 && a.keep != nullptr && row < a.N;
                 for (int c0 = 0; c0 < a.H; c0 += 32) {
                     float v[4][8];
@@ -555,11 +568,8 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
                     if (masked) kw = a.keep[row * a.UG + (c0 >> 5)];
                     tmem_ld_wait();
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) if (!((kw >> (k * 8 + q)) & 1u)) v[k][q] = 0.f;
-                        st8(a.out[p] + slot_off(m, (c0 >> 3) + k, r, a.H), v[k]);
-                    }
+                    for (int k = 0; k < 4; ++k)          // bf16, one 16-byte slot per (row, octet): a warp store is 512 contiguous bytes
+                        a.out[p][slot_off(m, (c0 >> 3) + k, r, a.H) >> 3] = and_mask8(pack_bf8(v[k]), (kw >> (k * 8)) & 0xFFu);
                 }
             }
             tc_fence_before();
@@ -576,12 +586,16 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
                     const uint32_t sa = qa % DG_NSA;
                     if (qa >= DG_NSA) mbar_wait(&emptyA[sa], ((qa / DG_NSA) - 1) & 1);
                     uint8_t* da = smem + sa * 2 * WCHUNK;
-                    mbar_arrive_expect_tx(&fullA[sa], (two ? 2u : 1u) * WCHUNK);
-                    bulk_copy_g2s(da, a.dG + ((size_t)m0 * a.UG + ug) * WCHUNK, WCHUNK, &fullA[sa]);
-                    if (two) bulk_copy_g2s(da + WCHUNK, a.dG + ((size_t)(m0 + 1) * a.UG + ug) * WCHUNK, WCHUNK, &fullA[sa]);
+                    if (a.dbg & 2) mbar_arrive(&fullA[sa]);
+                    else {
+                        mbar_arrive_expect_tx(&fullA[sa], (two ? 2u : 1u) * WCHUNK);
+                        bulk_copy_g2s(da, a.dG + ((size_t)m0 * a.UG + ug) * WCHUNK, WCHUNK, &fullA[sa]);
+                        if (two) bulk_copy_g2s(da + WCHUNK, a.dG + ((size_t)(m0 + 1) * a.UG + ug) * WCHUNK, WCHUNK, &fullA[sa]);
+                    }
                     for (int half = 0; half < 2; ++half, ++qb) {
                         const uint32_t sb = qb % DG_NSB;
                         if (qb >= DG_NSB) mbar_wait(&emptyB[sb], ((qb / DG_NSB) - 1) & 1);
+                        if (a.dbg & 6) { mbar_arrive(&fullB[sb]); continue; }
                         mbar_arrive_expect_tx(&fullB[sb], b_bytes);
                         bulk_copy_g2s(smem + S::off_b + sb * WCHUNK, a.wd[p] + (size_t)(ug * 2 + half) * b_bytes, b_bytes, &fullB[sb]);
                     }
@@ -768,7 +782,8 @@ w2_wgrad_reduce_kernel(const float* __restrict__ part, int splits, int H, int XC
 struct W2Ws {
     uint8_t *himg, *xmask, *x0img, *gimg, *zero, *pack;
     uint32_t* bits;
-    float *cst, *dx[2], *dh_rec, *dc, *part, *bsum;
+    float *cst, *dc, *part, *bsum;
+    uint4 *dx[2], *dh_rec;
     size_t himg_bytes, gimg_bytes, bits_words, pack_stride, slot_floats, total;
     int splits;
 };
@@ -797,9 +812,9 @@ void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
     w->gimg = take(w->gimg_bytes * g.L);
     w->bits = (uint32_t*)take(w->bits_words * 4 * (g.L > 1 ? g.L - 1 : 0));
     w->cst = (float*)take(lsz * g.L);
-    w->dx[0] = (float*)take(g.L > 1 ? lsz : 0);
-    w->dx[1] = (float*)take(g.L > 2 ? lsz : 0);
-    w->dh_rec = (float*)take(w->slot_floats * 4);
+    w->dx[0] = (uint4*)take(g.L > 1 ? lsz / 2 : 0);
+    w->dx[1] = (uint4*)take(g.L > 2 ? lsz / 2 : 0);
+    w->dh_rec = (uint4*)take(w->slot_floats * 2);
     w->dc = (float*)take(w->slot_floats * 4);
     w->part = (float*)take((size_t)w->splits * 4 * g.H * (2 * g.H) * 4);
     w->bsum = (float*)take((size_t)g.NT * g.UG * 128 * 4);
@@ -834,6 +849,9 @@ int opt_in_smem(K kernel, uint32_t bytes, const char* who) {
 }
 
 }  // namespace
+
+static int g_w2_dbg = 0;
+void wide2_set_dbg(int v) { g_w2_dbg = v; }
 
 bool wide2_supported(int H, int F) { return (H == 128 || H == 256) && F >= 1 && F <= 63; }
 
@@ -894,8 +912,8 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
             a.c_out = w.cst + ((size_t)l * T + t) * w.slot_floats;
             a.gates = w.gimg + (size_t)l * w.gimg_bytes + (size_t)t * gstep;
             a.h_last = (l == L - 1 && t == T - 1) ? stash_h + (int64_t)l * lsz + (int64_t)t * NH : nullptr;
-            a.N = N; a.NT = g.NT; a.XC = g.xc(l); a.HC = g.HC; a.UG = g.UG; a.GC = g.GC; a.H = H;
-            { TimedLaunch _t("w2_fwd_kernel", st); w2_fwd_kernel<<<(unsigned)(lanes * g.UG), W2_THREADS, FwdSmem::total, st>>>(a); }
+            a.N = N; a.NT = g.NT; a.XC = g.xc(l); a.HC = g.HC; a.UG = g.UG; a.GC = g.GC; a.H = H; a.dbg = g_w2_dbg;
+            { TimedLaunch _t("w2_fwd_kernel", st); w2_fwd_kernel<<<(unsigned)(lanes * g.UG), FWD_THREADS, FwdSmem::total, st>>>(a); }
             B200_LAUNCH_CHECK("w2_fwd_kernel");
         }
     }
@@ -928,8 +946,9 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
     uint8_t* gimg = w.gimg + (size_t)l * w.gimg_bytes;
     const float* cs = w.cst + (size_t)l * T * w.slot_floats;
     const bool top = l == L - 1;
-    const float* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
-    float* d_in = w.dx[(L - 1 - l) & 1];
+    const uint4* d_out = top ? nullptr : w.dx[((L - 1 - l) & 1) ^ 1];        // written by layer l + 1
+    uint4* d_in = w.dx[(L - 1 - l) & 1];
+    const size_t slot16 = w.slot_floats / 8;                                   // 16-byte slots of one [rows x H] bf16 array
     const size_t gstep = (size_t)g.NT * g.UG * WCHUNK;
     const float in_scale = (l > 0 && drop) ? 1.0f / (1.0f - p) : 1.0f;
 
@@ -940,7 +959,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
         c.G = gimg + (size_t)t * gstep;
         c.c_prev = t > 0 ? cs + (size_t)(t - 1) * w.slot_floats : nullptr;
         c.dh_rec = t < T - 1 ? w.dh_rec : nullptr;
-        c.d_out = d_out ? d_out + (size_t)t * w.slot_floats : nullptr;
+        c.d_out = d_out ? d_out + (size_t)t * slot16 : nullptr;
         c.dhT = (top && t == T - 1) ? dhT : nullptr;
         c.dc = w.dc; c.bsum = w.bsum; c.first = t == T - 1 ? 1 : 0;
         c.N = N; c.UG = g.UG; c.GC = g.GC; c.H = H;
@@ -948,13 +967,13 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
         B200_LAUNCH_CHECK("w2_cell_bwd_kernel");
         DgradArgs d;
         d.dG = c.G; d.wd[0] = pk + pl.wd_h; d.wd[1] = l > 0 ? pk + pl.wd_x : nullptr;
-        d.out[0] = w.dh_rec; d.out[1] = l > 0 ? d_in + (size_t)t * w.slot_floats : nullptr;
+        d.out[0] = w.dh_rec; d.out[1] = l > 0 ? d_in + (size_t)t * slot16 : nullptr;
         d.keep = (drop && l > 0) ? w.bits + (size_t)(l - 1) * w.bits_words + (size_t)t * N * g.UG : nullptr;
         d.np = 0;
         if (t > 0) d.part[d.np++] = 0;
         if (l > 0) d.part[d.np++] = 1;
         if (d.np == 1) d.part[1] = d.part[0];
-        d.N = N; d.NT = g.NT; d.H = H; d.UG = g.UG;
+        d.N = N; d.NT = g.NT; d.H = H; d.UG = g.UG; d.dbg = g_w2_dbg;
         if (d.np > 0) {
             int grid = ((g.NT + 1) / 2) * d.np;
             if (grid > num_sms()) grid = num_sms();
