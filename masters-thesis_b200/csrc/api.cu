@@ -87,6 +87,7 @@ int tc_hidden_states(int mode, int layer, int L, int64_t N, int T, const void* w
 size_t wide_workspace_bytes(int mode, int64_t N, int T, int F, int H, int L);
 void wide_set_images(int on);
 void wide2_set_dbg(int v);
+void wide2_set_mc(int v);
 bool wide_uses_images(int mode, int H, int F);
 int wide2_hidden_states(int layer, int F, int H, int L, int64_t N, int T, const void* workspace, size_t ws_bytes, float* out, cudaStream_t st);
 int wide_fwd(int mode, const float* params, int F, int H, int L, const float* x, int64_t N, int T, float* stash_h,
@@ -127,6 +128,7 @@ extern "C" int b200_set_option(const char* name, int value) {
     if (strcmp(name, "wide_fuse") == 0) { wide_set_fuse(value); return B200_OK; }
     if (strcmp(name, "wide_images") == 0) { wide_set_images(value); return B200_OK; }
     if (strcmp(name, "wide_dbg") == 0) { wide2_set_dbg(value); return B200_OK; }
+    if (strcmp(name, "wide_mc") == 0) { wide2_set_mc(value); return B200_OK; }
     set_error("set_option: unknown option '%s' (known: tc_prefetch, tc_fwd_eh, tc_wgrad, tc_dgrad, wide_fuse, wide_images)", name);
     return B200_ERR_INVALID;
 }

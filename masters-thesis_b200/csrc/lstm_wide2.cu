@@ -71,6 +71,21 @@ inline Geom make_geom(int64_t N, int T, int F, int H, int L) {
     return g;
 }
 
+// ---- two-CTA cluster helpers (forward kernel, MC variant).  The multicast copies read the activation images of THIS GPU's
+// workspace only: TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+// memory hung the GPU.
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s_mc(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar, uint16_t mask) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "h"(mask)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+
 // tanh on the XU pipe, one MUFU (relative error 2^-11: an eighth of the bf16 rounding the activations get when they are stored).
 // The bf16 mode computes sigma(x) = 0.5 + 0.5 tanh(x / 2) with it: 5 MUFU and ~11 FP32 operations per cell instead of the 7 and ~30 of
 // the exp2 / reciprocal form the fp32-accurate engines use -- the forward epilogue is XU-bound (ncu: XU 53 % busy, tensor pipe 31 %).
@@ -228,7 +243,8 @@ struct FwdArgs {
     const uint8_t* xin; const uint8_t* hprev; uint8_t* hout; uint8_t* hmask; const uint32_t* keep;
     const float* c_prev; float* c_out; uint8_t* gates; float* h_last;
     int64_t N; int NT, XC, HC, UG, GC, H;
-    int dbg;       // timing experiments (option "wide_dbg", results are wrong when set): 1 = no cell math / stores, 2 = no operand loads
+    int dbg;       // timing experiments (option "wide_dbg", results are wrong when set): 1 = no cell math / stores, 2 = no operand loads,
+                   // 8 = cell math but no stores, 16 = no c_{t-1} loads
 };
 constexpr int FWD_NST = 3;
 constexpr int FWD_GROUPS = 3;                            // epilogue warp groups (4 warps each) taking the tiles of a CTA in turn
@@ -243,6 +259,10 @@ struct FwdSmem {
     static constexpr uint32_t nbar = 2 * FWD_NST + 9, off_tmem = off_bar + nbar * 8, total = off_tmem + 16;
 };
 
+// MC: launched as clusters of two CTAs = two unit groups that walk the same row tiles.  Each CTA fetches one 64-row half (16 KB) of
+// every activation chunk and multicasts it into both CTAs' rings, so that a chunk crosses the L2 -> SM path once per CTA pair; a
+// stage is released when the MMAs of BOTH CTAs have read it (multicast tcgen05.commit on the `empty` barriers, count 2).
+template <bool MC>
 __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     using S = FwdSmem;
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -259,16 +279,18 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     const int nk = a.hprev ? a.XC + a.HC : a.XC;        // activation chunks per tile; t = 0: h_{-1} = 0, the recurrent ones are skipped
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < FWD_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < FWD_NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], MC ? 2 : 1); }
         for (int i = 0; i < 4; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 4); }
         mbar_init(w_ready, 1);
         fence_barrier_init();
     }
     constexpr int LD_WARP = FWD_GROUPS * 4, MMA_WARP = LD_WARP + 1;
+    const uint32_t crank = MC ? (blockIdx.x & 1u) : 0u;         // rank in the CTA pair (cluster dims 2 x 1 x 1)
     if (threadIdx.x < 128) bias_s[threadIdx.x] = a.bias[ug * 128 + threadIdx.x];
     if (warp == MMA_WARP) tmem_alloc(tmem_slot, 512);
     tc_fence_before();
     __syncthreads();
+    if (MC) cluster_sync_all();                                 // the peer's barriers exist before anything is sent to them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -286,7 +308,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             float cpv[4][8];                      // c_{t-1} of the row's 32 units, fetched while the MMAs of the tile run
 #pragma unroll
             for (int uc = 0; uc < 4; ++uc) {
-                if (a.c_prev != nullptr && !(a.dbg & 1)) ld8(a.c_prev + slot_off(m, ug * 4 + uc, r, a.H), cpv[uc]);
+                if (a.c_prev != nullptr && !(a.dbg & 17)) ld8(a.c_prev + slot_off(m, ug * 4 + uc, r, a.H), cpv[uc]);
                 else {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) cpv[uc][j] = 0.f;
@@ -324,6 +346,10 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     cv[j] = c;
                     hv[j] = go * tanha(c);
                 }
+                if (a.dbg & 8) {        // keep the math alive without storing anything (the condition never holds)
+                    if (cv[0] == 123.456f && hv[1] == ai[2] + af[3] + ag[4] + ao[5]) a.c_out[0] = 1.f;
+                    continue;
+                }
                 // activated gates: chunk ug, 16-byte slot gate * 4 + uc of this row
                 *reinterpret_cast<uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u) = pack_bf8(ai);
                 *reinterpret_cast<uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u) = pack_bf8(af);
@@ -357,7 +383,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     const uint8_t* src = kc < a.XC ? a.xin + ((size_t)m * a.XC + kc) * WCHUNK : a.hprev + ((size_t)m * a.HC + (kc - a.XC)) * WCHUNK;
                     if (a.dbg & 2) { mbar_arrive(&full[st]); continue; }
                     mbar_arrive_expect_tx(&full[st], WCHUNK);
-                    bulk_copy_g2s(smem + S::off_ring + st * WCHUNK, src, WCHUNK, &full[st]);
+                    if (MC) bulk_copy_g2s_mc(smem + S::off_ring + st * WCHUNK + crank * (WCHUNK / 2), src + crank * (WCHUNK / 2), WCHUNK / 2, &full[st], (uint16_t)3);
+                    else bulk_copy_g2s(smem + S::off_ring + st * WCHUNK, src, WCHUNK, &full[st]);
                 }
             }
         }
@@ -384,7 +411,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     for (int ks = 0; ks < 8; ++ks)          // two K = 64 halves of the activation chunk, one weight image each
                         umma_bf16(d, make_desc(aa + (ks >> 2) * 1024 + (ks & 3) * 256, LBO_BYTES, WRG_BYTES),
                                   make_desc(bb + (ks >> 2) * CHUNK + (ks & 3) * 256, LBO_BYTES, RG_BYTES), idesc, (kc > 0 || ks > 0) ? 1u : 0u);
-                    umma_commit(&empty[st]);
+                    if (MC) umma_commit_mc(&empty[st], (uint16_t)3); else umma_commit(&empty[st]);
                 }
                 umma_commit(&acc_full[slot]);
             }
@@ -393,6 +420,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
     }
     tc_fence_before();
     __syncthreads();
+    if (MC) cluster_sync_all();                                 // no CTA leaves while its peer may still signal its barriers
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, 512);
 }
 
@@ -852,6 +880,8 @@ int opt_in_smem(K kernel, uint32_t bytes, const char* who) {
 
 static int g_w2_dbg = 0;
 void wide2_set_dbg(int v) { g_w2_dbg = v; }
+static int g_w2_mc = 0;               // option "wide_mc": forward kernel as two-CTA clusters with multicast activation loads
+void wide2_set_mc(int v) { g_w2_mc = v; }
 
 bool wide2_supported(int H, int F) { return (H == 128 || H == 256) && F >= 1 && F <= 63; }
 
@@ -871,8 +901,11 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
     B200_CHECK_ARG(workspace != nullptr && w.total <= ws_bytes, "lstm_fwd (wide, bf16): workspace too small (%zu bytes, need %zu)", ws_bytes, w.total);
     const bool drop = training && p > 0.f && L > 1;
     const int64_t NH = N * H, lsz = (int64_t)T * NH;
-    int rc = opt_in_smem(w2_fwd_kernel, FwdSmem::total, "w2_fwd_kernel smem");
+    int rc = opt_in_smem(w2_fwd_kernel<false>, FwdSmem::total, "w2_fwd_kernel smem");
     if (rc) return rc;
+    rc = opt_in_smem(w2_fwd_kernel<true>, FwdSmem::total, "w2_fwd_kernel smem");
+    if (rc) return rc;
+    const bool mc = g_w2_mc != 0 && !(g_w2_dbg & 2);
     B200_CUDA(cudaMemsetAsync(w.zero, 0, WCHUNK, st));
     { TimedLaunch _t("w2_x0_kernel", st); w2_x0_kernel<<<ew_grid2((int64_t)T * g.NT * TM * 16), 256, 0, st>>>(x, N, T, F, g.NT, w.x0img); }
     B200_LAUNCH_CHECK("w2_x0_kernel");
@@ -913,7 +946,19 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
             a.gates = w.gimg + (size_t)l * w.gimg_bytes + (size_t)t * gstep;
             a.h_last = (l == L - 1 && t == T - 1) ? stash_h + (int64_t)l * lsz + (int64_t)t * NH : nullptr;
             a.N = N; a.NT = g.NT; a.XC = g.xc(l); a.HC = g.HC; a.UG = g.UG; a.GC = g.GC; a.H = H; a.dbg = g_w2_dbg;
-            { TimedLaunch _t("w2_fwd_kernel", st); w2_fwd_kernel<<<(unsigned)(lanes * g.UG), FWD_THREADS, FwdSmem::total, st>>>(a); }
+            if (mc) {
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3((unsigned)(lanes * g.UG)); cfg.blockDim = dim3(FWD_THREADS); cfg.dynamicSmemBytes = FwdSmem::total; cfg.stream = st;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                TimedLaunch _t("w2_fwd_kernel", st);
+                B200_CUDA(cudaLaunchKernelEx(&cfg, w2_fwd_kernel<true>, a));
+            } else {
+                TimedLaunch _t("w2_fwd_kernel", st);
+                w2_fwd_kernel<false><<<(unsigned)(lanes * g.UG), FWD_THREADS, FwdSmem::total, st>>>(a);
+            }
             B200_LAUNCH_CHECK("w2_fwd_kernel");
         }
     }

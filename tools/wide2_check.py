@@ -1,7 +1,7 @@
 """Bring-up check of the bf16 wide engine (csrc/lstm_wide2.cu): hidden states of every layer, loss and per-tensor gradients of
 B200_MODE_TC_FAST against B200_MODE_TC_PRECISE (the fp32-storage engine, itself gated against the oracle) on the golden batches.
 
-    python tools/wide2_check.py [H] [layers] [dropout] [windows]
+    python tools/wide2_check.py [H] [layers] [dropout] [windows] [option=value ...]
 """
 import json
 import sys
@@ -22,6 +22,9 @@ def main():
     layers = int(sys.argv[2]) if len(sys.argv) > 2 else 2
     p = float(sys.argv[3]) if len(sys.argv) > 3 else 0.0
     nwin = int(sys.argv[4]) if len(sys.argv) > 4 else 2
+    for o in sys.argv[5:]:                      # library options name=value (b200_set_option)
+        k, v = o.split("=")
+        assert B._lib.load().b200_set_option(k.encode(), int(v)) == 0, o
     data = golden_batches(ROOT / "tests" / "golden")
     torch.manual_seed(4)
     m = O.OracleLstm(3, H, layers, 0.0)
