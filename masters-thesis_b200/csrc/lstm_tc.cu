@@ -1085,25 +1085,29 @@ lstm_tc_bwd_kernel(const uint8_t* __restrict__ packed, const float* __restrict__
                 const int buf = (int)(g % XB);
                 uint8_t* xh_hi = smem + S::off_xh + (buf * NSPLIT) * S::XHB;
                 uint8_t* xh_lo = xh_hi + S::XHB;
-                if ((!LAYER0 || ISSUER_C) && lw != 0) continue;
+                if (LAYER0 && ISSUER_C && lw != 0) continue;
                 if (g >= XB) mbar_wait(&xh_free[buf], (uint32_t)(((g / XB) - 1) & 1));
                 if (tracer) trace_ev(1, 1, 0, g, ntr);
-                if (lw == 0) {
-                    if (lane == 0) mbar_arrive_expect_tx(&xh_full[buf], XH_TX);
+                {
+                    // lane = (image half: hi | lo, row group).  A warp's bulk copies are issued one lane after the other (UBLKCP is a
+                    // uniform-datapath instruction, ~60 clk each), so the two loader warps share them: warp 0 the h_{t-1} slices,
+                    // warp 1 (layers > 0) the x_t slices.  The barrier phase cannot complete before warp 0's expect_tx arrival.
+                    if (lw == 0 && lane == 0) mbar_arrive_expect_tx(&xh_full[buf], XH_TX);
                     __syncwarp();
-                    // lane = (image half: hi | lo, row group): every lane issues the h slice and (layers > 0) the x slice of its row group
                     const int rg16 = lane & 15, part = lane >> 4;
                     if (part < NSPLIT) {
                         const uint32_t so = (uint32_t)part * IMG_HALF + (uint32_t)rg16 * 1024u;
-                        const uint8_t* hsrc = (t > 0 ? himg + img_off(t - 1, tile, ntiles) : zero_blk) + so;
-                        uint8_t* dh_ = xh_hi + (uint32_t)part * S::XHB + (uint32_t)rg16 * SBO_W + (uint32_t)(KX / 8) * LBO_BYTES;
-                        bulk_copy_g2s(dh_, hsrc, 1024u, &xh_full[buf]);
-                        if (!LAYER0) {
+                        if (lw == 0) {
+                            const uint8_t* hsrc = (t > 0 ? himg + img_off(t - 1, tile, ntiles) : zero_blk) + so;
+                            uint8_t* dh_ = xh_hi + (uint32_t)part * S::XHB + (uint32_t)rg16 * SBO_W + (uint32_t)(KX / 8) * LBO_BYTES;
+                            bulk_copy_g2s(dh_, hsrc, 1024u, &xh_full[buf]);
+                        } else if (!LAYER0) {
                             const uint8_t* xsrc = ximg_in + img_off(t, tile, ntiles) + so;
                             bulk_copy_g2s(xh_hi + (uint32_t)part * S::XHB + (uint32_t)rg16 * SBO_W, xsrc, 1024u, &xh_full[buf]);
                         }
                     }
                 }
+                if (!LAYER0 && lw != 0) continue;
                 if (LAYER0 && ISSUER_C && kin == 3 && rows_live >= TM && (N & 3) == 0) {
                     // x part, whole tile, three features: the tile's 128 rows x 3 floats are 1,536 contiguous, 16-byte aligned bytes --
                     // three 128-bit loads per lane bring rows 4 lane .. 4 lane + 3; each row becomes one 16-byte slot
