@@ -151,7 +151,9 @@ B200_API int b200_dropout_mask(uint64_t seed, int layer, int64_t n_seq, int T, i
  * workspace: at least b200_lstm_workspace_bytes(...) bytes, shared by fwd and bwd calls of a step.  In the tcgen05 modes
  * the forward pass leaves state in it that the backward pass of the same step reads (hidden-state operand images, dropout
  * keep bits): pass the SAME pointer and size, untouched in between, with the same dropout_p / dropout_seed / training.
- * A backward launch that finds keep bits of another step (seed, layer or size mismatch) aborts (CUDA launch failure). */
+ * A backward launch that finds keep bits of another step (seed, layer or size mismatch) aborts (CUDA launch failure); so does a
+ * backward launch of the bf16 wide engine whose workspace was not filled by a forward pass with the same N, T, layers, hidden size,
+ * dropout and seed.  The workspace must be memory of the GPU the kernels run on. */
 B200_API size_t b200_lstm_workspace_bytes(int mode, int64_t n_seq, int T, int n_features, int hidden, int layers);
 B200_API int b200_lstm_fwd(int mode, const float* params, int n_features, int hidden, int layers,
                   const float* x, int64_t n_seq, int T, float* stash_h, float* stash_c,

@@ -214,6 +214,22 @@ w2_bits_kernel(uint64_t seed, int layer, int64_t N, int T, int UG, float p, uint
     }
 }
 
+// The backward pass reads what the forward pass left in the workspace (gates, images, cell state, keep bits, packed weights).  The
+// forward writes a 32-byte tag {magic, seed if dropout is on, N, T | L | H | dropout threshold}; every backward launch checks it against
+// its own arguments and aborts (trap) on a foreign, reused or differently sized workspace instead of producing gradients from stale data.
+struct W2Tag { uint64_t v[4]; };
+inline W2Tag make_tag(uint64_t seed, bool drop, float p, int64_t N, int T, int L, int H) {
+    W2Tag t;
+    t.v[0] = 0x77326c73746d3032ull;                       // "w2lstm02"
+    t.v[1] = drop ? seed : 0ull;
+    t.v[2] = (uint64_t)N;
+    t.v[3] = ((uint64_t)(uint32_t)T << 48) | ((uint64_t)(uint32_t)L << 40) | ((uint64_t)(uint32_t)H << 24) | (drop ? dropout_threshold(p) + 1u : 0u);
+    return t;
+}
+__global__ void w2_tag_kernel(uint64_t* tag, W2Tag t) {
+    for (int i = 0; i < 4; ++i) tag[i] = t.v[i];
+}
+
 // hidden states of one layer as fp32 [T][N][H] (b200_lstm_hidden_states)
 __global__ void __launch_bounds__(256)
 w2_unpack_kernel(const uint8_t* __restrict__ himg, int64_t N, int T, int H, int NT, float* __restrict__ out) {
@@ -431,11 +447,15 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
 // gradients, bf16, rows >= N zero), dc_{t-1}, and adds the tile's column sums of dG (the bias gradient) to its own slot of bsum.
 struct CellArgs {
     uint8_t* G; const float* c_prev; const uint4* dh_rec; const uint4* d_out; const float* dhT; float* dc; float* bsum;
+    const uint64_t* tag; W2Tag want;
     int first; int64_t N; int UG, GC, H;
 };
 
 __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
     __shared__ float red[4][4][32];
+    if (blockIdx.x == 0 && threadIdx.x == 0 &&
+        (a.tag[0] != a.want.v[0] || a.tag[1] != a.want.v[1] || a.tag[2] != a.want.v[2] || a.tag[3] != a.want.v[3]))
+        __trap();                                             // not the workspace this step's forward pass filled
     const int m = (int)(blockIdx.x / a.UG), ug = (int)(blockIdx.x % a.UG);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // a warp step = one 8-row group x the four unit octets of the group: lane = (row in group, octet), so that the fp32 slots of a
@@ -810,6 +830,7 @@ w2_wgrad_reduce_kernel(const float* __restrict__ part, int splits, int H, int XC
 struct W2Ws {
     uint8_t *himg, *xmask, *x0img, *gimg, *zero, *pack;
     uint32_t* bits;
+    uint64_t* tag;
     float *cst, *dc, *part, *bsum;
     uint4 *dx[2], *dh_rec;
     size_t himg_bytes, gimg_bytes, bits_words, pack_stride, slot_floats, total;
@@ -847,6 +868,7 @@ void w2_layout(const Geom& g, uint8_t* p, W2Ws* w) {
     w->part = (float*)take((size_t)w->splits * 4 * g.H * (2 * g.H) * 4);
     w->bsum = (float*)take((size_t)g.NT * g.UG * 128 * 4);
     w->zero = take(WCHUNK);
+    w->tag = (uint64_t*)take(sizeof(W2Tag));
     w->pack = take(w->pack_stride * g.L);
     w->total = off;
 }
@@ -907,6 +929,8 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
     if (rc) return rc;
     const bool mc = g_w2_mc != 0 && !(g_w2_dbg & 2);
     B200_CUDA(cudaMemsetAsync(w.zero, 0, WCHUNK, st));
+    w2_tag_kernel<<<1, 1, 0, st>>>(w.tag, make_tag(seed, drop, p, N, T, L, H));
+    B200_LAUNCH_CHECK("w2_tag_kernel");
     { TimedLaunch _t("w2_x0_kernel", st); w2_x0_kernel<<<ew_grid2((int64_t)T * g.NT * TM * 16), 256, 0, st>>>(x, N, T, F, g.NT, w.x0img); }
     B200_LAUNCH_CHECK("w2_x0_kernel");
     for (int l = 0; l < L; ++l) {
@@ -968,7 +992,7 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
 int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const float* x, int64_t N, int T, const float* stash_h,
                     const float* stash_c, const float* dhT, float* grads, float p, uint64_t seed, int training, void* workspace,
                     size_t ws_bytes, cudaStream_t st) {
-    (void)x; (void)stash_h; (void)stash_c; (void)seed;
+    (void)x; (void)stash_h; (void)stash_c;
     const Geom g = make_geom(N, T, F, H, L);
     W2Ws w;
     w2_layout(g, (uint8_t*)workspace, &w);
@@ -1008,6 +1032,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
         c.dhT = (top && t == T - 1) ? dhT : nullptr;
         c.dc = w.dc; c.bsum = w.bsum; c.first = t == T - 1 ? 1 : 0;
         c.N = N; c.UG = g.UG; c.GC = g.GC; c.H = H;
+        c.tag = w.tag; c.want = make_tag(seed, drop, p, N, T, L, H);
         { TimedLaunch _t("w2_cell_bwd_kernel", st); w2_cell_bwd_kernel<<<(unsigned)(g.NT * g.UG), 128, 0, st>>>(c); }
         B200_LAUNCH_CHECK("w2_cell_bwd_kernel");
         DgradArgs d;
