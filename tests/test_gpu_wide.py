@@ -271,3 +271,28 @@ def test_wide_images_option_selects_the_fp32_storage_path(data):
         lib.b200_set_option(b"wide_images", 1)
     assert out[0][0] == pytest.approx(out[1][0], rel=1e-3)
     assert rel_err(out[0][1], out[1][1]) < 2e-2
+
+
+def test_wide_forward_cluster_multicast_option_is_bit_identical(data):
+    """b200_set_option("wide_mc", 1): the forward kernel as two-CTA clusters that multicast the activation chunks to each other (all
+    sources are this GPU's own workspace) computes exactly what the default kernel computes."""
+    H, layers, p, seed = 256, 3, 0.3, 99
+    torch.manual_seed(5)
+    flat = O.flat_params(O.OracleLstm(3, H, layers, 0.0)).clone()
+    batch = B.DeviceBatch.from_reference(ref_batch(data, 0, 3), DEV)
+    lib = B._lib.load()
+    out = []
+    try:
+        for mc in (0, 1):
+            assert lib.b200_set_option(b"wide_mc", mc) == 0
+            e = make_engine(flat, layers, p, "tc_fast", 3, H)
+            e.forward(batch, training=True, dropout_seed=seed)
+            hs = [e.hidden_states(l, 3).clone() for l in range(layers)]
+            losses = e.heads(batch, "mse", 100.0, None, 1.0, True).clone()
+            e.backward(batch, True, dropout_seed=seed)
+            out.append((hs, losses, e.grads[: e.P].clone()))
+    finally:
+        lib.b200_set_option(b"wide_mc", 0)
+    for a, b in zip(out[0][0], out[1][0]):
+        assert torch.equal(a, b)
+    assert torch.equal(out[0][1], out[1][1]) and torch.equal(out[0][2], out[1][2])
