@@ -602,22 +602,33 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
         const uint32_t tl = tmem_base + ((uint32_t)(lq * 32) << 16) + (uint32_t)(j * 256);
         int i = 0;
         for (int task = blockIdx.x; task < ntask; task += gridDim.x, ++i) {
-            const int p = a.part[task % a.np], m = 2 * (task / a.np) + j;
+            const int p = (task % a.np) == 0 ? a.part[0] : a.part[1], m = 2 * (task / a.np) + j;
+            uint4* const outp = p == 0 ? a.out[0] : a.out[1];       // (selects, not indexed kernel parameters: no local-memory copy)
             const int64_t row = (int64_t)m * TM + r;
+            // the row's keep words are fetched while the MMAs of the task run (one global-load latency per 32 columns inside the
+            // loop below made the epilogue of the dx tasks ~11 k clk long)
+            uint32_t kws[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) kws[k] = 0xFFFFFFFFu;
+            if (p == 1 && a.keep != nullptr && m < a.NT && row < a.N) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) if (k < a.UG) kws[k] = a.keep[row * a.UG + k];
+            }
             mbar_wait(acc_full, (uint32_t)(i & 1));
             tc_fence_after();
             if (m < a.NT && !(a.dbg & 1)) {
-                const bool masked = p == 1 && a.keep != nullptr && row < a.N;
-                for (int c0 = 0; c0 < a.H; c0 += 32) {
+#pragma unroll
+                for (int cb = 0; cb < 8; ++cb) {
+                    const int c0 = cb * 32;
+                    if (c0 >= a.H) break;
                     float v[4][8];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) tmem_ld8(tl + (uint32_t)(c0 + k * 8), v[k]);
-                    uint32_t kw = 0xFFFFFFFFu;
-                    if (masked) kw = a.keep[row * a.UG + (c0 >> 5)];
+                    const uint32_t kw = kws[cb];
                     tmem_ld_wait();
 #pragma unroll
                     for (int k = 0; k < 4; ++k)          // bf16, one 16-byte slot per (row, octet): a warp store is 512 contiguous bytes
-                        a.out[p][slot_off(m, (c0 >> 3) + k, r, a.H) >> 3] = and_mask8(pack_bf8(v[k]), (kw >> (k * 8)) & 0xFFu);
+                        outp[slot_off(m, (c0 >> 3) + k, r, a.H) >> 3] = and_mask8(pack_bf8(v[k]), (kw >> (k * 8)) & 0xFFu);
                 }
             }
             tc_fence_before();
@@ -628,7 +639,8 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
         if (lane == 0) {
             uint32_t qa = 0, qb = 0;
             for (int task = blockIdx.x; task < ntask; task += gridDim.x) {
-                const int p = a.part[task % a.np], m0 = 2 * (task / a.np);
+                const int p = (task % a.np) == 0 ? a.part[0] : a.part[1], m0 = 2 * (task / a.np);
+                const uint8_t* const wdp = p == 0 ? a.wd[0] : a.wd[1];
                 const bool two = m0 + 1 < a.NT;
                 for (int ug = 0; ug < a.UG; ++ug, ++qa) {
                     const uint32_t sa = qa % DG_NSA;
@@ -645,7 +657,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) w2_dgrad_kernel(DgradArgs a) {
                         if (qb >= DG_NSB) mbar_wait(&emptyB[sb], ((qb / DG_NSB) - 1) & 1);
                         if (a.dbg & 6) { mbar_arrive(&fullB[sb]); continue; }
                         mbar_arrive_expect_tx(&fullB[sb], b_bytes);
-                        bulk_copy_g2s(smem + S::off_b + sb * WCHUNK, a.wd[p] + (size_t)(ug * 2 + half) * b_bytes, b_bytes, &fullB[sb]);
+                        bulk_copy_g2s(smem + S::off_b + sb * WCHUNK, wdp + (size_t)(ug * 2 + half) * b_bytes, b_bytes, &fullB[sb]);
                     }
                 }
             }
