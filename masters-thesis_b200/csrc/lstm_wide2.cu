@@ -330,14 +330,14 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     for (int j = 0; j < 8; ++j) cpv[uc][j] = 0.f;
                 }
             }
+            uint32_t keep = 0u;                   // keep bits of the row's 32 units (layer above), fetched before the wait as well
+            if (a.hmask != nullptr && live) keep = a.keep[row * a.UG + ug];
             mbar_wait(&acc_full[slot], (uint32_t)((i >> 2) & 1));
             tc_fence_after();
             uint8_t* gbase = a.gates + ((size_t)m * a.UG + ug) * WCHUNK + row_off;
             const size_t hoff = ((size_t)m * a.HC + (ug >> 2)) * WCHUNK + row_off + (uint32_t)((ug & 3) * 4) * 128u;
             uint8_t* hdst = a.hout + hoff;
             uint8_t* mdst = a.hmask ? a.hmask + hoff : nullptr;
-            uint32_t keep = 0u;
-            if (mdst != nullptr && live) keep = a.keep[row * a.UG + ug];
 #pragma unroll
             for (int uc = 0; uc < 4; ++uc) {
                 if (a.dbg & 1) break;
@@ -451,6 +451,7 @@ struct CellArgs {
     int first; int64_t N; int UG, GC, H;
 };
 
+// (121 registers, 4 blocks per SM.  Forcing 5 blocks per SM (96 registers, 56 bytes of spills) measured 426 instead of 311 ms per step.)
 __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
     __shared__ float red[4][4][32];
     if (blockIdx.x == 0 && threadIdx.x == 0 &&
