@@ -442,36 +442,61 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
 
 
 // ------------------------------------------------------------------------------------------------ backward cell
-// One block = the 128 rows of (row tile m, unit group ug), one thread = 32 hidden units of one row.  Reads the activated gates
-// (in place), c_{t-1}, the incoming dh (recurrent + from the layer above + from the heads) and dc; writes dG (pre-activation
-// gradients, bf16, rows >= N zero), dc_{t-1}, and adds the tile's column sums of dG (the bias gradient) to its own slot of bsum.
+// One block = the 128 rows x 32 hidden units of (row tile m, unit group ug).  Everything the block touches is contiguous in global
+// memory (the gate chunk, 32 KB; the row-slot slabs of c_{t-1} and dc, 16 KB each; of dh and d_out, 8 KB each), so the block
+// brings it into shared memory with five bulk copies, computes from there, and sends dG (in place) and dc_{t-1} back with two bulk
+// stores: no per-thread global access is left (ncu of the thread-load version: L1 71 % busy at 60 % of DRAM throughput).
+// Two blocks per SM overlap each other's copy and compute phases.  Output: dG (pre-activation gradients, bf16, rows >= N zero),
+// dc_{t-1}, and the tile's column sums of dG (the bias gradient) added to the block's own slot of bsum.
 struct CellArgs {
     uint8_t* G; const float* c_prev; const uint4* dh_rec; const uint4* d_out; const float* dhT; float* dc; float* bsum;
     const uint64_t* tag; W2Tag want;
     int first; int64_t N; int UG, GC, H;
 };
+constexpr int CELL_THREADS = 256;
+struct CellSmem {
+    static constexpr uint32_t off_g = 0, off_cp = WCHUNK, off_dc = off_cp + 16384, off_dh = off_dc + 16384, off_do = off_dh + 8192;
+    static constexpr uint32_t off_red = off_do + 8192, off_bar = off_red + 8 * 4 * 32 * 4, total = off_bar + 16;
+};
 
-// (121 registers, 4 blocks per SM.  Forcing 5 blocks per SM (96 registers, 56 bytes of spills) measured 426 instead of 311 ms per step.)
-__global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
-    __shared__ float red[4][4][32];
+__global__ void __launch_bounds__(CELL_THREADS, 2) w2_cell_bwd_kernel(CellArgs a) {
+    using S = CellSmem;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + S::off_bar);
+    float (*red)[4][32] = reinterpret_cast<float (*)[4][32]>(smem + S::off_red);
     if (blockIdx.x == 0 && threadIdx.x == 0 &&
         (a.tag[0] != a.want.v[0] || a.tag[1] != a.want.v[1] || a.tag[2] != a.want.v[2] || a.tag[3] != a.want.v[3]))
         __trap();                                             // not the workspace this step's forward pass filled
     const int m = (int)(blockIdx.x / a.UG), ug = (int)(blockIdx.x % a.UG);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // a warp step = one 8-row group x the four unit octets of the group: lane = (row in group, octet), so that the fp32 slots of a
-    // lane quartet and the 16-byte image slots of the warp are contiguous memory
-    const int rr = lane >> 2, uc = lane & 3;
+    uint8_t* gsrc = a.G + ((size_t)m * a.UG + ug) * WCHUNK;
+    const size_t e0 = slot_off(m, ug * 4, 0, a.H);             // first float of the block's four octet slabs (4 x 128 rows x 8)
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        fence_barrier_init();
+        const uint32_t bytes = WCHUNK + (a.c_prev ? 16384u : 0u) + (a.first ? 0u : 16384u) + (a.dh_rec ? 8192u : 0u) + (a.d_out ? 8192u : 0u);
+        mbar_arrive_expect_tx(bar, bytes);
+        bulk_copy_g2s(smem + S::off_g, gsrc, WCHUNK, bar);
+        if (a.c_prev) bulk_copy_g2s(smem + S::off_cp, a.c_prev + e0, 16384u, bar);
+        if (!a.first) bulk_copy_g2s(smem + S::off_dc, a.dc + e0, 16384u, bar);
+        if (a.dh_rec) bulk_copy_g2s(smem + S::off_dh, a.dh_rec + (e0 >> 3), 8192u, bar);
+        if (a.d_out) bulk_copy_g2s(smem + S::off_do, a.d_out + (e0 >> 3), 8192u, bar);
+    }
+    __syncthreads();
+    mbar_wait(bar, 0u);
+    // a warp step = one 8-row group x the four unit octets of the group: lane = (octet, row in group); the 8 lanes of a quarter warp
+    // read 128 contiguous bytes of an image slot
+    const int rr = lane & 7, uc = lane >> 3;
     float acc[32];
 #pragma unroll
     for (int k = 0; k < 32; ++k) acc[k] = 0.f;
 #pragma unroll 1
-    for (int it = 0; it < 4; ++it) {
-        const int rg = warp * 4 + it, r = rg * 8 + rr;
+    for (int it = 0; it < 2; ++it) {
+        const int rg = warp * 2 + it, r = rg * 8 + rr;
         const int64_t row = (int64_t)m * TM + r;
         const bool live = row < a.N;
-        uint8_t* gbase = a.G + ((size_t)m * a.UG + ug) * WCHUNK + (uint32_t)rg * WRG_BYTES + (uint32_t)rr * 16u;
-        const size_t e = slot_off(m, ug * 4 + uc, r, a.H);
+        uint8_t* gbase = smem + S::off_g + (uint32_t)rg * WRG_BYTES + (uint32_t)rr * 16u;
+        const uint32_t so = (uint32_t)(uc * 128 + r);          // slot of (octet, row) inside the block's slabs
         float gi[8], gf[8], gg[8], go[8], cp[8], dh[8], dc[8], v[32];
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(0 * 4 + uc) * 128u), gi);
         unpack_bf8(*reinterpret_cast<const uint4*>(gbase + (uint32_t)(1 * 4 + uc) * 128u), gf);
@@ -481,10 +506,10 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
         for (int j = 0; j < 8; ++j) { cp[j] = 0.f; dh[j] = 0.f; dc[j] = 0.f; }
         {
             float t8[8];
-            if (a.c_prev) ld8(a.c_prev + e, cp);
-            if (a.dh_rec) unpack_bf8(a.dh_rec[e >> 3], dh);
+            if (a.c_prev) ld8(reinterpret_cast<const float*>(smem + S::off_cp) + so * 8, cp);
+            if (a.dh_rec) unpack_bf8(reinterpret_cast<const uint4*>(smem + S::off_dh)[so], dh);
             if (a.d_out) {
-                unpack_bf8(a.d_out[e >> 3], t8);
+                unpack_bf8(reinterpret_cast<const uint4*>(smem + S::off_do)[so], t8);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) dh[j] += t8[j];
             }
@@ -493,7 +518,7 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) dh[j] += t8[j];
             }
-            if (!a.first) ld8(a.dc + e, dc);
+            if (!a.first) ld8(reinterpret_cast<const float*>(smem + S::off_dc) + so * 8, dc);
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -507,7 +532,7 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
             v[3 * 8 + j] = d_o * go[j] * (1.f - go[j]);
             dc[j] = dct * gf[j];
         }
-        st8(a.dc + e, dc);
+        st8(reinterpret_cast<float*>(smem + S::off_dc) + so * 8, dc);
         {
             float t8[8];
 #pragma unroll
@@ -520,23 +545,34 @@ __global__ void __launch_bounds__(128) w2_cell_bwd_kernel(CellArgs a) {
 #pragma unroll
         for (int k = 0; k < 32; ++k) acc[k] += v[k];
     }
-    // bias gradient: sum the 32 values (4 gates x 8 units of the lane's octet) over the 8 rows of the warp step; lane (rr, uc) ends up
+    // results back to global memory through the async proxy
+    fence_proxy_async();
+    // bias gradient: sum the 32 values (4 gates x 8 units of the lane's octet) over the 8 rows of the warp step; lane (uc, rr) ends up
     // with values rr * 4 .. rr * 4 + 3
 #pragma unroll
-    for (int S = 16; S >= 4; S >>= 1) {
-        const bool up = (lane & S) != 0;
+    for (int S2 = 16, LB = 4; S2 >= 4; S2 >>= 1, LB >>= 1) {
+        const bool up = (lane & LB) != 0;
 #pragma unroll
-        for (int k = 0; k < S; ++k) {
-            const float lo = acc[k], hi = acc[k + S];
-            acc[k] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, S);
+        for (int k = 0; k < 16; ++k) {
+            if (k < S2) {
+                const float lo = acc[k], hi = acc[k + S2];
+                acc[k] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, LB);
+            }
         }
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) red[warp][uc][rr * 4 + k] = acc[k];
     __syncthreads();
-    {
+    if (threadIdx.x == 0) {
+        bulk_copy_s2g(gsrc, smem + S::off_g, WCHUNK);
+        bulk_copy_s2g(a.dc + e0, smem + S::off_dc, 16384u);
+        bulk_commit_wait_read();
+    }
+    if (threadIdx.x < 128) {
         const int o = threadIdx.x >> 5, idx = threadIdx.x & 31, gate = idx >> 3, j = idx & 7;
-        const float sum = (red[0][o][idx] + red[1][o][idx]) + (red[2][o][idx] + red[3][o][idx]);
+        float sum = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) sum += red[w][o][idx];
         a.bsum[(size_t)blockIdx.x * 128 + gate * 32 + o * 8 + j] += sum;
     }
 }
@@ -1017,6 +1053,8 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
     if (rc) return rc;
     rc = opt_in_smem(w2_wgrad_kernel, WgSmem::total, "w2_wgrad_kernel smem");
     if (rc) return rc;
+    rc = opt_in_smem(w2_cell_bwd_kernel, CellSmem::total, "w2_cell_bwd_kernel smem");
+    if (rc) return rc;
     const LayerP lp = layer_p(params, F, H, l);
     const int64_t poff = lp.w_ih - params;
     float* gw_ih = grads + poff;
@@ -1046,7 +1084,7 @@ int wide2_bwd_layer(int layer, const float* params, int F, int H, int L, const f
         c.dc = w.dc; c.bsum = w.bsum; c.first = t == T - 1 ? 1 : 0;
         c.N = N; c.UG = g.UG; c.GC = g.GC; c.H = H;
         c.tag = w.tag; c.want = make_tag(seed, drop, p, N, T, L, H);
-        { TimedLaunch _t("w2_cell_bwd_kernel", st); w2_cell_bwd_kernel<<<(unsigned)(g.NT * g.UG), 128, 0, st>>>(c); }
+        { TimedLaunch _t("w2_cell_bwd_kernel", st); w2_cell_bwd_kernel<<<(unsigned)(g.NT * g.UG), CELL_THREADS, CellSmem::total, st>>>(c); }
         B200_LAUNCH_CHECK("w2_cell_bwd_kernel");
         DgradArgs d;
         d.dG = c.G; d.wd[0] = pk + pl.wd_h; d.wd[1] = l > 0 ? pk + pl.wd_x : nullptr;
