@@ -263,7 +263,11 @@ struct FwdArgs {
     int64_t N; int NT, XC, HC, UG, GC, H;
     int dbg;       // timing experiments (option "wide_dbg", results are wrong when set): 1 = no cell math / stores, 2 = no operand loads,
                    // 8 = cell math but no stores, 16 = no c_{t-1} loads
+    unsigned long long* trace;   // option "wide_dbg" bit 32: clock64 stamps of CTA 0, trace[(role * 256 + tile) * 4 + event] (tools/wide2_trace.py)
 };
+__device__ __forceinline__ void w2_stamp(unsigned long long* tr, int role, int tile, int ev) {
+    if (tr != nullptr && tile < 256) tr[(role * 256 + tile) * 4 + ev] = (unsigned long long)clock64();
+}
 constexpr int FWD_NST = 3;
 constexpr int FWD_GROUPS = 3;                            // epilogue warp groups (4 warps each) taking the tiles of a CTA in turn
 constexpr int FWD_THREADS = (FWD_GROUPS * 4 + 2) * 32;
@@ -334,8 +338,11 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             }
             uint32_t keep = 0u;                   // keep bits of the row's 32 units (layer above), fetched before the wait as well
             if (a.hmask != nullptr && live) keep = a.keep[row * a.UG + ug];
+            unsigned long long* const tr = (blockIdx.x == 0 && lq == 0 && lane == 0) ? a.trace : nullptr;
+            w2_stamp(tr, 0, i, 0);
             mbar_wait(&acc_full[slot], (uint32_t)((i >> 2) & 1));
             tc_fence_after();
+            w2_stamp(tr, 0, i, 1);
             uint8_t* gbase = a.gates + ((size_t)m * a.UG + ug) * WCHUNK + row_off;
             const size_t hoff = ((size_t)m * a.HC + (ug >> 2)) * WCHUNK + row_off + (uint32_t)((ug & 3) * 4) * 128u;
             uint8_t* hdst = a.hout + hoff;
@@ -382,6 +389,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_free[slot]);
+            w2_stamp(tr, 0, i, 2);
         }
     } else if (warp == LD_WARP) {
         // ================================ loader ================================================================
@@ -389,7 +397,10 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             mbar_arrive_expect_tx(w_ready, (uint32_t)KC * CHUNK);
             for (int kc = 0; kc < KC; ++kc) bulk_copy_g2s(smem + S::off_w + kc * CHUNK, a.wf + ((size_t)ug * KC + kc) * CHUNK, CHUNK, w_ready);
             uint32_t q = 0;
-            for (int m = first; m < a.NT; m += stride) {
+            unsigned long long* const tr = blockIdx.x == 0 ? a.trace : nullptr;
+            int li = 0;
+            for (int m = first; m < a.NT; m += stride, ++li) {
+                w2_stamp(tr, 2, li, 0);
                 const int mp = m + W2_PF_DIST * stride;          // L2 prefetch: the layer input of a later tile comes from HBM
                 if (W2_PF_DIST > 0 && mp < a.NT) {
                     if (ug < 2 * a.XC) prefetch_l2(a.xin + ((size_t)mp * a.XC + (ug >> 1)) * WCHUNK + (size_t)(ug & 1) * (WCHUNK / 2), WCHUNK / 2);
@@ -403,7 +414,9 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     mbar_arrive_expect_tx(&full[st], WCHUNK);
                     if (MC) bulk_copy_g2s_mc(smem + S::off_ring + st * WCHUNK + crank * (WCHUNK / 2), src + crank * (WCHUNK / 2), WCHUNK / 2, &full[st], (uint16_t)3);
                     else bulk_copy_g2s(smem + S::off_ring + st * WCHUNK, src, WCHUNK, &full[st]);
+                    if (kc == 0) w2_stamp(tr, 2, li, 1);
                 }
+                w2_stamp(tr, 2, li, 2);
             }
         }
         __syncwarp();
@@ -417,13 +430,17 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
             int i = 0;
             for (int m = first; m < a.NT; m += stride, ++i) {
                 const int slot = i & 3;
+                unsigned long long* const tr = blockIdx.x == 0 ? a.trace : nullptr;
+                w2_stamp(tr, 1, i, 0);
                 if (i >= 4) mbar_wait(&acc_free[slot], (uint32_t)(((i >> 2) - 1) & 1));
                 tc_fence_after();
+                w2_stamp(tr, 1, i, 1);
                 const uint32_t d = tmem_base + (uint32_t)(slot * 128);
                 for (int kc = 0; kc < nk; ++kc, ++q) {
                     const uint32_t st = q % FWD_NST;
                     mbar_wait(&full[st], (q / FWD_NST) & 1);
                     tc_fence_after();
+                    if (kc == 0) w2_stamp(tr, 1, i, 2);
                     const uint32_t aa = s_base + S::off_ring + st * WCHUNK, bb = s_base + S::off_w + (uint32_t)(2 * kc) * CHUNK;
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks)          // two K = 64 halves of the activation chunk, one weight image each
@@ -432,6 +449,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) w2_fwd_kernel(FwdArgs a) {
                     if (MC) umma_commit_mc(&empty[st], (uint16_t)3); else umma_commit(&empty[st]);
                 }
                 umma_commit(&acc_full[slot]);
+                w2_stamp(tr, 1, i, 3);
             }
         }
         __syncwarp();
@@ -1021,6 +1039,7 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
             a.gates = w.gimg + (size_t)l * w.gimg_bytes + (size_t)t * gstep;
             a.h_last = (l == L - 1 && t == T - 1) ? stash_h + (int64_t)l * lsz + (int64_t)t * NH : nullptr;
             a.N = N; a.NT = g.NT; a.XC = g.xc(l); a.HC = g.HC; a.UG = g.UG; a.GC = g.GC; a.H = H; a.dbg = g_w2_dbg;
+            a.trace = ((g_w2_dbg & 32) && l == L - 1 && t == T / 2) ? reinterpret_cast<unsigned long long*>(stash_h) : nullptr;
             if (mc) {
                 cudaLaunchConfig_t cfg = {};
                 cfg.gridDim = dim3((unsigned)(lanes * g.UG)); cfg.blockDim = dim3(FWD_THREADS); cfg.dynamicSmemBytes = FwdSmem::total; cfg.stream = st;
