@@ -270,3 +270,25 @@ def test_fama_french_loader(tmp_path):
         p_ref, m_ref = src.data.FamaFrench25Portfolios.load(tmp_path)
         np.testing.assert_allclose(stocks.numpy(), p_ref.numpy(), rtol=1e-6, atol=1e-6)
         np.testing.assert_allclose(market.numpy(), m_ref.numpy(), rtol=1e-6, atol=1e-6)
+
+
+def test_wide_workspace_sizes_are_pure_arithmetic():
+    """b200_lstm_workspace_bytes needs no GPU: the bf16 wide engine (operand images, lstm_wide2.cu) needs less workspace per row than the
+    fp32-storage path (b200_set_option("wide_images", 0)), both grow linearly with the rows, and unknown options are rejected."""
+    from masters_thesis_b200 import _lib
+    lib = _lib.load()
+    fast, precise = _lib.MODES["tc_fast"], _lib.MODES["tc_precise"]
+    T, F, H, L = 60, 3, 256, 8
+    img = [int(lib.b200_lstm_workspace_bytes(fast, n, T, F, H, L)) for n in (12800, 25600, 51200)]
+    try:
+        assert lib.b200_set_option(b"wide_images", 0) == 0
+        f32 = [int(lib.b200_lstm_workspace_bytes(fast, n, T, F, H, L)) for n in (12800, 25600, 51200)]
+    finally:
+        lib.b200_set_option(b"wide_images", 1)
+    assert all(a > 0 for a in img) and all(a < b for a, b in zip(img, f32))
+    # linear in the rows up to the constant part (packed weights, split-K partials)
+    assert abs((img[2] - img[1]) - 2 * (img[1] - img[0])) < 0.01 * img[2]
+    per_row_step_layer = (img[2] - img[1]) / (25600 * T * L)
+    assert 3000 < per_row_step_layer < 5000            # gates 2 KB + h and masked h 1 KB + c 1 KB + dx
+    assert int(lib.b200_lstm_workspace_bytes(precise, 51200, T, F, H, L)) == f32[2]
+    assert lib.b200_set_option(b"no_such_option", 1) != 0
