@@ -90,7 +90,10 @@ B200_API int b200_timing_report(char* buf_host, size_t buf_bytes);
  *   "tc_dgrad"     products of the data gradient, precise mode: 3 (default) or 2
  *   "wide_fuse"    1 = LSTM cell in the epilogue of the wide engine's recurrent GEMM, fp32-storage path (default 0)
  *   "wide_images"  0 = run bf16 mode of the wide engine on the fp32-storage path of csrc/lstm_wide.cu instead of the
- *                  operand-image engine of csrc/lstm_wide2.cu (default 1); changes b200_lstm_workspace_bytes */
+ *                  operand-image engine of csrc/lstm_wide2.cu (default 1); changes b200_lstm_workspace_bytes
+ *   "wide_mc"      1 = forward kernel of that engine as two-CTA clusters whose CTAs multicast the activation chunks to each other
+ *                  (default 0; used only when the workspace is device memory of the GPU the launch runs on)
+ *   "wide_dbg"     timing ablations of that engine (bit mask, results are wrong when set; bit 32 = event trace) */
 B200_API int b200_set_option(const char* name, int value);
 
 /* number of fp32 parameters of the model (src/model.py:88-97): 51,074 for F=3,H=64,L=2 */

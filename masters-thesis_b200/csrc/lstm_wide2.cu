@@ -996,7 +996,16 @@ int wide2_fwd(const float* params, int F, int H, int L, const float* x, int64_t 
     if (rc) return rc;
     rc = opt_in_smem(w2_fwd_kernel<true>, FwdSmem::total, "w2_fwd_kernel smem");
     if (rc) return rc;
-    const bool mc = g_w2_mc != 0 && !(g_w2_dbg & 2);
+    // The multicast variant is used only when the workspace (the source of every multicast copy) is ordinary device memory of the
+    // GPU this launch runs on; anything else (peer, mapped or managed memory) takes the plain kernel.
+    bool mc = g_w2_mc != 0 && !(g_w2_dbg & 2);
+    if (mc) {
+        cudaPointerAttributes pa;
+        int dev = -1;
+        mc = cudaGetDevice(&dev) == cudaSuccess && cudaPointerGetAttributes(&pa, workspace) == cudaSuccess &&
+             pa.type == cudaMemoryTypeDevice && pa.device == dev;
+        cudaGetLastError();
+    }
     B200_CUDA(cudaMemsetAsync(w.zero, 0, WCHUNK, st));
     w2_tag_kernel<<<1, 1, 0, st>>>(w.tag, make_tag(seed, drop, p, N, T, L, H));
     B200_LAUNCH_CHECK("w2_tag_kernel");
